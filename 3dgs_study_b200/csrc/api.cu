@@ -1,0 +1,227 @@
+// api.cu -- the C ABI of libb200splat.so (declared in include/b200splat.h): argument validation,
+// buffer carving, stage orchestration, optional per-stage timing, error strings.
+#include <cstdio>
+#include <string>
+
+#include "splat_internal.cuh"
+
+using namespace b200splat;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char* where) {
+    return fail(B200SPLAT_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+
+#define CU(call, where)                                         \
+    do {                                                        \
+        cudaError_t _e = (call);                                \
+        if (_e != cudaSuccess) return cuda_fail(_e, where);     \
+    } while (0)
+
+// In debug mode every stage is followed by a synchronisation + error check, like the `debug` flag
+// of the call being replaced (/root/reference/README.md:159-162).
+#define STAGE(call, where)                                                          \
+    do {                                                                            \
+        cudaError_t _e = (call);                                                    \
+        if (_e != cudaSuccess) return cuda_fail(_e, where);                         \
+        if (debug) {                                                                \
+            _e = cudaStreamSynchronize(stream);                                     \
+            if (_e != cudaSuccess) return cuda_fail(_e, where " (debug sync)");     \
+        }                                                                           \
+    } while (0)
+
+struct StageTimer {
+    bool on;
+    cudaStream_t s;
+    cudaEvent_t ev[10];
+    int n = 0;
+    StageTimer(bool on_, cudaStream_t s_) : on(on_), s(s_) {
+        if (on) for (auto& e : ev) cudaEventCreate(&e);
+    }
+    ~StageTimer() {
+        if (on) for (auto& e : ev) cudaEventDestroy(e);
+    }
+    void mark() { if (on && n < 10) cudaEventRecord(ev[n++], s); }
+    float ms(int i) {
+        float t = 0.f;
+        if (on && i + 1 < n) cudaEventElapsedTime(&t, ev[i], ev[i + 1]);
+        return t;
+    }
+};
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+int validate(const b200splat_view* v, const b200splat_gaussians* g) {
+    if (!v || !g) return fail(B200SPLAT_ERR_INVALID_ARG, "null view/gaussians");
+    if (g->P < 0 || v->image_width <= 0 || v->image_height <= 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad sizes");
+    if (v->sh_degree < 0 || v->sh_degree > 3) return fail(B200SPLAT_ERR_INVALID_ARG, "sh_degree must be in [0,3]");
+    if (!(v->tanfovx > 0.f) || !(v->tanfovy > 0.f)) return fail(B200SPLAT_ERR_INVALID_ARG, "tanfov must be positive");
+    if (!v->bg || !v->viewmatrix || !v->projmatrix) return fail(B200SPLAT_ERR_INVALID_ARG, "null bg/view/proj");
+    if (g->P > 0) {
+        if (!g->means3D || !g->opacities) return fail(B200SPLAT_ERR_INVALID_ARG, "null means3D/opacities");
+        if ((g->shs == nullptr) == (g->colors_precomp == nullptr))
+            return fail(B200SPLAT_ERR_INVALID_ARG, "provide exactly one of shs / colors_precomp");
+        const bool sr = g->scales != nullptr && g->rotations != nullptr;
+        if ((g->scales != nullptr) != (g->rotations != nullptr) || sr == (g->cov3D_precomp != nullptr))
+            return fail(B200SPLAT_ERR_INVALID_ARG, "provide exactly one of (scales, rotations) / cov3D_precomp");
+        if (g->shs) {
+            if (!v->campos) return fail(B200SPLAT_ERR_INVALID_ARG, "campos required with shs");
+            if (g->M < (v->sh_degree + 1) * (v->sh_degree + 1))
+                return fail(B200SPLAT_ERR_INVALID_ARG, "shs holds fewer coefficients than sh_degree needs");
+            if (!aligned16(g->shs)) return fail(B200SPLAT_ERR_INVALID_ARG, "shs must be 16-byte aligned");
+        }
+        if (g->rotations && !aligned16(g->rotations)) return fail(B200SPLAT_ERR_INVALID_ARG, "rotations must be 16-byte aligned");
+    }
+    return B200SPLAT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b200splat_last_error(void) { return g_last_error.c_str(); }
+int b200splat_version(void) { return B200SPLAT_VERSION; }
+
+size_t b200splat_geom_bytes(int32_t P) { return carve_geom(nullptr, P).total; }
+size_t b200splat_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).total; }
+size_t b200splat_binning_bytes(int32_t num_rendered) { return carve_binning(nullptr, num_rendered, 64).total; }
+
+int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g, const b200splat_forward_out* out,
+                      const b200splat_allocators* alloc, int32_t* num_rendered, b200splat_stage_times* times,
+                      void* stream_) {
+    int rc = validate(view, g);
+    if (rc) return rc;
+    if (!out || !out->color || (g->P > 0 && !out->radii)) return fail(B200SPLAT_ERR_INVALID_ARG, "null outputs");
+    if (!alloc || !alloc->alloc || !num_rendered) return fail(B200SPLAT_ERR_INVALID_ARG, "null allocator / num_rendered");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const bool debug = view->debug != 0;
+    const int P = g->P, W = view->image_width, H = view->image_height;
+
+    void* geom_mem = alloc->alloc(alloc->geom_ctx, b200splat_geom_bytes(P));
+    void* img_mem = alloc->alloc(alloc->image_ctx, b200splat_image_bytes(W, H));
+    if (!geom_mem || !img_mem) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (geometry / image buffer)");
+    GeomView gv = carve_geom(geom_mem, P);
+    ImgView iv = carve_image(img_mem, W, H);
+
+    StageTimer tm(times != nullptr, stream);
+    tm.mark();
+    STAGE(launch_preprocess_fwd(*view, *g, gv, out->radii, stream), "preprocess");
+    tm.mark();
+    STAGE(launch_scan(gv, P, stream), "scan");
+    uint32_t R = 0;
+    if (P > 0) {
+        CU(cudaMemcpyAsync(&R, gv.offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, stream), "read num_rendered");
+        CU(cudaStreamSynchronize(stream), "sync num_rendered");
+    }
+    if (R > 0x7fffffffu) return fail(B200SPLAT_ERR_INVALID_ARG, "more than 2^31-1 tile/Gaussian pairs");
+    tm.mark();
+    *num_rendered = (int32_t)R;
+
+    void* bin_mem = alloc->alloc(alloc->binning_ctx, b200splat_binning_bytes((int32_t)R));
+    if (!bin_mem) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (binning buffer)");
+    const int end_bit = sort_end_bit(W, H);
+    BinView bv = carve_binning(bin_mem, (int)R, 64);
+
+    STAGE(launch_duplicate(gv, out->radii, P, W, H, bv, stream), "duplicateWithKeys");
+    tm.mark();
+    STAGE(launch_sort(bv, (int)R, end_bit, stream), "sort");
+    tm.mark();
+    STAGE(launch_ranges(bv, (int)R, iv, W, H, stream), "identifyTileRanges");
+    tm.mark();
+    STAGE(launch_render_fwd(*view, gv, bv, iv, out->color, out->invdepth, stream), "render");
+    tm.mark();
+    if (times) {
+        CU(cudaStreamSynchronize(stream), "timing sync");
+        times->preprocess_ms = tm.ms(0); times->scan_ms = tm.ms(1); times->duplicate_ms = tm.ms(2);
+        times->sort_ms = tm.ms(3); times->ranges_ms = tm.ms(4); times->render_ms = tm.ms(5);
+    }
+    return B200SPLAT_OK;
+}
+
+int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
+                       const void* geom, const void* binning, const void* image, int32_t num_rendered,
+                       const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
+                       b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times,
+                       void* stream_) {
+    int rc = validate(view, g);
+    if (rc) return rc;
+    if (!grads || !grads->dL_dmeans3D) return fail(B200SPLAT_ERR_INVALID_ARG, "grads->dL_dmeans3D is required");
+    if (g->shs && !grads->dL_dsh) return fail(B200SPLAT_ERR_INVALID_ARG, "grads->dL_dsh is required with shs");
+    if (grads->dL_dsh && !aligned16(grads->dL_dsh)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dsh must be 16-byte aligned");
+    if (grads->dL_drotations && !aligned16(grads->dL_drotations))
+        return fail(B200SPLAT_ERR_INVALID_ARG, "dL_drotations must be 16-byte aligned");
+    if (!dL_dout_color || !scratch_alloc) return fail(B200SPLAT_ERR_INVALID_ARG, "null dL_dout_color / scratch allocator");
+    if (dL_dout_invdepth) return fail(B200SPLAT_ERR_INVALID_ARG, "inverse-depth gradients are not implemented");
+    if (g->P > 0 && (!radii || !geom || !binning || !image)) return fail(B200SPLAT_ERR_INVALID_ARG, "null forward state");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const bool debug = view->debug != 0;
+    const int P = g->P, W = view->image_width, H = view->image_height;
+    if (P == 0) return B200SPLAT_OK;
+
+    GeomView gv = carve_geom(const_cast<void*>(geom), P);
+    BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, 64);
+    ImgView iv = carve_image(const_cast<void*>(image), W, H);
+
+    const size_t acc_bytes = (size_t)P * 12 * sizeof(float);
+    float* acc = (float*)scratch_alloc(scratch_ctx, acc_bytes);
+    if (!acc) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (backward scratch)");
+
+    StageTimer tm(times != nullptr, stream);
+    tm.mark();
+    CU(cudaMemsetAsync(acc, 0, acc_bytes, stream), "clear backward scratch");
+    if (num_rendered > 0)
+        STAGE(launch_render_bwd(*view, gv, bv.vals_sorted, iv, dL_dout_color, dL_dout_invdepth, acc, stream), "render backward");
+    tm.mark();
+    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, *grads, stream), "preprocess backward");
+    tm.mark();
+    if (times) {
+        CU(cudaStreamSynchronize(stream), "timing sync");
+        times->render_bwd_ms = tm.ms(0); times->preprocess_bwd_ms = tm.ms(1);
+    }
+    return B200SPLAT_OK;
+}
+
+int b200splat_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                           uint8_t* present, void* stream_) {
+    (void)projmatrix;
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return fail(B200SPLAT_ERR_INVALID_ARG, "bad arguments");
+    CU(launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream_), "mark_visible");
+    return B200SPLAT_OK;
+}
+
+int b200splat_export_state(int32_t P, int32_t width, int32_t height, int32_t num_rendered, const int32_t* radii,
+                           const void* geom, const void* binning, const void* image, const b200splat_state_out* out,
+                           void* stream_) {
+    if (!out || P < 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (geom && radii && P > 0) {
+        GeomView gv = carve_geom(const_cast<void*>(geom), P);
+        CU(launch_export_geom(P, radii, gv, *out, stream), "export geometry");
+    }
+    if (binning && num_rendered > 0) {
+        BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, 64);
+        if (out->keys_sorted)
+            CU(cudaMemcpyAsync(out->keys_sorted, bv.keys_sorted, sizeof(uint64_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, stream), "export keys");
+        if (out->vals_sorted)
+            CU(cudaMemcpyAsync(out->vals_sorted, bv.vals_sorted, sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, stream), "export vals");
+    }
+    if (image) {
+        ImgView iv = carve_image(const_cast<void*>(image), width, height);
+        const size_t T = (size_t)((width + TILE - 1) / TILE) * ((height + TILE - 1) / TILE);
+        const size_t N = (size_t)width * height;
+        if (out->ranges) CU(cudaMemcpyAsync(out->ranges, iv.ranges, sizeof(int2) * T, cudaMemcpyDeviceToDevice, stream), "export ranges");
+        if (out->final_T) CU(cudaMemcpyAsync(out->final_T, iv.final_T, sizeof(float) * N, cudaMemcpyDeviceToDevice, stream), "export final_T");
+        if (out->n_contrib) CU(cudaMemcpyAsync(out->n_contrib, iv.n_contrib, sizeof(uint32_t) * N, cudaMemcpyDeviceToDevice, stream), "export n_contrib");
+    }
+    return B200SPLAT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,527 @@
+// preprocess.cu -- per-Gaussian forward (cull, 3D covariance, EWA projection, conic, radius, tile
+// rectangle, SH -> RGB, packed splat record) and per-Gaussian backward (conic -> cov2D -> cov3D /
+// mean, mean2D -> mean3D, SH, cov3D -> scale / rotation), sm_100a.
+//
+// Replaces the per-Gaussian stages of _C.rasterize_gaussians / _C.rasterize_gaussians_backward
+// named by BASELINE.json's north_star (call site /root/reference/gaussian_renderer/__init__.py:98-106).
+// Both kernels are HBM-bound: one thread per Gaussian, cull before the 12*M-byte SH row is touched,
+// 16-byte vector loads/stores for the SH rows and the packed record.
+#include "splat_internal.cuh"
+
+namespace b200splat {
+
+namespace {
+
+constexpr int PRE_THREADS = 256;
+
+struct PreParams {
+    int P, D, M, W, H, gx, gy;
+    float tanfovx, tanfovy, focal_x, focal_y, mod;
+    int antialiasing;
+    const float* means3D; const float* scales; const float* rotations; const float* opacities;
+    const float* shs; const float* colors_precomp; const float* cov3D_precomp;
+    const float* view; const float* proj; const float* campos;
+};
+
+// colour of one Gaussian from its SH row (canonical chain: res = b0*sh0; res = fma(bk, shk, res))
+__device__ __forceinline__ void eval_color_sh(const float* __restrict__ sh_row, int M, int D, float dx, float dy,
+                                              float dz, float* rgb, unsigned& clamped) {
+    float len = csqrt(cfma(dz, dz, cfma(dy, dy, cmul(dx, dx))));
+    float b[16];
+    sh_basis(D, cdiv(dx, len), cdiv(dy, len), cdiv(dz, len), b);
+    const int nb = (D + 1) * (D + 1);
+    float r0, r1, r2;
+    if ((M & 3) == 0) {
+        // 3*M floats, 16-byte aligned row: vector loads
+        const float4* v = reinterpret_cast<const float4*>(sh_row);
+        float f[48];
+        const int nv = (3 * nb + 3) >> 2;
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            if (k < nv) {
+                float4 t = __ldg(v + k);
+                f[4 * k] = t.x; f[4 * k + 1] = t.y; f[4 * k + 2] = t.z; f[4 * k + 3] = t.w;
+            }
+        }
+        r0 = cmul(b[0], f[0]); r1 = cmul(b[0], f[1]); r2 = cmul(b[0], f[2]);
+#pragma unroll
+        for (int k = 1; k < 16; k++) {
+            if (k < nb) {
+                r0 = cfma(b[k], f[3 * k], r0); r1 = cfma(b[k], f[3 * k + 1], r1); r2 = cfma(b[k], f[3 * k + 2], r2);
+            }
+        }
+    } else {
+        r0 = cmul(b[0], __ldg(sh_row)); r1 = cmul(b[0], __ldg(sh_row + 1)); r2 = cmul(b[0], __ldg(sh_row + 2));
+        for (int k = 1; k < nb; k++) {
+            r0 = cfma(b[k], __ldg(sh_row + 3 * k), r0);
+            r1 = cfma(b[k], __ldg(sh_row + 3 * k + 1), r1);
+            r2 = cfma(b[k], __ldg(sh_row + 3 * k + 2), r2);
+        }
+    }
+    r0 = cadd(r0, 0.5f); r1 = cadd(r1, 0.5f); r2 = cadd(r2, 0.5f);
+    clamped = (r0 < 0.0f ? 1u : 0u) | (r1 < 0.0f ? 2u : 0u) | (r2 < 0.0f ? 4u : 0u);
+    rgb[0] = fmaxf(r0, 0.0f); rgb[1] = fmaxf(r1, 0.0f); rgb[2] = fmaxf(r2, 0.0f);
+}
+
+// Geometry shared by forward and backward: everything up to the 2D covariance.
+struct Proj2D {
+    float tz, txc, tyc;        // view depth, clamped view x / y
+    float txtz, tytz;
+    float M0[3], M1[3];        // rows of J * Wv
+    float N0[3], N1[3];        // rows of (J Wv) Sigma
+    float cov00, cov01, cov11;
+};
+
+__device__ __forceinline__ void project_cov(const ViewConsts& vc, float tx, float ty, float tz, const float* c6,
+                                            float focal_x, float focal_y, float limx, float limy, Proj2D& o) {
+    o.tz = tz;
+    o.txtz = cdiv(tx, tz); o.tytz = cdiv(ty, tz);
+    o.txc = cmul(fminf(limx, fmaxf(-limx, o.txtz)), tz);
+    o.tyc = cmul(fminf(limy, fmaxf(-limy, o.tytz)), tz);
+    float tz2 = cmul(tz, tz);
+    float J00 = cdiv(focal_x, tz), J02 = cdiv(-cmul(focal_x, o.txc), tz2);
+    float J11 = cdiv(focal_y, tz), J12 = cdiv(-cmul(focal_y, o.tyc), tz2);
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        o.M0[k] = cfma(J02, vc.view[4 * k + 2], cmul(J00, vc.view[4 * k + 0]));
+        o.M1[k] = cfma(J12, vc.view[4 * k + 2], cmul(J11, vc.view[4 * k + 1]));
+    }
+    const float S[3][3] = {{c6[0], c6[1], c6[2]}, {c6[1], c6[3], c6[4]}, {c6[2], c6[4], c6[5]}};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        o.N0[k] = cdot3(o.M0[0], S[0][k], o.M0[1], S[1][k], o.M0[2], S[2][k]);
+        o.N1[k] = cdot3(o.M1[0], S[0][k], o.M1[1], S[1][k], o.M1[2], S[2][k]);
+    }
+    o.cov00 = cdot3(o.N0[0], o.M0[0], o.N0[1], o.M0[1], o.N0[2], o.M0[2]);
+    o.cov01 = cdot3(o.N0[0], o.M1[0], o.N0[1], o.M1[1], o.N0[2], o.M1[2]);
+    o.cov11 = cdot3(o.N1[0], o.M1[0], o.N1[1], o.M1[1], o.N1[2], o.M1[2]);
+}
+
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p, float* __restrict__ depths,
+                                                                     float4* __restrict__ rec,
+                                                                     uint32_t* __restrict__ tiles,
+                                                                     int32_t* __restrict__ radii) {
+    __shared__ ViewConsts vc;
+    load_view_consts(vc, p.view, p.proj, p.campos);
+    const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
+    if (i >= p.P) return;
+
+    const float x = __ldg(p.means3D + 3 * i), y = __ldg(p.means3D + 3 * i + 1), z = __ldg(p.means3D + 3 * i + 2);
+    const float tz = cadd(cfma(vc.view[10], z, cfma(vc.view[6], y, cmul(vc.view[2], x))), vc.view[14]);
+    int radius = 0;
+    uint32_t area = 0;
+    if (tz > NEAR_Z) {
+        const float tx = cadd(cfma(vc.view[8], z, cfma(vc.view[4], y, cmul(vc.view[0], x))), vc.view[12]);
+        const float ty = cadd(cfma(vc.view[9], z, cfma(vc.view[5], y, cmul(vc.view[1], x))), vc.view[13]);
+        const float hx = cadd(cfma(vc.proj[8], z, cfma(vc.proj[4], y, cmul(vc.proj[0], x))), vc.proj[12]);
+        const float hy = cadd(cfma(vc.proj[9], z, cfma(vc.proj[5], y, cmul(vc.proj[1], x))), vc.proj[13]);
+        const float hw = cadd(cfma(vc.proj[11], z, cfma(vc.proj[7], y, cmul(vc.proj[3], x))), vc.proj[15]);
+        const float pw = __frcp_rn(cadd(hw, 0.0000001f));
+        const float ndcx = cmul(hx, pw), ndcy = cmul(hy, pw);
+
+        float c6[6];
+        if (p.cov3D_precomp) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) c6[k] = __ldg(p.cov3D_precomp + 6 * (size_t)i + k);
+        } else {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + i);
+            cov3d_from_scale_rot(__ldg(p.scales + 3 * i), __ldg(p.scales + 3 * i + 1), __ldg(p.scales + 3 * i + 2),
+                                 p.mod, q, c6);
+        }
+        Proj2D pj;
+        project_cov(vc, tx, ty, tz, c6, p.focal_x, p.focal_y, cmul(1.3f, p.tanfovx), cmul(1.3f, p.tanfovy), pj);
+        const float a = cadd(pj.cov00, 0.3f), b = pj.cov01, c = cadd(pj.cov11, 0.3f);
+        const float det = cfma(a, c, -cmul(b, b));
+        if (det != 0.0f) {
+            float hconv = 1.0f;
+            if (p.antialiasing) {
+                float det0 = cfma(pj.cov00, pj.cov11, -cmul(pj.cov01, pj.cov01));
+                hconv = csqrt(fmaxf(0.000025f, cdiv(det0, det)));
+            }
+            const float det_inv = __frcp_rn(det);
+            const float conA = cmul(c, det_inv), conB = cmul(-b, det_inv), conC = cmul(a, det_inv);
+            const float mid = cmul(0.5f, cadd(a, c));
+            const float sq = csqrt(fmaxf(0.1f, cfma(mid, mid, -det)));
+            const float lam = fmaxf(cadd(mid, sq), csub(mid, sq));
+            const int rad = (int)ceilf(cmul(3.0f, csqrt(lam)));
+            // ndc -> pixel in double (exact), rounded once
+            const float px = (float)__dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn((double)ndcx, 1.0), (double)p.W), -1.0), 0.5);
+            const float py = (float)__dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn((double)ndcy, 1.0), (double)p.H), -1.0), 0.5);
+            int minx, miny, maxx, maxy;
+            get_rect(px, py, rad, p.gx, p.gy, minx, miny, maxx, maxy);
+            const int ar = (maxx - minx) * (maxy - miny);
+            if (ar != 0) {
+                float rgb[3];
+                if (p.colors_precomp) {
+                    rgb[0] = __ldg(p.colors_precomp + 3 * i); rgb[1] = __ldg(p.colors_precomp + 3 * i + 1);
+                    rgb[2] = __ldg(p.colors_precomp + 3 * i + 2);
+                } else {
+                    unsigned cl;
+                    eval_color_sh(p.shs + (size_t)i * p.M * 3, p.M, p.D, csub(x, vc.campos[0]), csub(y, vc.campos[1]),
+                                  csub(z, vc.campos[2]), rgb, cl);
+                }
+                const float o = cmul(__ldg(p.opacities + i), hconv);
+                // conservative early-out data for the render kernels (not part of the canonical result):
+                //   thr: power below which o*exp(power) is certainly < 1/255
+                //   ex, ey: half extents of the axis-aligned box of {power >= thr}
+                float thr, ex, ey;
+                if (o > 0.0f) {
+                    thr = -logf(255.0f * o) - THR_MARGIN;
+                    const float tau2 = -2.0f * thr;
+                    if (tau2 > 0.0f) {
+                        ex = sqrtf(tau2 * a) * 1.001f + 0.01f;
+                        ey = sqrtf(tau2 * c) * 1.001f + 0.01f;
+                    } else { ex = -1.0f; ey = -1.0f; }
+                } else { thr = __int_as_float(0x7f800000); ex = -1.0f; ey = -1.0f; }
+                depths[i] = tz;
+                rec[3 * (size_t)i + 0] = make_float4(px, py, ex, ey);
+                rec[3 * (size_t)i + 1] = make_float4(cmul(-0.5f, conA), conB, cmul(-0.5f, conC), thr);
+                rec[3 * (size_t)i + 2] = make_float4(o, rgb[0], rgb[1], rgb[2]);
+                radius = rad;
+                area = (uint32_t)ar;
+            }
+        }
+    }
+    radii[i] = radius;
+    tiles[i] = area;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-Gaussian backward.  fp32 with plain operators (gradient tolerance is 1e-3 relative).
+// ------------------------------------------------------------------------------------------------
+struct BwdParams {
+    PreParams p;
+    const int32_t* radii;
+    const float* acc;    // [P,12] packed render-backward sums
+    b200splat_grads out;
+};
+
+__device__ __forceinline__ void store3(float* base, size_t i, float a, float b, float c) {
+    base[3 * i] = a; base[3 * i + 1] = b; base[3 * i + 2] = c;
+}
+
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp) {
+    __shared__ ViewConsts vc;
+    const PreParams& p = bp.p;
+    load_view_consts(vc, p.view, p.proj, p.campos);
+    const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
+    if (i >= p.P) return;
+    const b200splat_grads& o = bp.out;
+    const bool visible = bp.radii[i] > 0;
+    const int M3 = 3 * p.M;
+
+    float dmean[3] = {0.f, 0.f, 0.f};
+    float dsc[3] = {0.f, 0.f, 0.f}, drot[4] = {0.f, 0.f, 0.f, 0.f}, dc6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float dop = 0.f, dcol[3] = {0.f, 0.f, 0.f}, dndc[2] = {0.f, 0.f};
+
+    if (visible) {
+        const float4 a0 = __ldg(reinterpret_cast<const float4*>(bp.acc) + 3 * (size_t)i);
+        const float4 a1 = __ldg(reinterpret_cast<const float4*>(bp.acc) + 3 * (size_t)i + 1);
+        const float4 a2 = __ldg(reinterpret_cast<const float4*>(bp.acc) + 3 * (size_t)i + 2);
+        const float LA = a0.z, LB = a0.w, LC = a1.x;
+        float dLo = a1.y;
+        dcol[0] = a1.z; dcol[1] = a1.w; dcol[2] = a2.x;
+        dndc[0] = a0.x * (0.5f * p.W); dndc[1] = a0.y * (0.5f * p.H);
+
+        const float x = __ldg(p.means3D + 3 * i), y = __ldg(p.means3D + 3 * i + 1), z = __ldg(p.means3D + 3 * i + 2);
+        const float tx = cadd(cfma(vc.view[8], z, cfma(vc.view[4], y, cmul(vc.view[0], x))), vc.view[12]);
+        const float ty = cadd(cfma(vc.view[9], z, cfma(vc.view[5], y, cmul(vc.view[1], x))), vc.view[13]);
+        const float tz = cadd(cfma(vc.view[10], z, cfma(vc.view[6], y, cmul(vc.view[2], x))), vc.view[14]);
+
+        float c6[6];
+        float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+        float s3[3] = {0.f, 0.f, 0.f};
+        if (p.cov3D_precomp) {
+#pragma unroll
+            for (int k = 0; k < 6; k++) c6[k] = __ldg(p.cov3D_precomp + 6 * (size_t)i + k);
+        } else {
+            q = __ldg(reinterpret_cast<const float4*>(p.rotations) + i);
+            s3[0] = __ldg(p.scales + 3 * i); s3[1] = __ldg(p.scales + 3 * i + 1); s3[2] = __ldg(p.scales + 3 * i + 2);
+            cov3d_from_scale_rot(s3[0], s3[1], s3[2], p.mod, q, c6);
+        }
+        const float limx = cmul(1.3f, p.tanfovx), limy = cmul(1.3f, p.tanfovy);
+        Proj2D pj;
+        project_cov(vc, tx, ty, tz, c6, p.focal_x, p.focal_y, limx, limy, pj);
+        const float xmul = (pj.txtz < -limx || pj.txtz > limx) ? 0.f : 1.f;
+        const float ymul = (pj.tytz < -limy || pj.tytz > limy) ? 0.f : 1.f;
+        const float a = pj.cov00 + 0.3f, b = pj.cov01, c = pj.cov11 + 0.3f;
+        const float det = a * c - b * b;
+        const float d2inv = 1.0f / (det * det + 0.0000001f);
+        float dL_da = d2inv * (-c * c * LA + b * c * LB + (det - a * c) * LC);
+        float dL_dc = d2inv * (-a * a * LC + a * b * LB + (det - a * c) * LA);
+        float dL_db = d2inv * (2.f * b * c * LA - (det + 2.f * b * b) * LB + 2.f * a * b * LC);
+        if (p.antialiasing) {
+            const float det0 = pj.cov00 * pj.cov11 - pj.cov01 * pj.cov01;
+            const float ratio = det0 / det;
+            const float h = sqrtf(fmaxf(0.000025f, ratio));
+            const float dL_dh = __ldg(p.opacities + i) * dLo;
+            dLo = h * dLo;
+            if (ratio > 0.000025f) {
+                const float dL_dratio = dL_dh * 0.5f / h;
+                const float inv2 = 1.0f / (det * det);
+                dL_da += dL_dratio * (pj.cov11 * det - det0 * c) * inv2;
+                dL_dc += dL_dratio * (pj.cov00 * det - det0 * a) * inv2;
+                dL_db += dL_dratio * (-2.f * pj.cov01 * det + det0 * 2.f * pj.cov01) * inv2;
+            }
+        }
+        dop = dLo;
+
+        const float* M0 = pj.M0; const float* M1 = pj.M1;
+        dc6[0] = M0[0] * M0[0] * dL_da + M0[0] * M1[0] * dL_db + M1[0] * M1[0] * dL_dc;
+        dc6[3] = M0[1] * M0[1] * dL_da + M0[1] * M1[1] * dL_db + M1[1] * M1[1] * dL_dc;
+        dc6[5] = M0[2] * M0[2] * dL_da + M0[2] * M1[2] * dL_db + M1[2] * M1[2] * dL_dc;
+        dc6[1] = 2.f * M0[0] * M0[1] * dL_da + (M0[0] * M1[1] + M0[1] * M1[0]) * dL_db + 2.f * M1[0] * M1[1] * dL_dc;
+        dc6[2] = 2.f * M0[0] * M0[2] * dL_da + (M0[0] * M1[2] + M0[2] * M1[0]) * dL_db + 2.f * M1[0] * M1[2] * dL_dc;
+        dc6[4] = 2.f * M0[1] * M0[2] * dL_da + (M0[1] * M1[2] + M0[2] * M1[1]) * dL_db + 2.f * M1[1] * M1[2] * dL_dc;
+
+        // cov2D -> (J Wv) -> J -> view-space point -> mean
+        float dJ00 = 0.f, dJ02 = 0.f, dJ11 = 0.f, dJ12 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const float dM0 = 2.f * dL_da * pj.N0[k] + dL_db * pj.N1[k];
+            const float dM1 = dL_db * pj.N0[k] + 2.f * dL_dc * pj.N1[k];
+            dJ00 += dM0 * vc.view[4 * k + 0]; dJ02 += dM0 * vc.view[4 * k + 2];
+            dJ11 += dM1 * vc.view[4 * k + 1]; dJ12 += dM1 * vc.view[4 * k + 2];
+        }
+        const float itz = 1.0f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
+        const float dtx = xmul * (-p.focal_x * itz2) * dJ02;
+        const float dty = ymul * (-p.focal_y * itz2) * dJ12;
+        float dtz = -p.focal_x * itz2 * dJ00 - p.focal_y * itz2 * dJ11 + (2.f * p.focal_x * pj.txc) * itz3 * dJ02 +
+                    (2.f * p.focal_y * pj.tyc) * itz3 * dJ12;
+        dtz += -a2.y * itz2;   // inverse-depth channel (zero unless a depth gradient was supplied)
+        dmean[0] = vc.view[0] * dtx + vc.view[1] * dty + vc.view[2] * dtz;
+        dmean[1] = vc.view[4] * dtx + vc.view[5] * dty + vc.view[6] * dtz;
+        dmean[2] = vc.view[8] * dtx + vc.view[9] * dty + vc.view[10] * dtz;
+
+        // mean2D (NDC) -> mean3D through the full projection
+        {
+            const float hx = vc.proj[0] * x + vc.proj[4] * y + vc.proj[8] * z + vc.proj[12];
+            const float hy = vc.proj[1] * x + vc.proj[5] * y + vc.proj[9] * z + vc.proj[13];
+            const float hw = vc.proj[3] * x + vc.proj[7] * y + vc.proj[11] * z + vc.proj[15];
+            const float mw = 1.0f / (hw + 0.0000001f);
+            const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
+            dmean[0] += (vc.proj[0] * mw - vc.proj[3] * mul1) * dndc[0] + (vc.proj[1] * mw - vc.proj[3] * mul2) * dndc[1];
+            dmean[1] += (vc.proj[4] * mw - vc.proj[7] * mul1) * dndc[0] + (vc.proj[5] * mw - vc.proj[7] * mul2) * dndc[1];
+            dmean[2] += (vc.proj[8] * mw - vc.proj[11] * mul1) * dndc[0] + (vc.proj[9] * mw - vc.proj[11] * mul2) * dndc[1];
+        }
+
+        // SH: dL/dsh rows and dL/dmean through the normalised view direction
+        if (p.shs) {
+            const float ddx = x - vc.campos[0], ddy = y - vc.campos[1], ddz = z - vc.campos[2];
+            const float len = csqrt(cfma(ddz, ddz, cfma(ddy, ddy, cmul(ddx, ddx))));
+            const float ux = cdiv(ddx, len), uy = cdiv(ddy, len), uz = cdiv(ddz, len);
+            // recompute the clamp mask with the forward's exact arithmetic
+            float rgbf[3]; unsigned cl;
+            const float* sh_row = p.shs + (size_t)i * M3;
+            eval_color_sh(sh_row, p.M, p.D, ddx, ddy, ddz, rgbf, cl);
+            const float g0 = (cl & 1u) ? 0.f : dcol[0], g1 = (cl & 2u) ? 0.f : dcol[1], g2 = (cl & 4u) ? 0.f : dcol[2];
+            float bb[16], bx[16], by[16], bz[16];
+#pragma unroll
+            for (int k = 0; k < 16; k++) { bb[k] = 0.f; bx[k] = 0.f; by[k] = 0.f; bz[k] = 0.f; }
+            bb[0] = 0.28209479177387814f;
+            if (p.D > 0) {
+                const float C1 = 0.4886025119029199f;
+                bb[1] = -C1 * uy; by[1] = -C1;
+                bb[2] = C1 * uz;  bz[2] = C1;
+                bb[3] = -C1 * ux; bx[3] = -C1;
+                if (p.D > 1) {
+                    const float c20 = 1.0925484305920792f, c22 = 0.31539156525252005f, c24 = 0.5462742152960396f;
+                    const float xx = ux * ux, yy = uy * uy, zz = uz * uz;
+                    bb[4] = c20 * ux * uy;  bx[4] = c20 * uy; by[4] = c20 * ux;
+                    bb[5] = -c20 * uy * uz; by[5] = -c20 * uz; bz[5] = -c20 * uy;
+                    bb[6] = c22 * (2.f * zz - xx - yy); bx[6] = -2.f * c22 * ux; by[6] = -2.f * c22 * uy; bz[6] = 4.f * c22 * uz;
+                    bb[7] = -c20 * ux * uz; bx[7] = -c20 * uz; bz[7] = -c20 * ux;
+                    bb[8] = c24 * (xx - yy); bx[8] = 2.f * c24 * ux; by[8] = -2.f * c24 * uy;
+                    if (p.D > 2) {
+                        const float c30 = -0.5900435899266435f, c31 = 2.890611442640554f, c32 = -0.4570457994644658f,
+                                    c33 = 0.3731763325901154f, c35 = 1.445305721320277f;
+                        bb[9] = c30 * uy * (3.f * xx - yy); bx[9] = c30 * uy * 6.f * ux; by[9] = c30 * (3.f * xx - 3.f * yy);
+                        bb[10] = c31 * ux * uy * uz; bx[10] = c31 * uy * uz; by[10] = c31 * ux * uz; bz[10] = c31 * ux * uy;
+                        bb[11] = c32 * uy * (4.f * zz - xx - yy); bx[11] = c32 * uy * -2.f * ux;
+                        by[11] = c32 * (4.f * zz - xx - 3.f * yy); bz[11] = c32 * uy * 8.f * uz;
+                        bb[12] = c33 * uz * (2.f * zz - 3.f * xx - 3.f * yy); bx[12] = c33 * uz * -6.f * ux;
+                        by[12] = c33 * uz * -6.f * uy; bz[12] = c33 * (6.f * zz - 3.f * xx - 3.f * yy);
+                        bb[13] = c32 * ux * (4.f * zz - xx - yy); bx[13] = c32 * (4.f * zz - 3.f * xx - yy);
+                        by[13] = c32 * ux * -2.f * uy; bz[13] = c32 * ux * 8.f * uz;
+                        bb[14] = c35 * uz * (xx - yy); bx[14] = c35 * uz * 2.f * ux; by[14] = c35 * uz * -2.f * uy;
+                        bz[14] = c35 * (xx - yy);
+                        bb[15] = c30 * ux * (xx - 3.f * yy); bx[15] = c30 * (3.f * xx - 3.f * yy); by[15] = c30 * ux * -6.f * uy;
+                    }
+                }
+            }
+            const int nb = (p.D + 1) * (p.D + 1);
+            float dRx = 0.f, dRy = 0.f, dRz = 0.f;
+            float* dsh_row = o.dL_dsh + (size_t)i * M3;
+            if ((p.M & 3) == 0 && p.M <= 16) {
+                const float4* v = reinterpret_cast<const float4*>(sh_row);
+                float4* w = reinterpret_cast<float4*>(dsh_row);
+                const int nvec = M3 >> 2;
+#pragma unroll
+                for (int kv = 0; kv < 12; kv++) {
+                    if (kv < nvec) {
+                        const float4 t = __ldg(v + kv);
+                        const float f[4] = {t.x, t.y, t.z, t.w};
+                        float out[4];
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const int idx = 4 * kv + e, k = idx / 3, ch = idx - 3 * k;
+                            const float gch = ch == 0 ? g0 : (ch == 1 ? g1 : g2);
+                            const bool act = k < nb;
+                            out[e] = act ? bb[k] * gch : 0.f;
+                            if (act) { const float sg = f[e] * gch; dRx += bx[k] * sg; dRy += by[k] * sg; dRz += bz[k] * sg; }
+                        }
+                        w[kv] = make_float4(out[0], out[1], out[2], out[3]);
+                    }
+                }
+            } else {
+                for (int k = 0; k < p.M; k++) {
+                    const bool act = k < nb;
+                    const float bk = act ? bb[k < 16 ? k : 15] : 0.f;
+                    for (int ch = 0; ch < 3; ch++) {
+                        const float gch = ch == 0 ? g0 : (ch == 1 ? g1 : g2);
+                        dsh_row[3 * k + ch] = bk * gch;
+                        if (act) {
+                            const float sg = __ldg(sh_row + 3 * k + ch) * gch;
+                            dRx += bx[k] * sg; dRy += by[k] * sg; dRz += bz[k] * sg;
+                        }
+                    }
+                }
+            }
+            const float dotp = ux * dRx + uy * dRy + uz * dRz;
+            const float il = 1.0f / len;
+            dmean[0] += (dRx - ux * dotp) * il;
+            dmean[1] += (dRy - uy * dotp) * il;
+            dmean[2] += (dRz - uz * dotp) * il;
+        }
+
+        // cov3D -> scale, rotation
+        if (!p.cov3D_precomp) {
+            const float r = q.x, qx = q.y, qy = q.z, qz = q.w;
+            const float R[3][3] = {
+                {1.f - 2.f * (qy * qy + qz * qz), 2.f * (qx * qy - r * qz), 2.f * (qx * qz + r * qy)},
+                {2.f * (qx * qy + r * qz), 1.f - 2.f * (qx * qx + qz * qz), 2.f * (qy * qz - r * qx)},
+                {2.f * (qx * qz - r * qy), 2.f * (qy * qz + r * qx), 1.f - 2.f * (qx * qx + qy * qy)}};
+            const float s[3] = {p.mod * s3[0], p.mod * s3[1], p.mod * s3[2]};
+            const float G3[3][3] = {{dc6[0], 0.5f * dc6[1], 0.5f * dc6[2]},
+                                    {0.5f * dc6[1], dc6[3], 0.5f * dc6[4]},
+                                    {0.5f * dc6[2], 0.5f * dc6[4], dc6[5]}};
+            float g[3][3];
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                float ds = 0.f;
+#pragma unroll
+                for (int a2i = 0; a2i < 3; a2i++) {
+                    float vsum = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 3; k++) vsum += G3[a2i][k] * (R[k][j] * s[j]);
+                    const float dLm = 2.f * vsum;
+                    ds += R[a2i][j] * dLm;
+                    g[a2i][j] = dLm * s[j];
+                }
+                dsc[j] = p.mod * ds;
+            }
+            drot[0] = 2.f * (-qz * g[0][1] + qy * g[0][2] + qz * g[1][0] - qx * g[1][2] - qy * g[2][0] + qx * g[2][1]);
+            drot[1] = 2.f * (qy * g[0][1] + qz * g[0][2] + qy * g[1][0] - 2.f * qx * g[1][1] - r * g[1][2] + qz * g[2][0] +
+                             r * g[2][1] - 2.f * qx * g[2][2]);
+            drot[2] = 2.f * (-2.f * qy * g[0][0] + qx * g[0][1] + r * g[0][2] + qx * g[1][0] + qz * g[1][2] - r * g[2][0] +
+                             qz * g[2][1] - 2.f * qy * g[2][2]);
+            drot[3] = 2.f * (-2.f * qz * g[0][0] - r * g[0][1] + qx * g[0][2] + r * g[1][0] - 2.f * qz * g[1][1] +
+                             qy * g[1][2] + qx * g[2][0] + qy * g[2][1]);
+        }
+    } else if (p.shs && o.dL_dsh) {
+        float* dsh_row = o.dL_dsh + (size_t)i * M3;
+        if ((M3 & 3) == 0) {
+            float4* w = reinterpret_cast<float4*>(dsh_row);
+            for (int k = 0; k < (M3 >> 2); k++) w[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+            for (int k = 0; k < M3; k++) dsh_row[k] = 0.f;
+        }
+    }
+
+    store3(o.dL_dmeans3D, i, dmean[0], dmean[1], dmean[2]);
+    if (o.dL_dmeans2D) store3(o.dL_dmeans2D, i, dndc[0], dndc[1], 0.f);
+    if (o.dL_dcolors) store3(o.dL_dcolors, i, dcol[0], dcol[1], dcol[2]);
+    if (o.dL_dopacity) o.dL_dopacity[i] = dop;
+    if (o.dL_dscales) store3(o.dL_dscales, i, dsc[0], dsc[1], dsc[2]);
+    if (o.dL_drotations) reinterpret_cast<float4*>(o.dL_drotations)[i] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+    if (o.dL_dcov3D) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) o.dL_dcov3D[6 * (size_t)i + k] = dc6[k];
+    }
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
+                                    uint8_t* __restrict__ present) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const float x = means3D[3 * i], y = means3D[3 * i + 1], z = means3D[3 * i + 2];
+    const float tz = cadd(cfma(view[10], z, cfma(view[6], y, cmul(view[2], x))), view[14]);
+    present[i] = tz > NEAR_Z ? 1 : 0;
+}
+
+__global__ void export_geom_kernel(int P, const int32_t* __restrict__ radii, GeomView gv, b200splat_state_out o) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const bool vis = radii[i] > 0;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a, c = a;
+    float d = 0.f;
+    if (vis) { a = gv.rec[3 * (size_t)i]; b = gv.rec[3 * (size_t)i + 1]; c = gv.rec[3 * (size_t)i + 2]; d = gv.depths[i]; }
+    if (o.means2D) { o.means2D[2 * i] = a.x; o.means2D[2 * i + 1] = a.y; }
+    if (o.depths) o.depths[i] = d;
+    if (o.conic_opacity) {
+        o.conic_opacity[4 * i] = -2.0f * b.x; o.conic_opacity[4 * i + 1] = b.y;
+        o.conic_opacity[4 * i + 2] = -2.0f * b.z; o.conic_opacity[4 * i + 3] = c.x;
+    }
+    if (o.rgb) { o.rgb[3 * i] = c.y; o.rgb[3 * i + 1] = c.z; o.rgb[3 * i + 2] = c.w; }
+    if (o.tiles_touched) o.tiles_touched[i] = gv.tiles[i];
+    if (o.point_offsets) o.point_offsets[i] = gv.offsets[i];
+}
+
+PreParams make_params(const b200splat_view& v, const b200splat_gaussians& g) {
+    PreParams p;
+    p.P = g.P; p.D = v.sh_degree; p.M = g.M; p.W = v.image_width; p.H = v.image_height;
+    p.gx = (p.W + TILE - 1) / TILE; p.gy = (p.H + TILE - 1) / TILE;
+    p.tanfovx = v.tanfovx; p.tanfovy = v.tanfovy;
+    p.focal_x = (float)p.W / (2.0f * v.tanfovx);
+    p.focal_y = (float)p.H / (2.0f * v.tanfovy);
+    p.mod = v.scale_modifier; p.antialiasing = v.antialiasing;
+    p.means3D = g.means3D; p.scales = g.scales; p.rotations = g.rotations; p.opacities = g.opacities;
+    p.shs = g.shs; p.colors_precomp = g.colors_precomp; p.cov3D_precomp = g.cov3D_precomp;
+    p.view = v.viewmatrix; p.proj = v.projmatrix; p.campos = v.campos;
+    return p;
+}
+
+}  // namespace
+
+cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gaussians& g, GeomView gv,
+                                  int32_t* radii, cudaStream_t s) {
+    if (g.P == 0) return cudaSuccess;
+    PreParams p = make_params(v, g);
+    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(p, gv.depths, gv.rec, gv.tiles, radii);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
+                                  GeomView gv, const float* acc, const b200splat_grads& out, cudaStream_t s) {
+    (void)gv;
+    if (g.P == 0) return cudaSuccess;
+    BwdParams bp;
+    bp.p = make_params(v, g);
+    bp.radii = radii; bp.acc = acc; bp.out = out;
+    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(bp);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_export_geom(int P, const int32_t* radii, GeomView gv, const b200splat_state_out& o, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    export_geom_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, gv, o);
+    return cudaGetLastError();
+}
+
+}  // namespace b200splat

@@ -1,0 +1,167 @@
+// splat_internal.cuh -- shared declarations of libb200splat (sm_100a).  Not part of the C ABI.
+//
+// State layout in HBM (all chunks 256-byte aligned inside the caller-allocated opaque buffers):
+//
+//   geometry buffer (per Gaussian, P entries)
+//     depths   f32[P]        view-space z (sort key low word)
+//     rec      float4[3P]    packed 48-byte splat record, gathered by the render kernels:
+//                              rec[3i+0] = (px, py, ex, ey)   pixel centre, half extents of {alpha >= 1/255}
+//                              rec[3i+1] = (hA, B, hC, thr)   hA = -A/2, hC = -C/2 (exact), power threshold
+//                              rec[3i+2] = (o, r, g, b)       effective opacity, colour
+//     tiles    u32[P]        tiles touched
+//     offsets  u32[P]        inclusive scan of tiles
+//     scan_tmp               CUB scan scratch
+//   binning buffer (per (tile, Gaussian) pair, R entries)
+//     keys_unsorted u64[R], keys_sorted u64[R], vals_unsorted u32[R], vals_sorted u32[R], sort_tmp
+//   image buffer
+//     ranges   int2[T]       [start, end) of each tile in the sorted list
+//     final_T  f32[H*W], n_contrib u32[H*W], counters u32[64] (persistent-kernel work counters)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "../../include/b200splat.h"
+
+namespace b200splat {
+
+constexpr int TILE = 16;
+constexpr float NEAR_Z = 0.2f;
+constexpr float ALPHA_MIN = 1.0f / 255.0f;
+constexpr float ALPHA_MAX = 0.99f;
+constexpr float T_EPS = 0.0001f;
+// power-threshold safety margin (natural-log units): a pair is skipped before the exp only when
+// o*exp(power) < (1/255)*exp(-THR_MARGIN), far outside any fp32 rounding of the exact test.
+constexpr float THR_MARGIN = 1.0e-3f;
+
+inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+struct GeomView {
+    float* depths; float4* rec; uint32_t* tiles; uint32_t* offsets; void* scan_tmp;
+    size_t scan_tmp_bytes; size_t total;
+};
+struct BinView {
+    uint64_t* keys_unsorted; uint64_t* keys_sorted; uint32_t* vals_unsorted; uint32_t* vals_sorted;
+    void* sort_tmp; size_t sort_tmp_bytes; size_t total;
+};
+struct ImgView {
+    int2* ranges; float* final_T; uint32_t* n_contrib; unsigned int* counters; size_t total;
+};
+
+size_t scan_temp_bytes(int P);
+size_t sort_temp_bytes(int R, int end_bit);
+GeomView carve_geom(void* base, int P);
+BinView carve_binning(void* base, int R, int end_bit);
+ImgView carve_image(void* base, int W, int H);
+int sort_end_bit(int W, int H);
+
+// ---- stage launchers (each enqueues on `s`, returns the launch status) ---------------------------
+cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gaussians& g, GeomView gv,
+                                  int32_t* radii, cudaStream_t s);
+cudaError_t launch_scan(GeomView gv, int P, cudaStream_t s);
+cudaError_t launch_duplicate(GeomView gv, const int32_t* radii, int P, int W, int H, BinView bv, cudaStream_t s);
+cudaError_t launch_sort(BinView bv, int R, int end_bit, cudaStream_t s);
+cudaError_t launch_ranges(BinView bv, int R, ImgView iv, int W, int H, cudaStream_t s);
+cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, ImgView iv, float* out_color,
+                              float* out_invdepth, cudaStream_t s);
+// packed per-Gaussian gradient accumulator written by the render backward, 12 floats / Gaussian:
+//   (d_ndc_x, d_ndc_y are produced later)   acc[12i+0..] = (dpx, dpy, dA, dB, dC, do, dr, dg, db, dinvd, -, -)
+cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
+                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s);
+cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
+                                  GeomView gv, const float* acc, const b200splat_grads& out, cudaStream_t s);
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
+cudaError_t launch_export_geom(int P, const int32_t* radii, GeomView gv, const b200splat_state_out& o, cudaStream_t s);
+
+// ---- canonical fp32 arithmetic (DESIGN.md "Canonical arithmetic") --------------------------------
+// Every rounding point is an explicit intrinsic, so the compiler can neither contract nor
+// reassociate; oracle/splat_oracle.c implements the same sequence with fmaf and -ffp-contract=off.
+#ifdef __CUDACC__
+__device__ __forceinline__ float cmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float cadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float csub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float cfma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float cdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float csqrt(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ float cdot3(float a0, float b0, float a1, float b1, float a2, float b2) {
+    return cfma(a2, b2, cfma(a1, b1, cmul(a0, b0)));
+}
+
+struct ViewConsts {   // staged in shared memory once per block
+    float view[16];
+    float proj[16];
+    float campos[3];
+};
+
+__device__ __forceinline__ void load_view_consts(ViewConsts& vc, const float* view, const float* proj,
+                                                 const float* campos) {
+    int t = threadIdx.x;
+    if (t < 16) vc.view[t] = view[t];
+    else if (t < 32) vc.proj[t - 16] = proj[t - 16];
+    else if (t < 35 && campos) vc.campos[t - 32] = campos[t - 32];
+    __syncthreads();
+}
+
+// tile rectangle of a splat: truncation toward zero (saturating), then clamp to the grid
+__device__ __forceinline__ void get_rect(float px, float py, int radius, int gx, int gy, int& minx, int& miny,
+                                         int& maxx, int& maxy) {
+    float fr = (float)radius;
+    minx = min(gx, max(0, (int)cmul(csub(px, fr), 0.0625f)));
+    miny = min(gy, max(0, (int)cmul(csub(py, fr), 0.0625f)));
+    maxx = min(gx, max(0, (int)cmul(csub(cadd(cadd(px, fr), 16.0f), 1.0f), 0.0625f)));
+    maxy = min(gy, max(0, (int)cmul(csub(cadd(cadd(py, fr), 16.0f), 1.0f), 0.0625f)));
+}
+
+// 3D covariance (xx,xy,xz,yy,yz,zz) from scale * modifier and a unit quaternion (w,x,y,z)
+__device__ __forceinline__ void cov3d_from_scale_rot(float s0, float s1, float s2, float mod, float4 q, float* c6) {
+    float r = q.x, x = q.y, y = q.z, z = q.w;
+    float R00 = cfma(-2.0f, cfma(y, y, cmul(z, z)), 1.0f);
+    float R01 = cmul(2.0f, cfma(x, y, -cmul(r, z)));
+    float R02 = cmul(2.0f, cfma(x, z, cmul(r, y)));
+    float R10 = cmul(2.0f, cfma(x, y, cmul(r, z)));
+    float R11 = cfma(-2.0f, cfma(x, x, cmul(z, z)), 1.0f);
+    float R12 = cmul(2.0f, cfma(y, z, -cmul(r, x)));
+    float R20 = cmul(2.0f, cfma(x, z, -cmul(r, y)));
+    float R21 = cmul(2.0f, cfma(y, z, cmul(r, x)));
+    float R22 = cfma(-2.0f, cfma(x, x, cmul(y, y)), 1.0f);
+    float sx = cmul(mod, s0), sy = cmul(mod, s1), sz = cmul(mod, s2);
+    float L00 = cmul(R00, sx), L01 = cmul(R01, sy), L02 = cmul(R02, sz);
+    float L10 = cmul(R10, sx), L11 = cmul(R11, sy), L12 = cmul(R12, sz);
+    float L20 = cmul(R20, sx), L21 = cmul(R21, sy), L22 = cmul(R22, sz);
+    c6[0] = cdot3(L00, L00, L01, L01, L02, L02);
+    c6[1] = cdot3(L00, L10, L01, L11, L02, L12);
+    c6[2] = cdot3(L00, L20, L01, L21, L02, L22);
+    c6[3] = cdot3(L10, L10, L11, L11, L12, L12);
+    c6[4] = cdot3(L10, L20, L11, L21, L12, L22);
+    c6[5] = cdot3(L20, L20, L21, L21, L22, L22);
+}
+
+// SH basis at a unit direction; polynomial forms of /root/reference/utils/sh_utils.py:74-100
+__device__ __forceinline__ void sh_basis(int D, float x, float y, float z, float* b) {
+    b[0] = 0.28209479177387814f;
+    if (D > 0) {
+        const float C1 = 0.4886025119029199f;
+        b[1] = -cmul(C1, y); b[2] = cmul(C1, z); b[3] = -cmul(C1, x);
+        if (D > 1) {
+            float xx = cmul(x, x), yy = cmul(y, y), zz = cmul(z, z);
+            float xy = cmul(x, y), yz = cmul(y, z), xz = cmul(x, z);
+            b[4] = cmul(1.0925484305920792f, xy);
+            b[5] = cmul(-1.0925484305920792f, yz);
+            b[6] = cmul(0.31539156525252005f, csub(csub(cmul(2.0f, zz), xx), yy));
+            b[7] = cmul(-1.0925484305920792f, xz);
+            b[8] = cmul(0.5462742152960396f, csub(xx, yy));
+            if (D > 2) {
+                b[9]  = cmul(cmul(-0.5900435899266435f, y), cfma(3.0f, xx, -yy));
+                b[10] = cmul(cmul(2.890611442640554f, xy), z);
+                b[11] = cmul(cmul(-0.4570457994644658f, y), csub(csub(cmul(4.0f, zz), xx), yy));
+                b[12] = cmul(cmul(0.3731763325901154f, z), csub(csub(cmul(2.0f, zz), cmul(3.0f, xx)), cmul(3.0f, yy)));
+                b[13] = cmul(cmul(-0.4570457994644658f, x), csub(csub(cmul(4.0f, zz), xx), yy));
+                b[14] = cmul(cmul(1.445305721320277f, z), csub(xx, yy));
+                b[15] = cmul(cmul(-0.5900435899266435f, x), cfma(-3.0f, yy, xx));
+            }
+        }
+    }
+}
+#endif  // __CUDACC__
+
+}  // namespace b200splat

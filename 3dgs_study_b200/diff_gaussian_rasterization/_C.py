@@ -1,0 +1,307 @@
+"""`_C` of the drop-in `diff_gaussian_rasterization` package: a thin ctypes binding over the C ABI of
+libb200splat.so (include/b200splat.h).
+
+It exposes the native surface BASELINE.json's north_star names -- `rasterize_gaussians`,
+`rasterize_gaussians_backward` (+ `mark_visible`) -- with the positional argument order of the pybind
+module it replaces (the submodule pinned at /root/reference/.gitmodules:4-6, absent from the
+snapshot; call site /root/reference/gaussian_renderer/__init__.py:98-106).  PyTorch is used for
+device memory and the current CUDA stream only; every kernel lives in libb200splat.so.
+
+There is NO fallback: if the library is missing or the tensors are not CUDA tensors this raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional, Tuple
+
+import torch
+
+_PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(_PKG_DIR, "libb200splat.so")
+
+_alloc_fn_t = ctypes.CFUNCTYPE(ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
+
+
+class _View(ctypes.Structure):
+    _fields_ = [
+        ("image_height", ctypes.c_int32), ("image_width", ctypes.c_int32),
+        ("tanfovx", ctypes.c_float), ("tanfovy", ctypes.c_float), ("scale_modifier", ctypes.c_float),
+        ("sh_degree", ctypes.c_int32), ("prefiltered", ctypes.c_int32), ("debug", ctypes.c_int32),
+        ("antialiasing", ctypes.c_int32),
+        ("bg", ctypes.c_void_p), ("viewmatrix", ctypes.c_void_p), ("projmatrix", ctypes.c_void_p),
+        ("campos", ctypes.c_void_p),
+    ]
+
+
+class _Gaussians(ctypes.Structure):
+    _fields_ = [
+        ("P", ctypes.c_int32), ("M", ctypes.c_int32),
+        ("means3D", ctypes.c_void_p), ("shs", ctypes.c_void_p), ("colors_precomp", ctypes.c_void_p),
+        ("opacities", ctypes.c_void_p), ("scales", ctypes.c_void_p), ("rotations", ctypes.c_void_p),
+        ("cov3D_precomp", ctypes.c_void_p),
+    ]
+
+
+class _ForwardOut(ctypes.Structure):
+    _fields_ = [("color", ctypes.c_void_p), ("radii", ctypes.c_void_p), ("invdepth", ctypes.c_void_p)]
+
+
+class _Allocators(ctypes.Structure):
+    _fields_ = [("alloc", _alloc_fn_t), ("geom_ctx", ctypes.c_void_p), ("binning_ctx", ctypes.c_void_p),
+                ("image_ctx", ctypes.c_void_p)]
+
+
+class StageTimes(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_float) for n in (
+        "preprocess_ms", "scan_ms", "duplicate_ms", "sort_ms", "ranges_ms", "render_ms",
+        "render_bwd_ms", "preprocess_bwd_ms")]
+
+    def as_dict(self):
+        return {n: float(getattr(self, n)) for n, _ in self._fields_}
+
+
+class _Grads(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_void_p) for n in (
+        "dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
+        "dL_drotations")]
+
+
+class _StateOut(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_void_p) for n in (
+        "means2D", "depths", "conic_opacity", "rgb", "tiles_touched", "point_offsets", "keys_sorted",
+        "vals_sorted", "ranges", "final_T", "n_contrib")]
+
+
+_lib = None
+
+
+def lib():
+    """Load libb200splat.so (once).  Raises if it has not been built: there is no CPU fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(or `make -C 3dgs_study_b200/csrc`). This package has no CPU or PyTorch fallback.")
+        L = ctypes.CDLL(LIB_PATH)
+        L.b200splat_last_error.restype = ctypes.c_char_p
+        L.b200splat_version.restype = ctypes.c_int
+        for f in ("b200splat_geom_bytes", "b200splat_image_bytes", "b200splat_binning_bytes"):
+            getattr(L, f).restype = ctypes.c_size_t
+        L.b200splat_forward.restype = ctypes.c_int
+        L.b200splat_forward.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                        ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_backward.restype = ctypes.c_int
+        L.b200splat_backward.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                         ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p,
+                                         ctypes.c_void_p, ctypes.c_void_p, _alloc_fn_t, ctypes.c_void_p,
+                                         ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_mark_visible.restype = ctypes.c_int
+        L.b200splat_mark_visible.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_export_state.restype = ctypes.c_int
+        L.b200splat_export_state.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_void_p, ctypes.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        msg = lib().b200splat_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"b200splat {what} failed (status {rc}): {msg}")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t: Optional[torch.Tensor], name: str, device) -> Optional[torch.Tensor]:
+    """Empty / None -> None; otherwise a contiguous fp32 CUDA tensor on `device`."""
+    if t is None or t.numel() == 0:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (this rasterizer has no CPU path)")
+    if t.device != device:
+        raise RuntimeError(f"{name} is on {t.device}, expected {device}")
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+class _TensorAllocator:
+    """Serves the library's allocator callbacks from torch's caching allocator, keeping the byte
+    tensors alive so autograd can save them for the backward pass."""
+
+    def __init__(self, device):
+        self.device = device
+        self.buffers = {}
+        self.error = None
+
+        def _cb(ctx, nbytes):
+            try:
+                t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
+                self.buffers[int(ctx) if ctx else 0] = t
+                return t.data_ptr()
+            except Exception as e:  # surfaced after the C call returns B200SPLAT_ERR_ALLOC
+                self.error = e
+                return None
+
+        self.cb = _alloc_fn_t(_cb)
+
+
+def _stream_ptr(device) -> int:
+    return int(torch.cuda.current_stream(device).cuda_stream)
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug, antialiasing=False, want_invdepth=False, stage_times: StageTimes = None):
+    """-> (num_rendered, out_color [3,H,W], radii [P] i32, geomBuffer, binningBuffer, imgBuffer, invdepth|None)"""
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    dev = means3D.device
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    P = means3D.shape[0]
+    H, W = int(image_height), int(image_width)
+    means3D = _f32c(means3D, "means3D", dev)
+    colors = _f32c(colors, "colors_precomp", dev)
+    opacity = _f32c(opacity, "opacities", dev)
+    scales = _f32c(scales, "scales", dev)
+    rotations = _f32c(rotations, "rotations", dev)
+    cov3D_precomp = _f32c(cov3D_precomp, "cov3D_precomp", dev)
+    sh = _f32c(sh, "shs", dev)
+    background = _f32c(background, "bg", dev)
+    viewmatrix = _f32c(viewmatrix, "viewmatrix", dev)
+    projmatrix = _f32c(projmatrix, "projmatrix", dev)
+    campos = _f32c(campos, "campos", dev)
+    M = int(sh.shape[1]) if sh is not None else 0
+
+    out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
+
+    view = _View(H, W, float(tan_fovx), float(tan_fovy), float(scale_modifier), int(degree), int(bool(prefiltered)),
+                 int(bool(debug)), int(bool(antialiasing)), _ptr(background), _ptr(viewmatrix), _ptr(projmatrix),
+                 _ptr(campos))
+    g = _Gaussians(P, M, _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacity), _ptr(scales), _ptr(rotations),
+                   _ptr(cov3D_precomp))
+    out = _ForwardOut(_ptr(out_color), _ptr(radii), _ptr(invdepth))
+    ta = _TensorAllocator(dev)
+    allocs = _Allocators(ta.cb, 1, 2, 3)
+    num_rendered = ctypes.c_int32(0)
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_forward(ctypes.addressof(view), ctypes.addressof(g), ctypes.addressof(out),
+                                     ctypes.addressof(allocs), ctypes.addressof(num_rendered),
+                                     ctypes.addressof(stage_times) if stage_times is not None else None,
+                                     _stream_ptr(dev))
+    if ta.error is not None:
+        raise ta.error
+    _check(rc, "forward")
+    empty = torch.empty(0, dtype=torch.uint8, device=dev)
+    return (int(num_rendered.value), out_color, radii, ta.buffers.get(1, empty), ta.buffers.get(2, empty),
+            ta.buffers.get(3, empty), invdepth)
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug, opacities=None, antialiasing=False,
+                                 image_height=None, image_width=None, stage_times: StageTimes = None):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)"""
+    dev = means3D.device
+    P = means3D.shape[0]
+    dL_dout_color = _f32c(dL_dout_color, "dL_dout_color", dev)
+    H = int(image_height) if image_height is not None else int(dL_dout_color.shape[1])
+    W = int(image_width) if image_width is not None else int(dL_dout_color.shape[2])
+    means3D = _f32c(means3D, "means3D", dev)
+    colors = _f32c(colors, "colors_precomp", dev)
+    scales = _f32c(scales, "scales", dev)
+    rotations = _f32c(rotations, "rotations", dev)
+    cov3D_precomp = _f32c(cov3D_precomp, "cov3D_precomp", dev)
+    sh = _f32c(sh, "shs", dev)
+    opacities = _f32c(opacities, "opacities", dev)
+    if opacities is None:
+        raise RuntimeError("opacities are required by the backward pass")
+    background = _f32c(background, "bg", dev)
+    viewmatrix = _f32c(viewmatrix, "viewmatrix", dev)
+    projmatrix = _f32c(projmatrix, "projmatrix", dev)
+    campos = _f32c(campos, "campos", dev)
+    M = int(sh.shape[1]) if sh is not None else 0
+
+    def new(*shape):
+        return torch.empty(shape, dtype=torch.float32, device=dev)
+
+    dL_dmeans2D = new(P, 3)
+    dL_dcolors = new(P, 3) if colors is not None else None
+    dL_dopacity = new(P, 1)
+    dL_dmeans3D = new(P, 3)
+    dL_dcov3D = new(P, 6) if cov3D_precomp is not None else None
+    dL_dsh = new(P, M, 3) if sh is not None else None
+    dL_dscales = new(P, 3) if scales is not None else None
+    dL_drotations = new(P, 4) if rotations is not None else None
+
+    view = _View(H, W, float(tan_fovx), float(tan_fovy), float(scale_modifier), int(degree), 0, int(bool(debug)),
+                 int(bool(antialiasing)), _ptr(background), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos))
+    g = _Gaussians(P, M, _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacities), _ptr(scales), _ptr(rotations),
+                   _ptr(cov3D_precomp))
+    grads = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dcolors), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcov3D),
+                   _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drotations))
+    ta = _TensorAllocator(dev)
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_backward(ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer),
+                                      _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(dL_dout_color), None,
+                                      ctypes.addressof(grads), ta.cb, 1,
+                                      ctypes.addressof(stage_times) if stage_times is not None else None,
+                                      _stream_ptr(dev))
+    if ta.error is not None:
+        raise ta.error
+    _check(rc, "backward")
+    # the scratch tensor may be released now: stream-ordered reuse by the caching allocator is safe
+    return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
+    dev = means3D.device
+    P = means3D.shape[0]
+    means3D = _f32c(means3D, "means3D", dev)
+    viewmatrix = _f32c(viewmatrix, "viewmatrix", dev)
+    projmatrix = _f32c(projmatrix, "projmatrix", dev)
+    present = torch.zeros((P,), dtype=torch.bool, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix), _ptr(present),
+                                          _stream_ptr(dev))
+    _check(rc, "mark_visible")
+    return present
+
+
+def export_state(P, W, H, num_rendered, radii, geomBuffer, binningBuffer, imageBuffer):
+    """Parity/inspection helper: unpack the opaque forward state into named tensors."""
+    dev = radii.device
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    R = int(num_rendered)
+    o = {
+        "means2D": torch.zeros((P, 2), dtype=torch.float32, device=dev),
+        "depths": torch.zeros((P,), dtype=torch.float32, device=dev),
+        "conic_opacity": torch.zeros((P, 4), dtype=torch.float32, device=dev),
+        "rgb": torch.zeros((P, 3), dtype=torch.float32, device=dev),
+        "tiles_touched": torch.zeros((P,), dtype=torch.int32, device=dev),
+        "point_offsets": torch.zeros((P,), dtype=torch.int32, device=dev),
+        "keys_sorted": torch.zeros((R,), dtype=torch.int64, device=dev),
+        "vals_sorted": torch.zeros((R,), dtype=torch.int32, device=dev),
+        "ranges": torch.zeros((T, 2), dtype=torch.int32, device=dev),
+        "final_T": torch.zeros((H, W), dtype=torch.float32, device=dev),
+        "n_contrib": torch.zeros((H, W), dtype=torch.int32, device=dev),
+    }
+    so = _StateOut(*[_ptr(o[n]) for n, _ in _StateOut._fields_])
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_export_state(P, W, H, R, _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
+                                          _ptr(imageBuffer), ctypes.addressof(so), _stream_ptr(dev))
+    _check(rc, "export_state")
+    return o

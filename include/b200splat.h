@@ -1,0 +1,186 @@
+/*
+ * b200splat.h -- C ABI of libb200splat.so, the B200 (sm_100a) differentiable Gaussian-splat
+ * rasterizer.  Plain pointers and sizes only: no C++ types, no torch types, no exceptions.
+ *
+ * What each entry point replaces in the reference (PoplarPoplar/3dgs_study):
+ *
+ *   The reference reaches this path through the Python package `diff_gaussian_rasterization`
+ *   (import: /root/reference/gaussian_renderer/__init__.py:14; settings: :47-60; module: :62;
+ *   call: :98-106), whose native half is the pybind module `_C` of the git submodule
+ *   submodules/diff-gaussian-rasterization (pinned @ 2cf59156, /root/reference/.gitmodules:4-6;
+ *   ABSENT from the snapshot, /root/reference/.SUBMODULES.json:16-22).  BASELINE.json's north_star
+ *   names the two native calls this library stands in for:
+ *
+ *     b200splat_forward   <->  _C.rasterize_gaussians            (forward of the call at :98-106)
+ *     b200splat_backward  <->  _C.rasterize_gaussians_backward   (autograd backward of the same call;
+ *                                                                 its means2D gradient is consumed at
+ *                                                                 /root/reference/scene/gaussian_model.py:576-580)
+ *     b200splat_mark_visible <-> _C.mark_visible                 (frustum test; not called by the reference)
+ *
+ *   The binding a maintainer adds on the reference side is in INTEGRATION.md; the one this repo
+ *   ships is 3dgs_study_b200/diff_gaussian_rasterization/_C.py (ctypes).
+ *
+ * Memory: every pointer in b200splat_view / b200splat_gaussians / outputs / gradients is a DEVICE
+ * pointer owned by the caller, valid on `stream`'s device.  Scratch that must survive until the
+ * backward pass is obtained through the caller's allocator callbacks (one per opaque buffer), so
+ * the caller's caching allocator owns it.  The library keeps no state between calls except a
+ * thread-local error string.
+ *
+ * Threading / streams: re-entrant; all work is enqueued on `stream` (a cudaStream_t passed as
+ * void*).  b200splat_forward performs ONE host synchronisation on `stream` (to learn the number
+ * of tile/Gaussian pairs before sizing the binning buffer), like the call it replaces.
+ */
+#ifndef B200SPLAT_H
+#define B200SPLAT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SPLAT_VERSION 1
+
+#if defined(__GNUC__)
+#define B200SPLAT_API __attribute__((visibility("default")))
+#else
+#define B200SPLAT_API
+#endif
+
+/* status codes */
+#define B200SPLAT_OK 0
+#define B200SPLAT_ERR_INVALID_ARG 1 /* bad sizes, missing/ambiguous inputs                     */
+#define B200SPLAT_ERR_CUDA 2        /* a CUDA call or kernel failed; see b200splat_last_error  */
+#define B200SPLAT_ERR_ALLOC 3       /* an allocator callback returned NULL                     */
+
+/* Allocator callback: return a device pointer to at least `bytes` bytes, aligned to 256 B, that
+ * stays valid until the matching backward call has completed (or NULL on failure). */
+typedef void* (*b200splat_alloc_fn)(void* ctx, size_t bytes);
+
+/* Per-view constants == the fields of GaussianRasterizationSettings
+ * (/root/reference/gaussian_renderer/__init__.py:47-60). */
+typedef struct b200splat_view {
+    int32_t image_height;
+    int32_t image_width;
+    float tanfovx;
+    float tanfovy;
+    float scale_modifier;
+    int32_t sh_degree;      /* active degree D (0..3), may be < the degree implied by M        */
+    int32_t prefiltered;    /* accepted for API parity; culled Gaussians are simply skipped     */
+    int32_t debug;          /* !=0: synchronise and check after every kernel                    */
+    int32_t antialiasing;   /* !=0: opacity *= sqrt(max(2.5e-5, det(cov2D)/det(cov2D+0.3I)))    */
+    const float* bg;         /* [3]                                                             */
+    const float* viewmatrix; /* [16] world_view_transform, row-vector convention (p' = [p,1] @ M) */
+    const float* projmatrix; /* [16] full_proj_transform, same convention                       */
+    const float* campos;     /* [3]                                                             */
+} b200splat_view;
+
+/* Per-Gaussian inputs == the tensor arguments of GaussianRasterizer.forward (:98-106).
+ * Exactly one of {shs, colors_precomp} and exactly one of {(scales, rotations), cov3D_precomp}
+ * must be non-NULL. */
+typedef struct b200splat_gaussians {
+    int32_t P;                   /* number of Gaussians                                          */
+    int32_t M;                   /* SH coefficients per Gaussian (tensor dim 1 of shs); 0 if none */
+    const float* means3D;        /* [P,3]                                                        */
+    const float* shs;            /* [P,M,3] coefficient-major, RGB innermost, or NULL            */
+    const float* colors_precomp; /* [P,3] or NULL                                                */
+    const float* opacities;      /* [P]                                                          */
+    const float* scales;         /* [P,3] or NULL                                                */
+    const float* rotations;      /* [P,4] unit quaternion (w,x,y,z) or NULL                      */
+    const float* cov3D_precomp;  /* [P,6] (xx,xy,xz,yy,yz,zz) or NULL                            */
+} b200splat_gaussians;
+
+typedef struct b200splat_forward_out {
+    float* color;     /* [3,H,W]                       */
+    int32_t* radii;   /* [P]; 0 = culled               */
+    float* invdepth;  /* [1,H,W] or NULL               */
+} b200splat_forward_out;
+
+/* The three opaque state buffers of the call being replaced (geometry / binning / image). */
+typedef struct b200splat_allocators {
+    b200splat_alloc_fn alloc;
+    void* geom_ctx;
+    void* binning_ctx;
+    void* image_ctx;
+} b200splat_allocators;
+
+/* Optional per-stage device times in milliseconds (NULL to skip).  Requesting them adds one
+ * synchronisation at the end of the call. */
+typedef struct b200splat_stage_times {
+    float preprocess_ms;
+    float scan_ms;
+    float duplicate_ms;
+    float sort_ms;
+    float ranges_ms;
+    float render_ms;
+    float render_bwd_ms;
+    float preprocess_bwd_ms;
+} b200splat_stage_times;
+
+/* Forward.  On success *num_rendered = number of (tile, Gaussian) pairs R. */
+B200SPLAT_API int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g,
+                      const b200splat_forward_out* out, const b200splat_allocators* alloc,
+                      int32_t* num_rendered, b200splat_stage_times* times /* nullable */,
+                      void* stream);
+
+/* Gradient outputs; each pointer may be NULL if the caller does not need it, except
+ * dL_dmeans3D.  Every non-NULL output is fully written (zeros for culled Gaussians): the caller
+ * need not clear them. */
+typedef struct b200splat_grads {
+    float* dL_dmeans2D;   /* [P,3]  xy = dL/d(NDC xy) (pixel gradient x 0.5W, 0.5H), z = 0      */
+    float* dL_dcolors;    /* [P,3]  gradient of colors_precomp                                   */
+    float* dL_dopacity;   /* [P]                                                                  */
+    float* dL_dmeans3D;   /* [P,3]                                                                */
+    float* dL_dcov3D;     /* [P,6]  gradient of cov3D_precomp                                    */
+    float* dL_dsh;        /* [P,M,3]                                                              */
+    float* dL_dscales;    /* [P,3]                                                                */
+    float* dL_drotations; /* [P,4]                                                                */
+} b200splat_grads;
+
+/* Backward.  geom / binning / image are the buffers the forward obtained through the allocator;
+ * radii is the forward's output.  scratch_alloc provides transient scratch for this call. */
+B200SPLAT_API int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g,
+                       const int32_t* radii, const void* geom, const void* binning,
+                       const void* image, int32_t num_rendered,
+                       const float* dL_dout_color /* [3,H,W] */,
+                       const float* dL_dout_invdepth /* [1,H,W] or NULL */,
+                       const b200splat_grads* grads, b200splat_alloc_fn scratch_alloc,
+                       void* scratch_ctx, b200splat_stage_times* times /* nullable */, void* stream);
+
+/* present[i] = 1 if Gaussian i passes the near-plane test (view z > 0.2), else 0. */
+B200SPLAT_API int b200splat_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                           const float* projmatrix, uint8_t* present, void* stream);
+
+/* Parity / inspection: copy pieces of the opaque forward state into caller device buffers (any
+ * pointer may be NULL).  Sorted keys are `(tile << 32) | float_bits(depth)`. */
+typedef struct b200splat_state_out {
+    float* means2D;           /* [P,2] pixel coordinates                  */
+    float* depths;            /* [P]                                      */
+    float* conic_opacity;     /* [P,4] (A,B,C,effective opacity)          */
+    float* rgb;               /* [P,3]                                    */
+    uint32_t* tiles_touched;  /* [P]                                      */
+    uint32_t* point_offsets;  /* [P] inclusive scan of tiles_touched      */
+    uint64_t* keys_sorted;    /* [R]                                      */
+    uint32_t* vals_sorted;    /* [R]                                      */
+    int32_t* ranges;          /* [T,2]                                    */
+    float* final_T;           /* [H,W]                                    */
+    uint32_t* n_contrib;      /* [H,W]                                    */
+} b200splat_state_out;
+
+B200SPLAT_API int b200splat_export_state(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
+                           const int32_t* radii, const void* geom, const void* binning,
+                           const void* image, const b200splat_state_out* out, void* stream);
+
+/* Sizes of the geometry and image buffers for given dimensions (the binning buffer depends on R). */
+B200SPLAT_API size_t b200splat_geom_bytes(int32_t P);
+B200SPLAT_API size_t b200splat_image_bytes(int32_t width, int32_t height);
+B200SPLAT_API size_t b200splat_binning_bytes(int32_t num_rendered);
+
+B200SPLAT_API const char* b200splat_last_error(void);
+B200SPLAT_API int b200splat_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SPLAT_H */
