@@ -1,0 +1,143 @@
+"""View-parallel training step (BASELINE.json configs[3]).
+
+The reference renders ONE view per optimizer step on ONE GPU (/root/reference/train.py:86-88,98) and has
+no distributed code.  The path shards naturally over camera views: Gaussians replicated, each rank
+rasterizes its own views, and the per-Gaussian parameter gradients (59 f32 per Gaussian at SH3:
+xyz 3 + SH 48 + opacity 1 + scale 3 + rotation 4, the optimizer groups of
+/root/reference/scene/gaussian_model.py:185-192) are sum-allreduced once per step.
+
+Densification side statistics keep the reference's semantics
+(/root/reference/scene/gaussian_model.py:576-581, /root/reference/train.py:127): the screen-space
+gradient NORM is taken per view and then summed (so it is accumulated locally per view, then
+sum-reduced), `denom` counts visible views, `max_radii2D` is max-reduced.
+
+Works with any torch.distributed backend (NCCL on the GPU box, gloo in the CPU tests -- the reduction
+logic is backend-agnostic and is tested with world_size 2 on CPU with a stand-in rasterize function).
+"""
+from __future__ import annotations
+
+from typing import Callable, List, NamedTuple, Optional, Sequence
+
+import torch
+
+
+class GaussianParams(NamedTuple):
+    means3D: torch.Tensor    # [P,3]
+    shs: torch.Tensor        # [P,M,3]
+    opacities: torch.Tensor  # [P,1]
+    scales: torch.Tensor     # [P,3]
+    rotations: torch.Tensor  # [P,4]
+
+
+GRAD_FLOATS_PER_GAUSSIAN = lambda M: 3 + 3 * M + 1 + 3 + 4   # noqa: E731  (59 at SH3)
+
+
+def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
+    """Rank r renders views {r, r + G, r + 2G, ...}."""
+    return list(range(rank, n_views, world_size))
+
+
+class ViewParallelStep:
+    """One data-parallel step: render this rank's views fwd+bwd, accumulate, reduce across ranks."""
+
+    def __init__(self, params: GaussianParams, sh_degree: int, bg: torch.Tensor, world_size: int = 1,
+                 process_group=None, rasterize: Optional[Callable] = None, scale_modifier: float = 1.0):
+        self.world_size = world_size
+        self.group = process_group
+        self.sh_degree = sh_degree
+        self.bg = bg
+        self.scale_modifier = scale_modifier
+        self.leaves = GaussianParams(*[t.detach().clone().requires_grad_(True) for t in params])
+        P = self.leaves.means3D.shape[0]
+        dev = self.leaves.means3D.device
+        self.xyz_gradient_accum = torch.zeros(P, 1, device=dev)
+        self.denom = torch.zeros(P, 1, device=dev)
+        self.max_radii2D = torch.zeros(P, device=dev)
+        self._rasterize = rasterize          # injectable for CPU tests; default = the CUDA operator
+        self.last_radii = None
+
+    # -- rasterizer call ------------------------------------------------------------------------------
+    def _render(self, cam, means2D):
+        if self._rasterize is not None:
+            return self._rasterize(cam, self.leaves, means2D, self.sh_degree, self.bg, self.scale_modifier)
+        import diff_gaussian_rasterization as dgr
+        rs = dgr.GaussianRasterizationSettings(cam.image_height, cam.image_width, cam.tanfovx, cam.tanfovy, self.bg,
+                                               self.scale_modifier, cam.world_view_transform, cam.full_proj_transform,
+                                               self.sh_degree, cam.camera_center, False, False)
+        lv = self.leaves
+        color, radii, _ = dgr.rasterize_gaussians(lv.means3D, means2D, lv.shs, None, lv.opacities, lv.scales,
+                                                  lv.rotations, None, rs)
+        return color, radii
+
+    # -- one step -------------------------------------------------------------------------------------
+    def step(self, cams: Sequence, dL_images: Sequence[torch.Tensor], reduce: bool = True) -> torch.Tensor:
+        for t in self.leaves:
+            t.grad = None
+        self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
+        color = None
+        for cam, dL in zip(cams, dL_images):
+            means2D = torch.zeros_like(self.leaves.means3D, requires_grad=True)
+            color, radii = self._render(cam, means2D)
+            torch.autograd.backward([color], [dL])
+            with torch.no_grad():
+                vis = radii > 0
+                self.xyz_gradient_accum += torch.norm(means2D.grad[:, :2], dim=-1, keepdim=True) * vis[:, None]
+                self.denom += vis[:, None].to(self.denom.dtype)
+                self.max_radii2D = torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype))
+            self.last_radii = radii
+        if reduce and self.world_size > 1:
+            self.all_reduce_grads()
+        return color.detach()
+
+    def all_reduce_grads(self):
+        import torch.distributed as dist
+        works = []
+        for t in self.leaves:
+            if t.grad is None:
+                t.grad = torch.zeros_like(t)
+            works.append(dist.all_reduce(t.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        works.append(dist.all_reduce(self.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        works.append(dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        works.append(dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=self.group, async_op=True))
+        for w in works:
+            w.wait()
+
+    def grads(self) -> GaussianParams:
+        return GaussianParams(*[t.grad for t in self.leaves])
+
+    def grad_checksum(self) -> torch.Tensor:
+        return self.leaves.means3D.grad.sum() + self.leaves.opacities.grad.sum()
+
+    # -- measurement helpers (CUDA path only) ------------------------------------------------------------
+    @staticmethod
+    def launches_per_view() -> int:
+        """Kernels of THIS library launched per view fwd+bwd: preprocess, duplicateWithKeys,
+        identifyTileRanges, render fwd, render bwd, per-Gaussian bwd (CUB scan/sort passes and memsets are
+        library / driver work and are not counted)."""
+        return 6
+
+    def stage_profile(self, cam, dL, iters: int = 5):
+        """Per-stage device milliseconds (CUDA events on the launch stream, inside the library) averaged
+        over `iters` fwd+bwd passes, plus workload statistics."""
+        import diff_gaussian_rasterization as dgr
+        C = dgr._C
+        lv = GaussianParams(*[t.detach() for t in self.leaves])
+        acc, stats = {}, {}
+        for it in range(iters + 1):
+            st = C.StageTimes()
+            res = C.rasterize_gaussians(self.bg, lv.means3D, None, lv.opacities, lv.scales, lv.rotations,
+                                        self.scale_modifier, None, cam.world_view_transform, cam.full_proj_transform,
+                                        cam.tanfovx, cam.tanfovy, cam.image_height, cam.image_width, lv.shs,
+                                        self.sh_degree, cam.camera_center, False, False, stage_times=st)
+            R, color, radii, geom, binning, img, _ = res
+            C.rasterize_gaussians_backward(self.bg, lv.means3D, radii, None, lv.scales, lv.rotations,
+                                           self.scale_modifier, None, cam.world_view_transform,
+                                           cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, self.sh_degree,
+                                           cam.camera_center, geom, R, binning, img, False, opacities=lv.opacities,
+                                           image_height=cam.image_height, image_width=cam.image_width, stage_times=st)
+            if it == 0:
+                stats = {"visible": int((radii > 0).sum().item()), "R": int(R)}
+                continue   # first pass is warm-up
+            for k, v in st.as_dict().items():
+                acc[k[:-3]] = acc.get(k[:-3], 0.0) + v / iters
+        return acc, stats

@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd views/s of the differentiable Gaussian-splat rasterizer (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" = one pass of the hot path (forward + backward) over one synthetic camera view per rank of the
+Garden-scale scene BASELINE.json configs[1] names: 3 M Gaussians, SH degree 3, 1920x1080.  With N > 1
+(torchrun, one rank per GPU) the Gaussians are replicated, every rank renders its own view each step
+(weak scaling) and the per-Gaussian parameter gradients are sum-allreduced with NCCL (configs[3]).
+
+One JSON line on stdout (rank 0).  `value` = whole-job views/s with inputs resident in HBM;
+`e2e` = the same through the drop-in operator with the per-view inputs (camera matrices, upstream image
+gradient) coming from pinned HOST memory and the rendered image + a gradient checksum read back to the
+host inside the timed region; `roofline` = dominant kernel against the measured HBM peak;
+`cpu_baseline` = the C oracle (all host threads) on a bounded sample of the same view.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+
+METRIC = "fwd+bwd views/s at 3M Gaussians SH3 1080p"
+UNIT = "views/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--gaussians", type=int, default=3_000_000)
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--sh-degree", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-tile-stride", type=int, default=16, help="CPU legs render 1/stride of the tiles")
+    ap.add_argument("--stages", action="store_true", help="print the per-stage table to stderr")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return f"synthetic scene seed 0: {a.gaussians} Gaussians SH{a.sh_degree}, {a.width}x{a.height}, one view per rank per step, fwd+bwd"
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.samples, self._stop, self._th = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._th = threading.Thread(target=self._run, daemon=True)
+        self._th.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        self._th.join(timeout=10)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            try:
+                sm.append(float(s[0])); mx.append(float(s[1]))
+                for nme, v in zip(names, s[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_setup(n):
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+# -----------------------------------------------------------------------------------------------------
+# our arm
+# -----------------------------------------------------------------------------------------------------
+def run_ours(a):
+    import torch.distributed as dist
+    rank, world, local = dist_setup(a.gpus)
+    pkg = importlib.import_module("3dgs_study_b200")
+    pkg.ensure_on_path()
+    synth = importlib.import_module("3dgs_study_b200.synth")
+    vp = importlib.import_module("3dgs_study_b200.view_parallel")
+    import diff_gaussian_rasterization as dgr
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    P, W, H, D = a.gaussians, a.width, a.height, a.sh_degree
+    scene_cpu = synth.make_scene(P, D, seed=0)
+    scene = scene_cpu.to(dev)
+    M = scene.shs.shape[1]
+    n_views = 8
+    cams_cpu = [synth.make_camera(W, H, yaw=2.0 * np.pi * k / n_views) for k in range(n_views)]
+    cams = [c.to(dev) for c in cams_cpu]
+    bg = torch.zeros(3, device=dev)
+    dL_cpu = synth.make_grad_image(W, H).pin_memory()
+    dL = dL_cpu.to(dev)
+    params = vp.GaussianParams(scene.means3D, scene.shs, scene.opacities, scene.scales, scene.rotations)
+    stepper = vp.ViewParallelStep(params, D, bg, world_size=world)
+
+    def view_of(step):   # rank r renders view (step * world + r) of the orbit
+        return (step * world + rank) % n_views
+
+    # ---------------- value: inputs resident in HBM -----------------------------------------------
+    def step_resident(i):
+        stepper.step([cams[view_of(i)]], [dL])
+
+    for i in range(a.warmup):
+        step_resident(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as cs:
+        torch.cuda.synchronize()
+        ev0.record()
+        for i in range(a.steps):
+            step_resident(a.warmup + i)
+        ev1.record()
+        torch.cuda.synchronize()
+    ms_total = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_per_step = ms_total / a.steps
+    value = world * 1000.0 / ms_per_step
+    clocks = cs.summary()
+
+    # ---------------- e2e: per-view inputs from pinned host memory, results read back ---------------
+    cam_host = [torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1), c.camera_center.reshape(-1)]).pin_memory()
+                for c in cams_cpu]
+    img_host = torch.empty(3, H, W).pin_memory()
+    chk_host = torch.empty(1).pin_memory()
+    h2d = cam_host[0].numel() * 4 + dL_cpu.numel() * 4
+    d2h = img_host.numel() * 4 + 4
+
+    def step_e2e(i):
+        k = view_of(i)
+        cm = cam_host[k].to(dev, non_blocking=True)
+        g_img = dL_cpu.to(dev, non_blocking=True)
+        cam = cams_cpu[k]._replace(world_view_transform=cm[:16].view(4, 4), full_proj_transform=cm[16:32].view(4, 4),
+                                   camera_center=cm[32:35])
+        img = stepper.step([cam], [g_img])
+        img_host.copy_(img, non_blocking=True)
+        chk_host.copy_(stepper.grad_checksum().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()      # the host consumes the result every step
+
+    for i in range(max(3, a.warmup // 2)):
+        step_e2e(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ev0.record()
+    for i in range(a.steps):
+        step_e2e(i)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms_e2e = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms_e2e], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+    e2e_value = world * 1000.0 / (ms_e2e / a.steps)
+
+    # ---------------- per-stage times + roofline (rank 0, CUDA events inside the library) ----------
+    stages, roof, launches, stats = {}, None, None, {}
+    if rank == 0:
+        stages, stats = stepper.stage_profile(cams[0], dL, iters=max(3, min(a.steps, 10)))
+        roof = roofline_from_stages(stages, stats, P, M, W, H)
+        launches = stepper.launches_per_view()
+    if world > 1:
+        dist.barrier()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return None
+    line = {
+        "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "gaussians": P, "sh_degree": D, "width": W, "height": H,
+                   "visible": stats.get("visible"), "tile_pairs_R": stats.get("R"), "views_per_rank_per_step": 1,
+                   "parallelism": f"view-parallel x{world}, Gaussians replicated" + (", NCCL sum-allreduce of 59 f32/Gaussian grads" if world > 1 else ""),
+                   "l2_note": "inputs (0.7 GB of Gaussians + 0.2 GB of keys per view) exceed the 126 MB L2; a different view every step"},
+        "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": round(ms_e2e / a.steps, 4),
+                "note": "Gaussians are model state resident in HBM (as in the reference); camera + upstream image gradient from pinned host, image + grad checksum to host, every step"},
+        "gpu_launches": int(launches * a.steps) if launches else None,
+        "clocks": clocks, "stages_ms": {k: round(v, 4) for k, v in stages.items()},
+        "roofline": roof,
+    }
+    if world > 1:
+        dist.destroy_process_group()
+    return line
+
+
+def roofline_from_stages(stages, stats, P, M, W, H):
+    """Dominant kernel vs the measured HBM peak; algorithmic bytes per SURVEY.md 8(d) / DESIGN.md."""
+    peaks, which = measured_peaks()
+    V, R = stats.get("visible", 0), stats.get("R", 0)
+    T, N = ((W + 15) // 16) * ((H + 15) // 16), W * H
+    end_bit = 32 + max(1, int(T).bit_length())
+    algo = {
+        "preprocess": 12 * P + V * (32 + 12 * M) + 8 * P + V * 52,
+        "scan": 8 * P,
+        "duplicate": V * 20 + 12 * R,
+        "sort": 24 * R * ((end_bit + 7) // 8) + 8 * R,
+        "ranges": 8 * R + 8 * T,
+        "render": 52 * R + 20 * N,
+        "render_bwd": 52 * R + 20 * N + 12 * N + 48 * V,
+        "preprocess_bwd": V * (12 + 4 + 28 + 12 * M + 48) + P * (40 + 12 * M),
+    }
+    rows = {}
+    for k, ms in stages.items():
+        if ms > 0 and k in algo:
+            gbs = algo[k] / (ms * 1e-3) / 1e9
+            rows[k] = {"ms": round(ms, 4), "algo_bytes": int(algo[k]), "gbs": round(gbs, 1), "frac_hbm": round(gbs / peaks["hbm_gbs"], 4)}
+    if not rows:
+        return None
+    top = max(rows, key=lambda k: rows[k]["ms"])
+    return {"kernel": top, "bound": "hbm", "achieved": rows[top]["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "frac": rows[top]["frac_hbm"], "traffic": None, "peak_source": which,
+            "note": "render kernels are FP32-issue / atomic bound, not HBM bound (DESIGN.md); HBM fraction reported per contract",
+            "per_stage": rows}
+
+
+# -----------------------------------------------------------------------------------------------------
+# CPU legs (the only places bench.py executes oracle/): cpu_baseline of our arm and --impl reference
+# -----------------------------------------------------------------------------------------------------
+class CpuOracleView:
+    """C oracle (oracle/splat_oracle.c, OpenMP over all host threads) on a BOUNDED SAMPLE of one view of the
+    same workload: all P Gaussians are preprocessed, binned and sorted and the per-Gaussian backward runs in
+    full; the tile render forward + backward runs on every `stride`-th tile and its time is scaled by
+    `stride`.  estimated full-view time = t_pre + t_bin + stride * (t_render + t_render_bwd) + t_pre_bwd."""
+
+    def __init__(self, a):
+        from oracle import c_oracle as co
+        synth = importlib.import_module("3dgs_study_b200.synth")
+        self.co, self.a = co, a
+        P, W, H, D = a.gaussians, a.width, a.height, a.sh_degree
+        sc = synth.make_scene(P, D, seed=0)
+        self.M = sc.shs.shape[1]
+        self.arr = {k: getattr(sc, k).numpy() for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        self.cams = [synth.make_camera(W, H, yaw=2.0 * np.pi * k / 8) for k in range(8)]
+        self.bg = np.zeros(3, np.float32)
+        self.dL = synth.make_grad_image(W, H).numpy()
+        self.cores = os.cpu_count() or 1
+
+    def step(self, i):
+        co, a, A = self.co, self.a, self.arr
+        P, W, H, D, M, s = a.gaussians, a.width, a.height, a.sh_degree, self.M, max(1, a.cpu_tile_stride)
+        cam = self.cams[i % 8]
+        v, p, c = cam.world_view_transform.numpy(), cam.full_proj_transform.numpy(), cam.camera_center.numpy()
+        t0 = time.perf_counter()
+        g = co.preprocess(P, D, M, W, H, A["means3D"], A["scales"], 1.0, A["rotations"], A["opacities"], A["shs"], None, None,
+                          v, p, c, cam.tanfovx, cam.tanfovy)
+        t1 = time.perf_counter()
+        b = co.bin_tiles(P, W, H, g)
+        t2 = time.perf_counter()
+        off = i % s
+        color, _, fT, nc = co.render(W, H, g, b, self.bg, tile_stride=s, tile_offset=off)
+        t3 = time.perf_counter()
+        rg = co.render_backward(P, W, H, g, b, self.bg, fT, nc, self.dL, tile_stride=s, tile_offset=off)
+        t4 = time.perf_counter()
+        co.preprocess_backward(P, D, M, W, H, A["means3D"], A["scales"], 1.0, A["rotations"], A["opacities"], A["shs"], None,
+                               v, p, c, cam.tanfovx, cam.tanfovy, False, g, rg)
+        t5 = time.perf_counter()
+        est = (t1 - t0) + (t2 - t1) + s * ((t3 - t2) + (t4 - t3)) + (t5 - t4)
+        return est, t5 - t0
+
+    def sample_desc(self):
+        a = self.a
+        return (f"C oracle (OpenMP, {self.cores} threads) per step: all {a.gaussians} Gaussians preprocessed+binned+sorted and "
+                f"per-Gaussian backward in full; tile render fwd+bwd on 1/{a.cpu_tile_stride} of the tiles, that time x{a.cpu_tile_stride}")
+
+
+def cpu_baseline_quick(a, budget_s=25.0):
+    """cpu_baseline of our arm: 1 warm-up + as many sampled steps as fit in ~budget_s (at least 1)."""
+    ov = CpuOracleView(a)
+    ov.step(0)
+    ests, spent, i = [], 0.0, 1
+    while spent < budget_s and i <= 4:
+        est, wall = ov.step(i)
+        ests.append(est); spent += wall; i += 1
+    est = float(np.median(ests))
+    return {"value": round(1.0 / est, 5), "unit": UNIT, "cores": ov.cores, "kind": "port",
+            "sample": ov.sample_desc(), "est_ms_per_view": round(est * 1e3, 1)}
+
+
+def torch_oracle_config1():
+    """BASELINE configs[0]: 10k Gaussians SH0, 256x256, fwd+bwd through the pure-PyTorch CPU oracle."""
+    from oracle import torch_ref as tr
+    synth = importlib.import_module("3dgs_study_b200.synth")
+    torch.set_num_threads(os.cpu_count() or 1)
+    P, W, H = 10000, 256, 256
+    sc, cam, dL = synth.make_scene(P, 0, seed=0), synth.make_camera(W, H), synth.make_grad_image(W, H)
+    times = []
+    for it in range(3):
+        lv = {k: getattr(sc, k).clone().requires_grad_() for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        t0 = time.perf_counter()
+        color, radii, _, _ = tr.rasterize_gaussians(image_height=H, image_width=W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+                                                    bg=torch.zeros(3), scale_modifier=1.0, viewmatrix=cam.world_view_transform,
+                                                    projmatrix=cam.full_proj_transform, sh_degree=0, campos=cam.camera_center,
+                                                    means2D=torch.zeros(P, 3, requires_grad=True), **lv)
+        torch.autograd.backward([color], [dL])
+        times.append(time.perf_counter() - t0)
+    return {"workload": "BASELINE configs[0]: 10k Gaussians SH0 256x256 fwd+bwd, pure-PyTorch CPU oracle",
+            "views_per_s": round(1.0 / float(np.median(times[1:])), 4), "cores": os.cpu_count()}
+
+
+def run_reference(a):
+    """--impl reference: the reference has no CPU rasterizer and its CUDA rasterizer source is absent from the
+    snapshot (unbuildable), so this arm times the oracle port on the host cores (kind "port")."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    ov = CpuOracleView(a)
+    for i in range(a.warmup):
+        ov.step(i)
+    ests = []
+    for i in range(a.steps):
+        est, _ = ov.step(a.warmup + i)
+        ests.append(est)
+    ms = float(np.mean(ests)) * 1e3
+    val = 1000.0 / ms
+    return {"impl": "reference", "metric": METRIC, "value": round(val, 5), "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": round(ms, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "gaussians": a.gaussians,
+                                                            "sh_degree": a.sh_degree, "width": a.width, "height": a.height},
+            "cpu_baseline": {"value": round(val, 5), "unit": UNIT, "cores": ov.cores, "kind": "port", "sample": ov.sample_desc()},
+            "e2e": {"value": round(val, 5), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference CUDA rasterizer: unavailable on this box (submodule source absent from /root/reference)"}
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        line = run_reference(a)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (impl ours) needs a CUDA GPU: the product has no CPU fallback")
+    line = run_ours(a)
+    if line is None:
+        return
+    if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not a.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline_quick(a)
+        try:
+            line["cpu_baseline_torch_config1"] = torch_oracle_config1()
+        except Exception as e:   # reported, never fatal
+            line["cpu_baseline_torch_config1"] = {"error": str(e)}
+    if a.stages:
+        for k, v in (line.get("roofline") or {}).get("per_stage", {}).items():
+            print(f"{k:16s} {v['ms']:8.3f} ms  {v['gbs']:8.1f} GB/s  {100 * v['frac_hbm']:5.1f}% of HBM peak", file=sys.stderr)
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

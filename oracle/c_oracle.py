@@ -98,7 +98,7 @@ def bin_tiles(P, W, H, g: Geom) -> Binning:
     return Binning(keys[:R], vals[:R], ranges)
 
 
-def render(W, H, g: Geom, b: Binning, bg, want_invdepth=False):
+def render(W, H, g: Geom, b: Binning, bg, want_invdepth=False, tile_stride=1, tile_offset=0):
     bg = _f32(bg)
     color = np.zeros((3, H, W), np.float32)
     invd = np.zeros((1, H, W), np.float32) if want_invdepth else None
@@ -107,7 +107,7 @@ def render(W, H, g: Geom, b: Binning, bg, want_invdepth=False):
     vals = b.vals if b.vals.size else np.zeros(1, np.uint32)
     lib().orc_render(ctypes.c_int(W), ctypes.c_int(H), _p(b.ranges), _p(vals), _p(g.means2D),
                      _p(g.conic_opacity), _p(g.rgb), _p(g.depths), _p(bg), _p(color), _p(invd),
-                     _p(final_T), _p(n_contrib))
+                     _p(final_T), _p(n_contrib), ctypes.c_int(tile_stride), ctypes.c_int(tile_offset))
     return color, invd, final_T, n_contrib
 
 
@@ -119,7 +119,8 @@ class RenderGrads(NamedTuple):
     dL_dinvd: np.ndarray     # [P]
 
 
-def render_backward(P, W, H, g: Geom, b: Binning, bg, final_T, n_contrib, dL_dpix, dL_dinvdepth=None) -> RenderGrads:
+def render_backward(P, W, H, g: Geom, b: Binning, bg, final_T, n_contrib, dL_dpix, dL_dinvdepth=None,
+                    tile_stride=1, tile_offset=0) -> RenderGrads:
     bg, dL_dpix, dL_dinvdepth = _f32(bg), _f32(dL_dpix), _f32(dL_dinvdepth)
     out = RenderGrads(np.zeros((P, 2), np.float32), np.zeros((P, 3), np.float32), np.zeros(P, np.float32),
                       np.zeros((P, 3), np.float32), np.zeros(P, np.float32))
@@ -128,7 +129,7 @@ def render_backward(P, W, H, g: Geom, b: Binning, bg, final_T, n_contrib, dL_dpi
                               _p(g.means2D), _p(g.conic_opacity), _p(g.rgb), _p(g.depths), _p(bg),
                               _p(final_T), _p(n_contrib), _p(dL_dpix), _p(dL_dinvdepth),
                               _p(out.dL_dmean2D), _p(out.dL_dconic), _p(out.dL_dopacity), _p(out.dL_dcolor),
-                              _p(out.dL_dinvd))
+                              _p(out.dL_dinvd), ctypes.c_int(tile_stride), ctypes.c_int(tile_offset))
     return out
 
 

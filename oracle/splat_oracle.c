@@ -311,11 +311,13 @@ static inline float gauss_power(float gxp, float gyp, float A, float B, float C,
 HOT ORC_API void orc_render(int W, int H, const int32_t* ranges, const uint32_t* vals,
                         const float* means2D, const float* conic_opacity, const float* rgb,
                         const float* depths, const float* bg, float* out_color,
-                        float* out_invdepth /* nullable */, float* final_T, uint32_t* n_contrib)
+                        float* out_invdepth /* nullable */, float* final_T, uint32_t* n_contrib,
+                        int tile_stride, int tile_offset /* bounded CPU sample: tiles with tile % stride == offset */)
 {
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 #pragma omp parallel for schedule(dynamic, 1)
     for (int tile = 0; tile < gx * gy; tile++) {
+        if (tile_stride > 1 && tile % tile_stride != tile_offset) continue;
         int ty = tile / gx, tx = tile % gx;
         int s = ranges[2 * tile], e = ranges[2 * tile + 1];
         for (int ly = 0; ly < TILE; ly++) for (int lx = 0; lx < TILE; lx++) {
@@ -365,13 +367,15 @@ HOT ORC_API void orc_render_backward(int P, int W, int H, const int32_t* ranges,
                                  const uint32_t* n_contrib, const float* dL_dpix,
                                  const float* dL_dinvdepth /* nullable */,
                                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
-                                 float* dL_dcolor, float* dL_dinvd /* [P], nullable: d/d(1/depth) */)
+                                 float* dL_dcolor, float* dL_dinvd /* [P], nullable: d/d(1/depth) */,
+                                 int tile_stride, int tile_offset)
 {
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
     double* acc = (double*)calloc((size_t)P * 10, sizeof(double));
     const size_t HW = (size_t)H * W;
 #pragma omp parallel for schedule(dynamic, 1)
     for (int tile = 0; tile < gx * gy; tile++) {
+        if (tile_stride > 1 && tile % tile_stride != tile_offset) continue;
         int ty = tile / gx, tx = tile % gx;
         int s = ranges[2 * tile];
         for (int ly = 0; ly < TILE; ly++) for (int lx = 0; lx < TILE; lx++) {
