@@ -57,6 +57,37 @@ struct StageTimer {
     }
 };
 
+// Host-side mailbox for the pair count R: a pinned 8-byte slot and an event per host thread, created on
+// first use and kept for the life of the thread (the only state the library keeps besides the error
+// string).  The forward copies R into the slot right after the preprocess kernel, records the event, then
+// keeps enqueueing work that does not depend on R (the depth sort) BEFORE waiting on the event, so the
+// host round trip and the binning-buffer allocation are hidden behind device work.
+struct Mailbox {
+    unsigned long long* slot = nullptr;
+    cudaEvent_t ev = nullptr;
+    int device = -1;
+    ~Mailbox() {
+        if (slot) cudaFreeHost(slot);
+        if (ev) cudaEventDestroy(ev);
+    }
+    cudaError_t ensure() {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (slot && dev == device) return cudaSuccess;
+        if (ev) { cudaEventDestroy(ev); ev = nullptr; }
+        if (!slot) {
+            e = cudaHostAlloc((void**)&slot, sizeof(unsigned long long), cudaHostAllocDefault);
+            if (e != cudaSuccess) { slot = nullptr; return e; }
+        }
+        e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+        if (e != cudaSuccess) { ev = nullptr; return e; }
+        device = dev;
+        return cudaSuccess;
+    }
+};
+thread_local Mailbox g_mailbox;
+
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 int validate(const b200splat_view* v, const b200splat_gaussians* g) {
@@ -92,7 +123,9 @@ int b200splat_version(void) { return B200SPLAT_VERSION; }
 
 size_t b200splat_geom_bytes(int32_t P) { return carve_geom(nullptr, P).total; }
 size_t b200splat_image_bytes(int32_t width, int32_t height) { return carve_image(nullptr, width, height).total; }
-size_t b200splat_binning_bytes(int32_t num_rendered) { return carve_binning(nullptr, num_rendered, 64).total; }
+size_t b200splat_binning_bytes(int32_t num_rendered, int32_t width, int32_t height) {
+    return carve_binning(nullptr, num_rendered, tiles_of(width, height)).total;
+}
 
 int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g, const b200splat_forward_out* out,
                       const b200splat_allocators* alloc, int32_t* num_rendered, b200splat_stage_times* times,
@@ -111,28 +144,37 @@ int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g, 
     GeomView gv = carve_geom(geom_mem, P);
     ImgView iv = carve_image(img_mem, W, H);
 
+    const int T = tiles_of(W, H);
+    unsigned long long* pair_counter = reinterpret_cast<unsigned long long*>(iv.counters + CTR_PAIRS);
+    CU(g_mailbox.ensure(), "pinned mailbox");
+
     StageTimer tm(times != nullptr, stream);
     tm.mark();
-    STAGE(launch_preprocess_fwd(*view, *g, gv, out->radii, stream), "preprocess");
+    CU(cudaMemsetAsync(iv.counters, 0, 64 * sizeof(unsigned int), stream), "clear counters");
+    STAGE(launch_preprocess_fwd(*view, *g, gv, out->radii, pair_counter, stream), "preprocess");
     tm.mark();
-    STAGE(launch_scan(gv, P, stream), "scan");
-    uint32_t R = 0;
+    unsigned long long R = 0;
     if (P > 0) {
-        CU(cudaMemcpyAsync(&R, gv.offsets + (P - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, stream), "read num_rendered");
-        CU(cudaStreamSynchronize(stream), "sync num_rendered");
+        CU(cudaMemcpyAsync(g_mailbox.slot, pair_counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream), "read num_rendered");
+        CU(cudaEventRecord(g_mailbox.ev, stream), "record num_rendered");
     }
-    if (R > 0x7fffffffu) return fail(B200SPLAT_ERR_INVALID_ARG, "more than 2^31-1 tile/Gaussian pairs");
+    // independent of R: runs on the device while the host waits for R and sizes the binning buffer
+    STAGE(launch_depth_order(gv, P, stream), "depth order");
     tm.mark();
+    if (P > 0) {
+        CU(cudaEventSynchronize(g_mailbox.ev), "sync num_rendered");
+        R = *g_mailbox.slot;
+    }
+    if (R > 0x7fffffffull) return fail(B200SPLAT_ERR_INVALID_ARG, "more than 2^31-1 tile/Gaussian pairs");
     *num_rendered = (int32_t)R;
 
-    void* bin_mem = alloc->alloc(alloc->binning_ctx, b200splat_binning_bytes((int32_t)R));
+    void* bin_mem = alloc->alloc(alloc->binning_ctx, b200splat_binning_bytes((int32_t)R, W, H));
     if (!bin_mem) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (binning buffer)");
-    const int end_bit = sort_end_bit(W, H);
-    BinView bv = carve_binning(bin_mem, (int)R, 64);
+    BinView bv = carve_binning(bin_mem, (int)R, T);
 
-    STAGE(launch_duplicate(gv, out->radii, P, W, H, bv, stream), "duplicateWithKeys");
+    if (R > 0) STAGE(launch_emit(gv, P, W, H, bv, stream), "duplicateWithKeys");
     tm.mark();
-    STAGE(launch_sort(bv, (int)R, end_bit, stream), "sort");
+    STAGE(launch_tile_sort(bv, (int)R, T, stream), "sort");
     tm.mark();
     STAGE(launch_ranges(bv, (int)R, iv, W, H, stream), "identifyTileRanges");
     tm.mark();
@@ -167,7 +209,7 @@ int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g,
     if (P == 0) return B200SPLAT_OK;
 
     GeomView gv = carve_geom(const_cast<void*>(geom), P);
-    BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, 64);
+    BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, tiles_of(W, H));
     ImgView iv = carve_image(const_cast<void*>(image), W, H);
 
     const size_t acc_bytes = (size_t)P * 12 * sizeof(float);
@@ -206,12 +248,13 @@ int b200splat_export_state(int32_t P, int32_t width, int32_t height, int32_t num
         GeomView gv = carve_geom(const_cast<void*>(geom), P);
         CU(launch_export_geom(P, radii, gv, *out, stream), "export geometry");
     }
-    if (binning && num_rendered > 0) {
-        BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, 64);
-        if (out->keys_sorted)
-            CU(cudaMemcpyAsync(out->keys_sorted, bv.keys_sorted, sizeof(uint64_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, stream), "export keys");
-        if (out->vals_sorted)
-            CU(cudaMemcpyAsync(out->vals_sorted, bv.vals_sorted, sizeof(uint32_t) * (size_t)num_rendered, cudaMemcpyDeviceToDevice, stream), "export vals");
+    if (geom && P > 0) {
+        GeomView gv = carve_geom(const_cast<void*>(geom), P);
+        BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, tiles_of(width, height));
+        const int R = binning ? num_rendered : 0;
+        CU(launch_export_binning(P, R, gv, bv, *out, stream), "export binning");
+        if (out->vals_sorted && R > 0)
+            CU(cudaMemcpyAsync(out->vals_sorted, bv.vals_sorted, sizeof(uint32_t) * (size_t)R, cudaMemcpyDeviceToDevice, stream), "export vals");
     }
     if (image) {
         ImgView iv = carve_image(const_cast<void*>(image), width, height);

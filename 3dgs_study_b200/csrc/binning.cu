@@ -1,35 +1,81 @@
-// binning.cu -- tile binning: inclusive scan of tiles_touched, duplicateWithKeys (64-bit
-// tile|depth keys emitted in Gaussian-index order, row-major over each tile rectangle), stable
-// radix sort of the (key, Gaussian) pairs and identifyTileRanges.  HBM-bound integer work.
+// binning.cu -- tile binning, sm_100a.  HBM-bound integer work.
 //
 // Stands in for the binning stages of _C.rasterize_gaussians named by BASELINE.json's north_star
 // ("duplicateWithKeys pass emitting 64-bit tile|depth keys, then a radix sort and identifyTileRanges").
+// The RESULT is bit-identical to that formulation -- every tile's list is ordered by (depth bits,
+// Gaussian id), exactly what a stable sort of (tile << 32 | depth) keys emitted in Gaussian order
+// yields -- but the traffic is a fraction of it (see splat_internal.cuh "Binning order"):
+//
+//   1. depth order   stable radix sort of the P (depth bits, id) pairs      4 passes x 16 B x P
+//   2. offsets       inclusive scan of tiles touched, in depth order          gather + 4 B x P
+//   3. emit          block-cooperative duplicateWithKeys: a block owns 256 consecutive Gaussians of the
+//                    depth order and therefore a CONTIGUOUS output range; consecutive threads write
+//                    consecutive (tile key, id) slots (binary search in the block's offsets), so the
+//                    writes are fully coalesced and a huge splat cannot serialise one thread
+//   4. tile sort     stable radix sort on the tile bits only                  2 passes x 12 B x R
+//   5. ranges        identifyTileRanges on the sorted tile keys
+//
+// The 64-bit keys are never materialised on the hot path; b200splat_export_state rebuilds them for
+// the parity tests from (sorted tile key, depth of the sorted id).
 #include <cub/cub.cuh>
 
 #include "splat_internal.cuh"
 
 namespace b200splat {
 
+namespace {
+
+// tiles touched by the j-th Gaussian of the depth order
+struct TilesInDepthOrder {
+    const uint32_t* order;
+    const uint2* rect;
+    __device__ __forceinline__ uint32_t operator()(uint32_t j) const {
+        const uint32_t wh = __ldg(&rect[__ldg(order + j)].y);
+        return (wh & 0xffffu) * (wh >> 16);
+    }
+};
+// tiles touched by Gaussian i (index order; export only)
+struct TilesInIndexOrder {
+    const uint2* rect;
+    __device__ __forceinline__ uint32_t operator()(uint32_t i) const {
+        const uint32_t wh = rect[i].y;
+        return (wh & 0xffffu) * (wh >> 16);
+    }
+};
+template <typename Op>
+using TilesIt = cub::TransformInputIterator<uint32_t, Op, cub::CountingInputIterator<uint32_t>>;
+
 size_t scan_temp_bytes(int P) {
+    size_t a = 0, b = 0;
+    TilesIt<TilesInDepthOrder> it(cub::CountingInputIterator<uint32_t>(0), TilesInDepthOrder{nullptr, nullptr});
+    cub::DeviceScan::InclusiveSum(nullptr, a, it, (uint32_t*)nullptr, P > 0 ? P : 1);
+    TilesIt<TilesInIndexOrder> it2(cub::CountingInputIterator<uint32_t>(0), TilesInIndexOrder{nullptr});
+    cub::DeviceScan::InclusiveSum(nullptr, b, it2, (uint32_t*)nullptr, P > 0 ? P : 1);
+    return a > b ? a : b;
+}
+
+size_t depth_sort_temp_bytes(int P) {
     size_t bytes = 0;
-    cub::DeviceScan::InclusiveSum(nullptr, bytes, (uint32_t*)nullptr, (uint32_t*)nullptr, P > 0 ? P : 1);
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr,
+                                    (uint32_t*)nullptr, P > 0 ? P : 1, 0, 32);
     return bytes;
 }
 
-size_t sort_temp_bytes(int R, int end_bit) {
+int tile_bits(int num_tiles) {
+    int bits = 1;
+    while (bits < 32 && ((unsigned)(num_tiles - 1) >> bits) != 0) bits++;
+    return bits;
+}
+
+template <typename KeyT>
+size_t tile_sort_temp_bytes(int R, int num_tiles) {
     size_t bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (uint64_t*)nullptr, (uint64_t*)nullptr, (uint32_t*)nullptr,
-                                    (uint32_t*)nullptr, R > 0 ? R : 1, 0, end_bit);
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (KeyT*)nullptr, (KeyT*)nullptr, (uint32_t*)nullptr,
+                                    (uint32_t*)nullptr, R > 0 ? R : 1, 0, tile_bits(num_tiles));
     return bytes;
 }
 
-// number of key bits that can differ: 32 depth bits + bits of the largest tile id
-int sort_end_bit(int W, int H) {
-    unsigned tiles = (unsigned)(((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE));
-    int bits = 0;
-    while ((tiles >> bits) != 0 && bits < 32) bits++;
-    return 32 + bits;
-}
+}  // namespace
 
 GeomView carve_geom(void* base, int P) {
     GeomView g;
@@ -38,24 +84,30 @@ GeomView carve_geom(void* base, int P) {
     size_t n = (size_t)(P > 0 ? P : 1);
     g.depths = (float*)(b + off); off += align256(n * sizeof(float));
     g.rec = (float4*)(b + off); off += align256(n * 3 * sizeof(float4));
-    g.tiles = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.rect = (uint2*)(b + off); off += align256(n * sizeof(uint2));
+    g.iota = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.depth_sorted = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.order = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
     g.offsets = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
     g.scan_tmp_bytes = scan_temp_bytes(P);
     g.scan_tmp = (void*)(b + off); off += align256(g.scan_tmp_bytes);
+    g.dsort_tmp_bytes = depth_sort_temp_bytes(P);
+    g.dsort_tmp = (void*)(b + off); off += align256(g.dsort_tmp_bytes);
     g.total = off;
     return g;
 }
 
-BinView carve_binning(void* base, int R, int end_bit) {
+BinView carve_binning(void* base, int R, int num_tiles) {
     BinView v;
     size_t off = 0;
     char* b = (char*)base;
     size_t n = (size_t)(R > 0 ? R : 1);
-    v.keys_unsorted = (uint64_t*)(b + off); off += align256(n * sizeof(uint64_t));
-    v.keys_sorted = (uint64_t*)(b + off); off += align256(n * sizeof(uint64_t));
+    v.key_bytes = num_tiles <= 65536 ? 2 : 4;
+    v.keys_unsorted = (void*)(b + off); off += align256(n * v.key_bytes);
+    v.keys_sorted = (void*)(b + off); off += align256(n * v.key_bytes);
     v.vals_unsorted = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
     v.vals_sorted = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
-    v.sort_tmp_bytes = sort_temp_bytes(R, end_bit);
+    v.sort_tmp_bytes = v.key_bytes == 2 ? tile_sort_temp_bytes<uint16_t>(R, num_tiles) : tile_sort_temp_bytes<uint32_t>(R, num_tiles);
     v.sort_tmp = (void*)(b + off); off += align256(v.sort_tmp_bytes);
     v.total = off;
     return v;
@@ -65,7 +117,7 @@ ImgView carve_image(void* base, int W, int H) {
     ImgView v;
     size_t off = 0;
     char* b = (char*)base;
-    size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    size_t T = (size_t)tiles_of(W, H);
     size_t N = (size_t)W * H;
     v.ranges = (int2*)(b + off); off += align256((T > 0 ? T : 1) * sizeof(int2));
     v.final_T = (float*)(b + off); off += align256((N > 0 ? N : 1) * sizeof(float));
@@ -77,72 +129,142 @@ ImgView carve_image(void* base, int W, int H) {
 
 namespace {
 
-// One thread per Gaussian; keys are written at [offsets[i-1], offsets[i]) in row-major tile order so
-// that a stable sort leaves equal (tile, depth) keys in Gaussian-index order.
-__global__ void __launch_bounds__(256) duplicate_with_keys_kernel(int P, int gx, int gy, const int32_t* __restrict__ radii,
-                                                                  const float4* __restrict__ rec,
-                                                                  const float* __restrict__ depths,
-                                                                  const uint32_t* __restrict__ offsets,
-                                                                  uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    const int r = radii[i];
-    if (r <= 0) return;
-    uint32_t off = (i == 0) ? 0u : offsets[i - 1];
-    const float4 a = __ldg(rec + 3 * (size_t)i);
-    int minx, miny, maxx, maxy;
-    get_rect(a.x, a.y, r, gx, gy, minx, miny, maxx, maxy);
-    const uint64_t dbits = (uint64_t)__float_as_uint(depths[i]);
-    for (int y = miny; y < maxy; y++) {
-        for (int x = minx; x < maxx; x++) {
-            keys[off] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | dbits;
-            vals[off] = (uint32_t)i;
-            off++;
+constexpr int EMIT_THREADS = 256;
+
+// Block-cooperative duplicateWithKeys.  Block b owns depth-order positions [256 b, 256 b + 256) and the
+// output slots [offsets[256 b - 1], offsets[256 b + 255]).  Slot k of Gaussian g (rect minx, miny, w, h)
+// is tile (miny + k / w) * gx + minx + k % w: row-major over the rectangle, as the oracle emits.
+template <typename KeyT>
+__global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int P, int gx, const uint32_t* __restrict__ order,
+                                                                 const uint2* __restrict__ rect,
+                                                                 const uint32_t* __restrict__ offsets,
+                                                                 KeyT* __restrict__ keys, uint32_t* __restrict__ vals) {
+    __shared__ uint32_t s_end[EMIT_THREADS];     // inclusive offsets of this block's Gaussians
+    __shared__ uint32_t s_id[EMIT_THREADS];
+    __shared__ uint2 s_rect[EMIT_THREADS];
+    const int tid = threadIdx.x;
+    const int j0 = blockIdx.x * EMIT_THREADS;
+    const int j = min(j0 + tid, P - 1);
+    const uint32_t id = __ldg(order + j);
+    s_id[tid] = id;
+    s_rect[tid] = __ldg(rect + id);
+    s_end[tid] = __ldg(offsets + j);
+    const uint32_t base = j0 == 0 ? 0u : __ldg(offsets + j0 - 1);
+    __syncthreads();
+    const uint32_t total = s_end[EMIT_THREADS - 1] - base;
+    for (uint32_t k = tid; k < total; k += EMIT_THREADS) {
+        const uint32_t slot = base + k;
+        // first g with s_end[g] > slot
+        int lo = 0, hi = EMIT_THREADS - 1;
+#pragma unroll
+        for (int it = 0; it < 8; it++) {
+            const int mid = (lo + hi) >> 1;
+            if (s_end[mid] > slot) hi = mid; else lo = mid + 1;
         }
+        const int g = lo;
+        const uint2 r = s_rect[g];
+        const uint32_t w = r.y & 0xffffu;
+        const uint32_t first = s_end[g] - w * (r.y >> 16);
+        const uint32_t local = slot - first;
+        const uint32_t row = local / w, col = local - row * w;
+        keys[slot] = (KeyT)(((r.x >> 16) + row) * (uint32_t)gx + (r.x & 0xffffu) + col);
+        vals[slot] = s_id[g];
     }
 }
 
-__global__ void __launch_bounds__(256) identify_tile_ranges_kernel(int R, const uint64_t* __restrict__ keys,
+template <typename KeyT>
+__global__ void __launch_bounds__(256) identify_tile_ranges_kernel(int R, const KeyT* __restrict__ keys,
                                                                    int2* __restrict__ ranges) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= R) return;
-    const uint32_t t = (uint32_t)(keys[j] >> 32);
+    const uint32_t t = (uint32_t)keys[j];
     if (j == 0) ranges[t].x = 0;
     else {
-        const uint32_t tp = (uint32_t)(keys[j - 1] >> 32);
+        const uint32_t tp = (uint32_t)keys[j - 1];
         if (tp != t) { ranges[tp].y = j; ranges[t].x = j; }
     }
     if (j == R - 1) ranges[t].y = R;
 }
 
-}  // namespace
-
-cudaError_t launch_scan(GeomView gv, int P, cudaStream_t s) {
-    if (P == 0) return cudaSuccess;
-    size_t bytes = gv.scan_tmp_bytes;
-    return cub::DeviceScan::InclusiveSum(gv.scan_tmp, bytes, gv.tiles, gv.offsets, P, s);
+template <typename KeyT>
+__global__ void export_keys_kernel(int R, const KeyT* __restrict__ tile_keys, const uint32_t* __restrict__ vals,
+                                   const float* __restrict__ depths, uint64_t* __restrict__ out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= R) return;
+    out[j] = ((uint64_t)tile_keys[j] << 32) | (uint64_t)__float_as_uint(depths[vals[j]]);
 }
 
-cudaError_t launch_duplicate(GeomView gv, const int32_t* radii, int P, int W, int H, BinView bv, cudaStream_t s) {
+__global__ void export_tiles_kernel(int P, const uint2* __restrict__ rect, uint32_t* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t wh = rect[i].y;
+    out[i] = (wh & 0xffffu) * (wh >> 16);
+}
+
+}  // namespace
+
+cudaError_t launch_depth_order(GeomView gv, int P, cudaStream_t s) {
     if (P == 0) return cudaSuccess;
-    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
-    duplicate_with_keys_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, gx, gy, radii, gv.rec, gv.depths, gv.offsets,
-                                                             bv.keys_unsorted, bv.vals_unsorted);
+    size_t bytes = gv.dsort_tmp_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(gv.dsort_tmp, bytes, reinterpret_cast<const uint32_t*>(gv.depths),
+                                                    gv.depth_sorted, gv.iota, gv.order, P, 0, 32, s);
+    if (e != cudaSuccess) return e;
+    TilesIt<TilesInDepthOrder> it(cub::CountingInputIterator<uint32_t>(0), TilesInDepthOrder{gv.order, gv.rect});
+    bytes = gv.scan_tmp_bytes;
+    return cub::DeviceScan::InclusiveSum(gv.scan_tmp, bytes, it, gv.offsets, P, s);
+}
+
+cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    const int gx = (W + TILE - 1) / TILE;
+    const int blocks = (P + EMIT_THREADS - 1) / EMIT_THREADS;
+    if (bv.key_bytes == 2)
+        emit_keys_kernel<uint16_t><<<blocks, EMIT_THREADS, 0, s>>>(P, gx, gv.order, gv.rect, gv.offsets,
+                                                                  (uint16_t*)bv.keys_unsorted, bv.vals_unsorted);
+    else
+        emit_keys_kernel<uint32_t><<<blocks, EMIT_THREADS, 0, s>>>(P, gx, gv.order, gv.rect, gv.offsets,
+                                                                  (uint32_t*)bv.keys_unsorted, bv.vals_unsorted);
     return cudaGetLastError();
 }
 
-cudaError_t launch_sort(BinView bv, int R, int end_bit, cudaStream_t s) {
+cudaError_t launch_tile_sort(BinView bv, int R, int num_tiles, cudaStream_t s) {
     if (R == 0) return cudaSuccess;
     size_t bytes = bv.sort_tmp_bytes;
-    return cub::DeviceRadixSort::SortPairs(bv.sort_tmp, bytes, bv.keys_unsorted, bv.keys_sorted, bv.vals_unsorted,
-                                           bv.vals_sorted, R, 0, end_bit, s);
+    const int bits = tile_bits(num_tiles);
+    if (bv.key_bytes == 2)
+        return cub::DeviceRadixSort::SortPairs(bv.sort_tmp, bytes, (const uint16_t*)bv.keys_unsorted, (uint16_t*)bv.keys_sorted,
+                                               bv.vals_unsorted, bv.vals_sorted, R, 0, bits, s);
+    return cub::DeviceRadixSort::SortPairs(bv.sort_tmp, bytes, (const uint32_t*)bv.keys_unsorted, (uint32_t*)bv.keys_sorted,
+                                           bv.vals_unsorted, bv.vals_sorted, R, 0, bits, s);
 }
 
 cudaError_t launch_ranges(BinView bv, int R, ImgView iv, int W, int H, cudaStream_t s) {
-    const size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    const size_t T = (size_t)tiles_of(W, H);
     cudaError_t e = cudaMemsetAsync(iv.ranges, 0, T * sizeof(int2), s);
     if (e != cudaSuccess || R == 0) return e;
-    identify_tile_ranges_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, bv.keys_sorted, iv.ranges);
+    if (bv.key_bytes == 2)
+        identify_tile_ranges_kernel<uint16_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, iv.ranges);
+    else
+        identify_tile_ranges_kernel<uint32_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, iv.ranges);
+    return cudaGetLastError();
+}
+
+// Parity / inspection only: rebuild the 64-bit keys, tiles touched and the index-order offsets.
+cudaError_t launch_export_binning(int P, int R, GeomView gv, BinView bv, const b200splat_state_out& o, cudaStream_t s) {
+    if (o.keys_sorted && R > 0) {
+        if (bv.key_bytes == 2)
+            export_keys_kernel<uint16_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, bv.vals_sorted, gv.depths, o.keys_sorted);
+        else
+            export_keys_kernel<uint32_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, bv.vals_sorted, gv.depths, o.keys_sorted);
+    }
+    if (o.tiles_touched && P > 0) export_tiles_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, gv.rect, o.tiles_touched);
+    if (o.point_offsets && P > 0) {
+        // the forward's scan scratch is dead once the forward has finished
+        TilesIt<TilesInIndexOrder> it(cub::CountingInputIterator<uint32_t>(0), TilesInIndexOrder{gv.rect});
+        size_t bytes = gv.scan_tmp_bytes;
+        cudaError_t e = cub::DeviceScan::InclusiveSum(gv.scan_tmp, bytes, it, o.point_offsets, P, s);
+        if (e != cudaSuccess) return e;
+    }
     return cudaGetLastError();
 }
 

@@ -99,18 +99,25 @@ __device__ __forceinline__ void project_cov(const ViewConsts& vc, float tx, floa
 
 __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p, float* __restrict__ depths,
                                                                      float4* __restrict__ rec,
-                                                                     uint32_t* __restrict__ tiles,
-                                                                     int32_t* __restrict__ radii) {
+                                                                     uint2* __restrict__ rect,
+                                                                     uint32_t* __restrict__ iota,
+                                                                     int32_t* __restrict__ radii,
+                                                                     unsigned long long* __restrict__ pair_counter) {
     __shared__ ViewConsts vc;
+    __shared__ uint32_t s_pairs[PRE_THREADS / 32];
     load_view_consts(vc, p.view, p.proj, p.campos);
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
-    if (i >= p.P) return;
+    const bool in_range = i < p.P;
 
-    const float x = __ldg(p.means3D + 3 * i), y = __ldg(p.means3D + 3 * i + 1), z = __ldg(p.means3D + 3 * i + 2);
-    const float tz = cadd(cfma(vc.view[10], z, cfma(vc.view[6], y, cmul(vc.view[2], x))), vc.view[14]);
+    float x = 0.f, y = 0.f, z = 0.f, tz = 0.f;
+    if (in_range) {
+        x = __ldg(p.means3D + 3 * i); y = __ldg(p.means3D + 3 * i + 1); z = __ldg(p.means3D + 3 * i + 2);
+        tz = cadd(cfma(vc.view[10], z, cfma(vc.view[6], y, cmul(vc.view[2], x))), vc.view[14]);
+    }
     int radius = 0;
     uint32_t area = 0;
-    if (tz > NEAR_Z) {
+    uint2 rc = make_uint2(0u, 0u);
+    if (in_range && tz > NEAR_Z) {
         const float tx = cadd(cfma(vc.view[8], z, cfma(vc.view[4], y, cmul(vc.view[0], x))), vc.view[12]);
         const float ty = cadd(cfma(vc.view[9], z, cfma(vc.view[5], y, cmul(vc.view[1], x))), vc.view[13]);
         const float hx = cadd(cfma(vc.proj[8], z, cfma(vc.proj[4], y, cmul(vc.proj[0], x))), vc.proj[12]);
@@ -173,7 +180,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
                         ey = sqrtf(tau2 * c) * 1.001f + 0.01f;
                     } else { ex = -1.0f; ey = -1.0f; }
                 } else { thr = __int_as_float(0x7f800000); ex = -1.0f; ey = -1.0f; }
-                depths[i] = tz;
+                rc = make_uint2((uint32_t)minx | ((uint32_t)miny << 16), (uint32_t)(maxx - minx) | ((uint32_t)(maxy - miny) << 16));
                 rec[3 * (size_t)i + 0] = make_float4(px, py, ex, ey);
                 rec[3 * (size_t)i + 1] = make_float4(cmul(-0.5f, conA), conB, cmul(-0.5f, conC), thr);
                 rec[3 * (size_t)i + 2] = make_float4(o, rgb[0], rgb[1], rgb[2]);
@@ -182,8 +189,21 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
             }
         }
     }
-    radii[i] = radius;
-    tiles[i] = area;
+    if (in_range) {
+        radii[i] = radius;
+        rect[i] = rc;
+        iota[i] = (uint32_t)i;
+        depths[i] = area ? tz : __uint_as_float(0xffffffffu);   // as u32: the depth-sort key, culled last
+    }
+    // pair count R: one atomic per block
+    uint32_t sum = __reduce_add_sync(0xffffffffu, area);
+    if ((threadIdx.x & 31) == 0) s_pairs[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        sum = threadIdx.x < PRE_THREADS / 32 ? s_pairs[threadIdx.x] : 0u;
+        sum = __reduce_add_sync(0xffffffffu, sum);
+        if (threadIdx.x == 0 && sum) atomicAdd(pair_counter, (unsigned long long)sum);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -473,8 +493,6 @@ __global__ void export_geom_kernel(int P, const int32_t* __restrict__ radii, Geo
         o.conic_opacity[4 * i + 2] = -2.0f * b.z; o.conic_opacity[4 * i + 3] = c.x;
     }
     if (o.rgb) { o.rgb[3 * i] = c.y; o.rgb[3 * i + 1] = c.z; o.rgb[3 * i + 2] = c.w; }
-    if (o.tiles_touched) o.tiles_touched[i] = gv.tiles[i];
-    if (o.point_offsets) o.point_offsets[i] = gv.offsets[i];
 }
 
 PreParams make_params(const b200splat_view& v, const b200splat_gaussians& g) {
@@ -494,10 +512,11 @@ PreParams make_params(const b200splat_view& v, const b200splat_gaussians& g) {
 }  // namespace
 
 cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gaussians& g, GeomView gv,
-                                  int32_t* radii, cudaStream_t s) {
+                                  int32_t* radii, unsigned long long* pair_counter, cudaStream_t s) {
     if (g.P == 0) return cudaSuccess;
     PreParams p = make_params(v, g);
-    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(p, gv.depths, gv.rec, gv.tiles, radii);
+    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(p, gv.depths, gv.rec, gv.rect, gv.iota,
+                                                                                      radii, pair_counter);
     return cudaGetLastError();
 }
 

@@ -161,6 +161,12 @@ __global__ void __launch_bounds__(RW * 32) render_fwd_kernel(
     }
 }
 
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
     v += __shfl_xor_sync(FULL, v, 16);
     v += __shfl_xor_sync(FULL, v, 8);
@@ -260,7 +266,7 @@ __global__ void __launch_bounds__(RW * 32) render_bwd_kernel(
                                     const float G = expf(power);
                                     const float alpha = fminf(ALPHA_MAX, cmul(c.x, G));
                                     if (alpha >= ALPHA_MIN) {
-                                        const float ra = __frcp_rn(1.0f - alpha);
+                                        const float ra = fast_rcp(1.0f - alpha);
                                         const float Ti = T[s] * ra;
                                         T[s] = Ti;
                                         const float cg = c.y * g0[s] + c.z * g1[s] + c.w * g2[s];
@@ -280,23 +286,28 @@ __global__ void __launch_bounds__(RW * 32) render_bwd_kernel(
                     }
                 }
                 if (__any_sync(FULL, any)) {
-                    m0 = warp_sum(m0); mx = warp_sum(mx); my = warp_sum(my);
-                    mxx = warp_sum(mxx); mxy = warp_sum(mxy); myy = warp_sum(myy);
-                    c0 = warp_sum(c0); c1 = warp_sum(c1); c2 = warp_sum(c2);
+                    // per-lane linear maps first (they commute with the sum over lanes), then ONE transposed
+                    // butterfly: 8 values over 32 lanes in 4+2+1+1+1 shuffles; lane L ends up holding the
+                    // warp total of value L >> 2, the ninth value takes a plain butterfly.
                     const float A = -2.0f * b.x, B = b.y, C = -2.0f * b.z;
-                    float v;
-                    switch (lane) {
-                        case 0: v = -(A * mx + B * my); break;
-                        case 1: v = -(C * my + B * mx); break;
-                        case 2: v = -0.5f * mxx; break;
-                        case 3: v = -mxy; break;
-                        case 4: v = -0.5f * myy; break;
-                        case 5: v = m0 / c.x; break;
-                        case 6: v = c0; break;
-                        case 7: v = c1; break;
-                        default: v = c2; break;
-                    }
-                    if (lane < 9) atomicAdd(acc + 12 * (size_t)s_id[warp][j] + lane, v);
+                    const float v0 = -(A * mx + B * my), v1 = -(C * my + B * mx);
+                    const float v2 = -0.5f * mxx, v3 = -mxy, v4 = -0.5f * myy, v5 = m0 * fast_rcp(c.x);
+                    const bool up16 = lane & 16, up8 = lane & 8, up4 = lane & 4;
+                    float w0 = (up16 ? v4 : v0) + __shfl_xor_sync(FULL, up16 ? v0 : v4, 16);
+                    float w1 = (up16 ? v5 : v1) + __shfl_xor_sync(FULL, up16 ? v1 : v5, 16);
+                    float w2 = (up16 ? c0 : v2) + __shfl_xor_sync(FULL, up16 ? v2 : c0, 16);
+                    float w3 = (up16 ? c1 : v3) + __shfl_xor_sync(FULL, up16 ? v3 : c1, 16);
+                    float u0 = (up8 ? w2 : w0) + __shfl_xor_sync(FULL, up8 ? w0 : w2, 8);
+                    float u1 = (up8 ? w3 : w1) + __shfl_xor_sync(FULL, up8 ? w1 : w3, 8);
+                    float t0 = (up4 ? u1 : u0) + __shfl_xor_sync(FULL, up4 ? u0 : u1, 4);
+                    t0 += __shfl_xor_sync(FULL, t0, 2);
+                    t0 += __shfl_xor_sync(FULL, t0, 1);
+                    c2 = warp_sum(c2);
+                    // value index held by lane L: 4*bit4 + 2*bit3 + bit2 -> component slot of acc
+                    //   0: v0 (dpx)  1: v1 (dpy)  2: v2 (dA)  3: v3 (dB)  4: v4 (dC)  5: v5 (do)  6: c0  7: c1
+                    float* dst = acc + 12 * (size_t)s_id[warp][j];
+                    if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), t0);
+                    else if (lane == 1) atomicAdd(dst + 8, c2);
                 }
             }
         }
@@ -311,15 +322,14 @@ cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, 
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
     const int T = gx * gy;
     if (T == 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(iv.counters, 0, 64 * sizeof(unsigned int), s);
-    if (e != cudaSuccess) return e;
+    // iv.counters was zeroed at the start of the forward call
     const int blocks = min((T + RW - 1) / RW, 148 * 8);
     if (out_invdepth)
         render_fwd_kernel<true><<<blocks, RW * 32, 0, s>>>(iv.ranges, bv.vals_sorted, gv.rec, gv.depths, W, H, gx, T, v.bg,
-                                                           out_color, out_invdepth, iv.final_T, iv.n_contrib, iv.counters);
+                                                           out_color, out_invdepth, iv.final_T, iv.n_contrib, iv.counters + CTR_RENDER_FWD);
     else
         render_fwd_kernel<false><<<blocks, RW * 32, 0, s>>>(iv.ranges, bv.vals_sorted, gv.rec, gv.depths, W, H, gx, T, v.bg,
-                                                            out_color, nullptr, iv.final_T, iv.n_contrib, iv.counters);
+                                                            out_color, nullptr, iv.final_T, iv.n_contrib, iv.counters + CTR_RENDER_FWD);
     return cudaGetLastError();
 }
 
@@ -330,11 +340,11 @@ cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
     const int T = gx * gy;
     if (T == 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(iv.counters + 16, 0, sizeof(unsigned int), s);
+    cudaError_t e = cudaMemsetAsync(iv.counters + CTR_RENDER_BWD, 0, sizeof(unsigned int), s);
     if (e != cudaSuccess) return e;
     const int blocks = min((T + RW - 1) / RW, 148 * 8);
     render_bwd_kernel<<<blocks, RW * 32, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, gx, T, v.bg, iv.final_T,
-                                                 iv.n_contrib, dL_dpix, acc, iv.counters + 16);
+                                                 iv.n_contrib, dL_dpix, acc, iv.counters + CTR_RENDER_BWD);
     return cudaGetLastError();
 }
 

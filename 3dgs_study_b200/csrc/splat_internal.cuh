@@ -3,19 +3,29 @@
 // State layout in HBM (all chunks 256-byte aligned inside the caller-allocated opaque buffers):
 //
 //   geometry buffer (per Gaussian, P entries)
-//     depths   f32[P]        view-space z (sort key low word)
+//     depths   f32[P]        view-space z; culled Gaussians hold the bit pattern 0xFFFFFFFF so that the
+//                            same array, read as u32, is the depth-sort key (culled sort last)
 //     rec      float4[3P]    packed 48-byte splat record, gathered by the render kernels:
 //                              rec[3i+0] = (px, py, ex, ey)   pixel centre, half extents of {alpha >= 1/255}
 //                              rec[3i+1] = (hA, B, hC, thr)   hA = -A/2, hC = -C/2 (exact), power threshold
 //                              rec[3i+2] = (o, r, g, b)       effective opacity, colour
-//     tiles    u32[P]        tiles touched
-//     offsets  u32[P]        inclusive scan of tiles
-//     scan_tmp               CUB scan scratch
-//   binning buffer (per (tile, Gaussian) pair, R entries)
-//     keys_unsorted u64[R], keys_sorted u64[R], vals_unsorted u32[R], vals_sorted u32[R], sort_tmp
+//     rect     uint2[P]      tile rectangle (minx | miny << 16, w | h << 16); w*h = tiles touched (0 = culled)
+//     iota     u32[P]        0..P-1 (value input of the depth sort)
+//     depth_sorted u32[P]    sorted depth keys (scratch), order u32[P] Gaussian ids by (depth, id)
+//     offsets  u32[P]        inclusive scan of tiles touched IN DEPTH ORDER
+//     scan_tmp / dsort_tmp   CUB scratch
+//   binning buffer (per (tile, Gaussian) pair, R entries; tile keys are u16 when T <= 65536, else u32)
+//     keys_unsorted[R], keys_sorted[R], vals_unsorted u32[R], vals_sorted u32[R], sort_tmp
 //   image buffer
 //     ranges   int2[T]       [start, end) of each tile in the sorted list
-//     final_T  f32[H*W], n_contrib u32[H*W], counters u32[64] (persistent-kernel work counters)
+//     final_T  f32[H*W], n_contrib u32[H*W], counters u32[64] (work counters; [32..33] = u64 pair count R)
+//
+// Binning order.  The list of every tile must end up sorted by (depth bits, Gaussian id), i.e. exactly
+// the order a stable sort of the 64-bit (tile << 32 | depth) keys emitted in Gaussian order gives.  We
+// get the same order with far less traffic: Gaussians are sorted ONCE by depth (stable, P elements),
+// pairs are emitted in that order with only the tile id as key, and a stable sort on the tile bits
+// (13 bits at 1080p: two 8-bit passes over 6-byte pairs instead of six passes over 12-byte pairs)
+// finishes the job.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -37,30 +47,31 @@ constexpr float THR_MARGIN = 1.0e-3f;
 inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct GeomView {
-    float* depths; float4* rec; uint32_t* tiles; uint32_t* offsets; void* scan_tmp;
-    size_t scan_tmp_bytes; size_t total;
+    float* depths; float4* rec; uint2* rect; uint32_t* iota; uint32_t* depth_sorted; uint32_t* order;
+    uint32_t* offsets; void* scan_tmp; void* dsort_tmp;
+    size_t scan_tmp_bytes; size_t dsort_tmp_bytes; size_t total;
 };
 struct BinView {
-    uint64_t* keys_unsorted; uint64_t* keys_sorted; uint32_t* vals_unsorted; uint32_t* vals_sorted;
-    void* sort_tmp; size_t sort_tmp_bytes; size_t total;
+    void* keys_unsorted; void* keys_sorted; uint32_t* vals_unsorted; uint32_t* vals_sorted;
+    void* sort_tmp; size_t sort_tmp_bytes; size_t total; int key_bytes;
 };
 struct ImgView {
     int2* ranges; float* final_T; uint32_t* n_contrib; unsigned int* counters; size_t total;
 };
 
-size_t scan_temp_bytes(int P);
-size_t sort_temp_bytes(int R, int end_bit);
 GeomView carve_geom(void* base, int P);
-BinView carve_binning(void* base, int R, int end_bit);
+BinView carve_binning(void* base, int R, int num_tiles);
 ImgView carve_image(void* base, int W, int H);
-int sort_end_bit(int W, int H);
+inline int tiles_of(int W, int H) { return ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE); }
+constexpr int CTR_RENDER_FWD = 0, CTR_RENDER_BWD = 16, CTR_PAIRS = 32;   // slots of ImgView::counters
 
 // ---- stage launchers (each enqueues on `s`, returns the launch status) ---------------------------
+// preprocess also accumulates the pair count R into pair_counter (u64, zeroed by the caller)
 cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gaussians& g, GeomView gv,
-                                  int32_t* radii, cudaStream_t s);
-cudaError_t launch_scan(GeomView gv, int P, cudaStream_t s);
-cudaError_t launch_duplicate(GeomView gv, const int32_t* radii, int P, int W, int H, BinView bv, cudaStream_t s);
-cudaError_t launch_sort(BinView bv, int R, int end_bit, cudaStream_t s);
+                                  int32_t* radii, unsigned long long* pair_counter, cudaStream_t s);
+cudaError_t launch_depth_order(GeomView gv, int P, cudaStream_t s);   // depth sort + scan of tiles in that order
+cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, cudaStream_t s);
+cudaError_t launch_tile_sort(BinView bv, int R, int num_tiles, cudaStream_t s);
 cudaError_t launch_ranges(BinView bv, int R, ImgView iv, int W, int H, cudaStream_t s);
 cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, ImgView iv, float* out_color,
                               float* out_invdepth, cudaStream_t s);
@@ -72,6 +83,7 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
                                   GeomView gv, const float* acc, const b200splat_grads& out, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
 cudaError_t launch_export_geom(int P, const int32_t* radii, GeomView gv, const b200splat_state_out& o, cudaStream_t s);
+cudaError_t launch_export_binning(int P, int R, GeomView gv, BinView bv, const b200splat_state_out& o, cudaStream_t s);
 
 // ---- canonical fp32 arithmetic (DESIGN.md "Canonical arithmetic") --------------------------------
 // Every rounding point is an explicit intrinsic, so the compiler can neither contract nor

@@ -27,8 +27,10 @@
  * thread-local error string.
  *
  * Threading / streams: re-entrant; all work is enqueued on `stream` (a cudaStream_t passed as
- * void*).  b200splat_forward performs ONE host synchronisation on `stream` (to learn the number
- * of tile/Gaussian pairs before sizing the binning buffer), like the call it replaces.
+ * void*).  b200splat_forward waits ONCE on the host for the number of tile/Gaussian pairs (needed to
+ * size the binning buffer, like the call it replaces), but it waits on an event recorded right after
+ * the preprocess kernel while the depth sort is already queued behind it, so the device does not idle.
+ * Per host thread the library keeps one pinned 8-byte slot and one event for that hand-off.
  */
 #ifndef B200SPLAT_H
 #define B200SPLAT_H
@@ -40,7 +42,7 @@
 extern "C" {
 #endif
 
-#define B200SPLAT_VERSION 1
+#define B200SPLAT_VERSION 2
 
 #if defined(__GNUC__)
 #define B200SPLAT_API __attribute__((visibility("default")))
@@ -109,9 +111,9 @@ typedef struct b200splat_allocators {
  * synchronisation at the end of the call. */
 typedef struct b200splat_stage_times {
     float preprocess_ms;
-    float scan_ms;
-    float duplicate_ms;
-    float sort_ms;
+    float scan_ms;       /* depth order: stable sort of the Gaussians by depth + scan of tiles touched */
+    float duplicate_ms;  /* duplicateWithKeys (includes any host wait for the pair count)              */
+    float sort_ms;       /* stable sort of the (tile, Gaussian) pairs on the tile bits                 */
     float ranges_ms;
     float render_ms;
     float render_bwd_ms;
@@ -172,10 +174,11 @@ B200SPLAT_API int b200splat_export_state(int32_t P, int32_t width, int32_t heigh
                            const int32_t* radii, const void* geom, const void* binning,
                            const void* image, const b200splat_state_out* out, void* stream);
 
-/* Sizes of the geometry and image buffers for given dimensions (the binning buffer depends on R). */
+/* Sizes of the geometry and image buffers for given dimensions (the binning buffer depends on R and,
+ * through the width of the tile key, on the number of tiles). */
 B200SPLAT_API size_t b200splat_geom_bytes(int32_t P);
 B200SPLAT_API size_t b200splat_image_bytes(int32_t width, int32_t height);
-B200SPLAT_API size_t b200splat_binning_bytes(int32_t num_rendered);
+B200SPLAT_API size_t b200splat_binning_bytes(int32_t num_rendered, int32_t width, int32_t height);
 
 B200SPLAT_API const char* b200splat_last_error(void);
 B200SPLAT_API int b200splat_version(void);
