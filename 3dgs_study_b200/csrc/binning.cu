@@ -123,6 +123,15 @@ ImgView carve_image(void* base, int W, int H) {
     v.final_T = (float*)(b + off); off += align256((N > 0 ? N : 1) * sizeof(float));
     v.n_contrib = (uint32_t*)(b + off); off += align256((N > 0 ? N : 1) * sizeof(uint32_t));
     v.counters = (unsigned int*)(b + off); off += align256(64 * sizeof(unsigned int));
+    const size_t Tn = T > 0 ? T : 1;
+    v.tile_order = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
+    v.tile_len = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
+    v.tile_iota = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
+    v.tile_len_sorted = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
+    v.order_tmp_bytes = 0;
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, v.order_tmp_bytes, (uint32_t*)nullptr, (uint32_t*)nullptr,
+                                              (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Tn, 0, 32);
+    v.order_tmp = (void*)(b + off); off += align256(v.order_tmp_bytes);
     v.total = off;
     return v;
 }
@@ -186,6 +195,14 @@ __global__ void __launch_bounds__(256) identify_tile_ranges_kernel(int R, const 
     if (j == R - 1) ranges[t].y = R;
 }
 
+__global__ void tile_len_kernel(int T, const int2* __restrict__ ranges, uint32_t* __restrict__ len, uint32_t* __restrict__ iota) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= T) return;
+    const int2 r = ranges[t];
+    len[t] = (uint32_t)(r.y - r.x);
+    iota[t] = (uint32_t)t;
+}
+
 template <typename KeyT>
 __global__ void export_keys_kernel(int R, const KeyT* __restrict__ tile_keys, const uint32_t* __restrict__ vals,
                                    const float* __restrict__ depths, uint64_t* __restrict__ out) {
@@ -240,13 +257,24 @@ cudaError_t launch_tile_sort(BinView bv, int R, int num_tiles, cudaStream_t s) {
 
 cudaError_t launch_ranges(BinView bv, int R, ImgView iv, int W, int H, cudaStream_t s) {
     const size_t T = (size_t)tiles_of(W, H);
+    if (T == 0) return cudaSuccess;
     cudaError_t e = cudaMemsetAsync(iv.ranges, 0, T * sizeof(int2), s);
-    if (e != cudaSuccess || R == 0) return e;
-    if (bv.key_bytes == 2)
-        identify_tile_ranges_kernel<uint16_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, iv.ranges);
-    else
-        identify_tile_ranges_kernel<uint32_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, iv.ranges);
-    return cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (R > 0) {
+        if (bv.key_bytes == 2)
+            identify_tile_ranges_kernel<uint16_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, iv.ranges);
+        else
+            identify_tile_ranges_kernel<uint32_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, iv.ranges);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    // longest list first: the render kernels' critical path is their heaviest tile
+    tile_len_kernel<<<((int)T + 255) / 256, 256, 0, s>>>((int)T, iv.ranges, iv.tile_len, iv.tile_iota);
+    size_t bytes = iv.order_tmp_bytes;
+    int bits = 1;
+    while (bits < 32 && ((unsigned)R >> bits) != 0) bits++;
+    return cub::DeviceRadixSort::SortPairsDescending(iv.order_tmp, bytes, iv.tile_len, iv.tile_len_sorted, iv.tile_iota,
+                                                     iv.tile_order, (int)T, 0, bits, s);
 }
 
 // Parity / inspection only: rebuild the 64-bit keys, tiles touched and the index-order offsets.

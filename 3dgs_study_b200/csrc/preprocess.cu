@@ -24,6 +24,7 @@ struct PreParams {
 };
 
 // colour of one Gaussian from its SH row (canonical chain: res = b0*sh0; res = fma(bk, shk, res))
+template <bool GLOBAL = true>
 __device__ __forceinline__ void eval_color_sh(const float* __restrict__ sh_row, int M, int D, float dx, float dy,
                                               float dz, float* rgb, unsigned& clamped) {
     float len = csqrt(cfma(dz, dz, cfma(dy, dy, cmul(dx, dx))));
@@ -39,7 +40,7 @@ __device__ __forceinline__ void eval_color_sh(const float* __restrict__ sh_row, 
 #pragma unroll
         for (int k = 0; k < 12; k++) {
             if (k < nv) {
-                float4 t = __ldg(v + k);
+                float4 t = GLOBAL ? __ldg(v + k) : v[k];
                 f[4 * k] = t.x; f[4 * k + 1] = t.y; f[4 * k + 2] = t.z; f[4 * k + 3] = t.w;
             }
         }
@@ -51,11 +52,11 @@ __device__ __forceinline__ void eval_color_sh(const float* __restrict__ sh_row, 
             }
         }
     } else {
-        r0 = cmul(b[0], __ldg(sh_row)); r1 = cmul(b[0], __ldg(sh_row + 1)); r2 = cmul(b[0], __ldg(sh_row + 2));
+        r0 = cmul(b[0], sh_row[0]); r1 = cmul(b[0], sh_row[1]); r2 = cmul(b[0], sh_row[2]);
         for (int k = 1; k < nb; k++) {
-            r0 = cfma(b[k], __ldg(sh_row + 3 * k), r0);
-            r1 = cfma(b[k], __ldg(sh_row + 3 * k + 1), r1);
-            r2 = cfma(b[k], __ldg(sh_row + 3 * k + 2), r2);
+            r0 = cfma(b[k], sh_row[3 * k], r0);
+            r1 = cfma(b[k], sh_row[3 * k + 1], r1);
+            r2 = cfma(b[k], sh_row[3 * k + 2], r2);
         }
     }
     r0 = cadd(r0, 0.5f); r1 = cadd(r1, 0.5f); r2 = cadd(r2, 0.5f);

@@ -1,0 +1,473 @@
+// render_tiles.cu -- tiled alpha compositing, forward and backward, sm_100a: NW WARPS PER 16x16 TILE.
+//
+// Stands in for the renderCUDA forward / backward stages of _C.rasterize_gaussians(_backward) named
+// by BASELINE.json's north_star: front-to-back blending over 16x16 tiles with the 1/255 alpha cutoff,
+// the 0.99 alpha clamp and the 1e-4 transmittance exit; reverse traversal with warp-level reduction
+// of the per-Gaussian sums before any global atomic.
+//
+// Mapping (DESIGN.md "Render kernels").  One 128-thread block per tile; warp w owns the 16x4 pixel
+// strip of rows 4w..4w+3, and lane l the two pixels (l & 7, l >> 3) and (8 + (l & 7), l >> 3) of it.
+//   * A tile's depth-sorted list is streamed through shared memory 128 packed 48-byte records at a
+//     time (one record per thread, three 16-byte loads, the next batch prefetched into registers).
+//   * Every record carries the bounding box of its {alpha >= 1/255} ellipse; the staging thread
+//     reduces it to a 4-bit strip mask, a ballot turns the masks into one 128-bit "reaches my strip"
+//     bitmap per warp, and each warp walks ONLY the set bits of its bitmap (find-first-set), so
+//     a splat that cannot touch a strip costs that warp nothing.  Results are identical: a skipped
+//     pixel would have failed the exact alpha test.
+//   * Both pixels of a lane are evaluated in straight-line predicated code (two independent chains);
+//     the state per thread is ~12 registers, so ~12 warps per scheduler hide the exp / rcp latency.
+//   * Backward: the per-Gaussian sums of a strip are finished with ONE transposed butterfly
+//     (8 values over 32 lanes in 4+2+1+1+1 shuffles) and nine red.global.add per (strip, Gaussian)
+//     instead of nine atomics per pixel.
+// The critical path of the kernel is one tile's list divided over four warps; tiles are issued
+// longest list first (tile_order) so the heavy ones do not start last.
+#include "splat_internal.cuh"
+
+namespace b200splat {
+
+namespace {
+
+#ifndef FWD_NW
+#define FWD_NW 2                       // warps per tile, forward   (strip = 16 x 16/NW pixels)
+#endif
+#ifndef BWD_NW
+#define BWD_NW 2                       // warps per tile, backward
+#endif
+constexpr unsigned FULL = 0xffffffffu;
+
+// NW-bit mask of the 16 x (16/NW) strips the box (rx +- ex, ry +- ey), tile-relative, can reach
+template <int NW>
+__device__ __forceinline__ unsigned strip_mask(float rx, float ry, float ex, float ey) {
+    if (!(ex >= 0.0f)) return 0u;
+    const float lox = rx - ex, hix = rx + ex, loy = ry - ey, hiy = ry + ey;
+    if (!(lox <= 15.0f && hix >= 0.0f)) return 0u;
+    constexpr int RH = 16 / NW;
+    unsigned m = 0;
+#pragma unroll
+    for (int g = 0; g < NW; g++)
+        m |= (loy <= (float)(g * RH + RH - 1) && hiy >= (float)(g * RH)) ? (1u << g) : 0u;
+    return m;
+}
+
+// Pixel slots of a lane.  NW <= 4: lane -> (lane & 7, lane >> 3) inside an 8x4 cell, slot k -> cell (k & 1, k >> 1)
+// of the strip; NW == 8: the strip is 16x2 and a lane owns the single pixel (lane & 15, lane >> 4).
+template <int NW> struct Layout {
+    static constexpr int NP = 8 / NW;            // pixels per thread
+    static constexpr int NY = NP > 1 ? NP / 2 : 1;   // distinct rows per thread
+    static constexpr int NX = NP > 1 ? 2 : 1;
+    static constexpr int RH = 16 / NW;
+    __device__ static __forceinline__ int x(int lane, int kx) { return NW == 8 ? (lane & 15) : (lane & 7) + 8 * kx; }
+    __device__ static __forceinline__ int y(int lane, int warp, int ky) {
+        return NW == 8 ? 2 * warp + (lane >> 4) : RH * warp + (lane >> 3) + 4 * ky;
+    }
+};
+
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+    v += __shfl_xor_sync(FULL, v, 16);
+    v += __shfl_xor_sync(FULL, v, 8);
+    v += __shfl_xor_sync(FULL, v, 4);
+    v += __shfl_xor_sync(FULL, v, 2);
+    v += __shfl_xor_sync(FULL, v, 1);
+    return v;
+}
+
+
+template <int NW, bool DEPTH>
+__global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
+    const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
+    const float* __restrict__ depths, int W, int H, int gx, const uint32_t* __restrict__ tile_order,
+    const float* __restrict__ bg, float* __restrict__ out_color, float* __restrict__ out_invdepth,
+    float* __restrict__ final_T, uint32_t* __restrict__ n_contrib) {
+    using L = Layout<NW>;
+    constexpr int TB = NW * 32, NX = L::NX, NY = L::NY, NP = L::NP;
+    __shared__ float4 s_rec[TB * 3];
+    __shared__ float s_invd[DEPTH ? TB : 1];
+    __shared__ unsigned s_bits[NW][NW];          // [consumer strip][staging warp]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = tile_order ? (int)__ldg(tile_order + blockIdx.x) : (int)blockIdx.x;
+    const int2 range = __ldg(ranges + tile);
+    const int n = range.y - range.x;
+    const int ox = (tile % gx) * TILE, oy = (tile / gx) * TILE;
+    const float fox = (float)ox, foy = (float)oy;
+    int pxi[NX], pyi[NY];
+    float pxf[NX], pyf[NY];
+#pragma unroll
+    for (int k = 0; k < NX; k++) { pxi[k] = ox + L::x(lane, k); pxf[k] = (float)pxi[k]; }
+#pragma unroll
+    for (int k = 0; k < NY; k++) { pyi[k] = oy + L::y(lane, warp, k); pyf[k] = (float)pyi[k]; }
+    float T[NP], C0[NP], C1[NP], C2[NP], Dp[NP];
+    uint32_t last[NP];
+    bool any_in = false;
+#pragma unroll
+    for (int s = 0; s < NP; s++) {
+        const bool inside = pxi[s % NX] < W && pyi[s / NX] < H;
+        T[s] = inside ? 1.0f : -1.0f;                 // T < 0: pixel finished, |T| is final
+        C0[s] = 0.f; C1[s] = 0.f; C2[s] = 0.f; Dp[s] = 0.f; last[s] = 0;
+        any_in |= inside;
+    }
+    bool warp_live = __any_sync(FULL, any_in);
+
+    float4 ra = make_float4(0.f, 0.f, -1.f, -1.f), rb = ra, rc = ra;
+    float rinvd = 0.f;
+    if (tid < n) {
+        const uint32_t id = __ldg(point_list + range.x + tid);
+        ra = __ldg(rec + 3 * (size_t)id); rb = __ldg(rec + 3 * (size_t)id + 1); rc = __ldg(rec + 3 * (size_t)id + 2);
+        if (DEPTH) rinvd = __frcp_rn(__ldg(depths + id));
+    }
+    for (int base = 0; base < n; base += TB) {
+        // all strips finished -> the rest of the list cannot change anything
+        if (__syncthreads_and(!warp_live)) break;
+        s_rec[tid * 3 + 0] = ra; s_rec[tid * 3 + 1] = rb; s_rec[tid * 3 + 2] = rc;
+        if (DEPTH) s_invd[tid] = rinvd;
+        const unsigned m = (base + tid < n) ? strip_mask<NW>(ra.x - fox, ra.y - foy, ra.z, ra.w) : 0u;
+#pragma unroll
+        for (int g = 0; g < NW; g++) {
+            const unsigned bits = __ballot_sync(FULL, (m >> g) & 1u);
+            if (lane == 0) s_bits[g][warp] = bits;
+        }
+        __syncthreads();
+        {   // prefetch the next batch while this one is consumed
+            const int nidx = base + TB + tid;
+            if (nidx < n) {
+                const uint32_t id = __ldg(point_list + range.x + nidx);
+                ra = __ldg(rec + 3 * (size_t)id); rb = __ldg(rec + 3 * (size_t)id + 1); rc = __ldg(rec + 3 * (size_t)id + 2);
+                if (DEPTH) rinvd = __frcp_rn(__ldg(depths + id));
+            }
+        }
+        if (warp_live) {
+#pragma unroll 1
+            for (int sw = 0; sw < NW; sw++) {
+                unsigned bits = s_bits[warp][sw];
+                while (bits) {
+                    const int j = sw * 32 + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const float4 a = s_rec[3 * j], b = s_rec[3 * j + 1], c = s_rec[3 * j + 2];
+                    float dx[NX], pw[NP];
+                    bool ok[NP], any_ok = false;
+#pragma unroll
+                    for (int k = 0; k < NX; k++) dx[k] = csub(a.x, pxf[k]);
+#pragma unroll
+                    for (int ky = 0; ky < NY; ky++) {
+                        const float dy = csub(a.y, pyf[ky]);
+                        const float bdy = cmul(b.y, dy);
+                        const float t2 = cmul(cmul(b.z, dy), dy);
+#pragma unroll
+                        for (int kx = 0; kx < NX; kx++) {
+                            const float p = cfma(dx[kx], cfma(b.x, dx[kx], -bdy), t2);
+                            pw[ky * NX + kx] = p;
+                            ok[ky * NX + kx] = p <= 0.0f && p >= b.w;
+                            any_ok |= ok[ky * NX + kx];
+                        }
+                    }
+                    if (!__any_sync(FULL, any_ok)) continue;
+                    const uint32_t contributor = (uint32_t)(base + j + 1);
+                    const float invd = DEPTH ? s_invd[j] : 0.f;
+#pragma unroll
+                    for (int s = 0; s < NP; s++) {
+                        const float e = fminf(ALPHA_MAX, cmul(c.x, expf(pw[s])));
+                        const float alpha = ok[s] ? e : 0.0f;
+                        const float test_T = cmul(T[s], csub(1.0f, alpha));
+                        const bool valid = alpha >= ALPHA_MIN;
+                        const bool blend = valid && !(test_T < T_EPS);
+                        const float w = cmul(alpha, T[s]);
+                        C0[s] = blend ? cfma(c.y, w, C0[s]) : C0[s];
+                        C1[s] = blend ? cfma(c.z, w, C1[s]) : C1[s];
+                        C2[s] = blend ? cfma(c.w, w, C2[s]) : C2[s];
+                        if (DEPTH) Dp[s] = blend ? cfma(invd, w, Dp[s]) : Dp[s];
+                        T[s] = blend ? test_T : (valid ? -fabsf(T[s]) : T[s]);
+                        last[s] = blend ? contributor : last[s];
+                    }
+                }
+            }
+            bool live = false;
+#pragma unroll
+            for (int s = 0; s < NP; s++) live |= T[s] > 0.0f;
+            warp_live = __any_sync(FULL, live);
+        }
+    }
+    const float bg0 = __ldg(bg), bg1 = __ldg(bg + 1), bg2 = __ldg(bg + 2);
+    const size_t HW = (size_t)H * W;
+#pragma unroll
+    for (int s = 0; s < NP; s++) {
+        const int px = pxi[s % NX], py = pyi[s / NX];
+        if (px < W && py < H) {
+            const size_t pix = (size_t)py * W + px;
+            const float Tf = fabsf(T[s]);
+            final_T[pix] = Tf;
+            n_contrib[pix] = last[s];
+            out_color[pix] = cfma(Tf, bg0, C0[s]);
+            out_color[HW + pix] = cfma(Tf, bg1, C1[s]);
+            out_color[2 * HW + pix] = cfma(Tf, bg2, C2[s]);
+            if (DEPTH) out_invdepth[pix] = Dp[s];
+        }
+    }
+}
+
+// Backward: reverse traversal.  Per pixel the running state is (T_i, S_i) with
+//   S_i = sum_{j behind i} T_j alpha_j (c_j . g) + T_final (bg . g),   g = dL/dC(pixel)
+//   dL/dalpha_i = T_i (c_i . g) - S_i / (1 - alpha_i)
+// and per (strip, Gaussian) the pixel sums are the moments of z = G * o * dL/dalpha:
+//   m0 = sum z, mx = sum z dx, my = sum z dy, mxx = sum z dx^2, mxy = sum z dx dy, myy = sum z dy^2
+//   dL/dpx = -(A mx + B my), dL/dpy = -(C my + B mx), dL/dA = -mxx/2, dL/dB = -mxy, dL/dC = -myy/2,
+//   dL/do = m0 / o, dL/dcolour = sum alpha T g.
+template <int NW>
+__global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
+    const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
+    int W, int H, int gx, const uint32_t* __restrict__ tile_order, const float* __restrict__ bg,
+    const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
+    float* __restrict__ acc) {
+    using L = Layout<NW>;
+    constexpr int TB = NW * 32, NX = L::NX, NY = L::NY, NP = L::NP;
+    __shared__ float4 s_rec[TB * 3];
+    __shared__ uint32_t s_id[TB];
+    __shared__ unsigned s_bits[NW][NW];
+    __shared__ int s_wmax[NW];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = tile_order ? (int)__ldg(tile_order + blockIdx.x) : (int)blockIdx.x;
+    const int2 range = __ldg(ranges + tile);
+    const int ox = (tile % gx) * TILE, oy = (tile / gx) * TILE;
+    const float fox = (float)ox, foy = (float)oy;
+    const float bg0 = __ldg(bg), bg1 = __ldg(bg + 1), bg2 = __ldg(bg + 2);
+    const size_t HW = (size_t)H * W;
+    float pxf[NX], pyf[NY];
+#pragma unroll
+    for (int k = 0; k < NX; k++) pxf[k] = (float)(ox + L::x(lane, k));
+#pragma unroll
+    for (int k = 0; k < NY; k++) pyf[k] = (float)(oy + L::y(lane, warp, k));
+    float T[NP], S[NP], g0[NP], g1[NP], g2[NP];
+    int last[NP];
+    int lmax = 0;
+#pragma unroll
+    for (int s = 0; s < NP; s++) {
+        const int px = ox + L::x(lane, s % NX), py = oy + L::y(lane, warp, s / NX);
+        T[s] = 1.f; S[s] = 0.f; g0[s] = 0.f; g1[s] = 0.f; g2[s] = 0.f; last[s] = 0;
+        if (px < W && py < H) {
+            const size_t pix = (size_t)py * W + px;
+            T[s] = __ldg(final_T + pix);
+            last[s] = (int)__ldg(n_contrib + pix);
+            g0[s] = __ldg(dL_dpix + pix); g1[s] = __ldg(dL_dpix + HW + pix); g2[s] = __ldg(dL_dpix + 2 * HW + pix);
+            S[s] = T[s] * (bg0 * g0[s] + bg1 * g1[s] + bg2 * g2[s]);
+        }
+        lmax = max(lmax, last[s]);
+    }
+    const int wmax = __reduce_max_sync(FULL, lmax);   // deepest contributor of this strip
+    if (lane == 0) s_wmax[warp] = wmax;
+    __syncthreads();
+    int maxc = 0;
+#pragma unroll
+    for (int g = 0; g < NW; g++) maxc = max(maxc, s_wmax[g]);
+    const bool up16 = lane & 16, up8 = lane & 8, up4 = lane & 4;
+
+    float4 ra = make_float4(0.f, 0.f, -1.f, -1.f), rb = ra, rc = ra;
+    uint32_t rid = 0;
+    {
+        const int idx = max(0, maxc - TB) + tid;
+        if (idx < maxc) {
+            rid = __ldg(point_list + range.x + idx);
+            ra = __ldg(rec + 3 * (size_t)rid); rb = __ldg(rec + 3 * (size_t)rid + 1); rc = __ldg(rec + 3 * (size_t)rid + 2);
+        }
+    }
+    for (int hi = maxc; hi > 0; hi -= TB) {
+        const int lo = max(0, hi - TB);
+        const int cnt = hi - lo;
+        __syncthreads();                         // previous batch fully consumed
+        s_rec[tid * 3 + 0] = ra; s_rec[tid * 3 + 1] = rb; s_rec[tid * 3 + 2] = rc;
+        s_id[tid] = rid;
+        const unsigned m = tid < cnt ? strip_mask<NW>(ra.x - fox, ra.y - foy, ra.z, ra.w) : 0u;
+#pragma unroll
+        for (int g = 0; g < NW; g++) {
+            const unsigned bits = __ballot_sync(FULL, (m >> g) & 1u);
+            if (lane == 0) s_bits[g][warp] = bits;
+        }
+        __syncthreads();
+        {   // prefetch the next (shallower) batch
+            const int nhi = lo, nlo = max(0, nhi - TB);
+            const int idx = nlo + tid;
+            if (idx < nhi) {
+                rid = __ldg(point_list + range.x + idx);
+                ra = __ldg(rec + 3 * (size_t)rid); rb = __ldg(rec + 3 * (size_t)rid + 1); rc = __ldg(rec + 3 * (size_t)rid + 2);
+            }
+        }
+        if (lo >= wmax) continue;                // this batch lies entirely behind this strip's deepest contributor
+#pragma unroll 1
+        for (int sw = NW - 1; sw >= 0; sw--) {
+            unsigned bits = s_bits[warp][sw];
+            const int wlo = lo + sw * 32;
+            if (wlo >= wmax) continue;
+            if (wmax - wlo < 32) bits &= (1u << (wmax - wlo)) - 1u;
+            while (bits) {
+                const int jb = 31 - __clz(bits);
+                bits ^= 1u << jb;
+                const int j = sw * 32 + jb;
+                const int pos = lo + j;
+                const float4 a = s_rec[3 * j], b = s_rec[3 * j + 1], c = s_rec[3 * j + 2];
+                float dx[NX], dyv[NY], pw[NP];
+                bool ok[NP], any_ok = false;
+#pragma unroll
+                for (int k = 0; k < NX; k++) dx[k] = csub(a.x, pxf[k]);
+#pragma unroll
+                for (int ky = 0; ky < NY; ky++) {
+                    const float dy = csub(a.y, pyf[ky]);
+                    dyv[ky] = dy;
+                    const float bdy = cmul(b.y, dy);
+                    const float t2 = cmul(cmul(b.z, dy), dy);
+#pragma unroll
+                    for (int kx = 0; kx < NX; kx++) {
+                        const int s = ky * NX + kx;
+                        const float p = cfma(dx[kx], cfma(b.x, dx[kx], -bdy), t2);
+                        pw[s] = p;
+                        ok[s] = p <= 0.0f && p >= b.w && pos < last[s];
+                        any_ok |= ok[s];
+                    }
+                }
+                if (!__any_sync(FULL, any_ok)) continue;
+                float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
+                bool any_valid = false;
+#pragma unroll
+                for (int s = 0; s < NP; s++) {
+                    const float G = expf(pw[s]);
+                    const float alpha = fminf(ALPHA_MAX, cmul(c.x, G));
+                    const bool valid = ok[s] && alpha >= ALPHA_MIN;
+                    const float r = fast_rcp(1.0f - alpha);
+                    const float Ti = T[s] * r;
+                    const float cg = c.y * g0[s] + c.z * g1[s] + c.w * g2[s];
+                    const float w = valid ? alpha * Ti : 0.0f;
+                    const float dLda = Ti * cg - S[s] * r;
+                    const float z = valid ? G * c.x * dLda : 0.0f;
+                    T[s] = valid ? Ti : T[s];
+                    S[s] = fmaf(w, cg, S[s]);
+                    c0 = fmaf(w, g0[s], c0); c1 = fmaf(w, g1[s], c1); c2 = fmaf(w, g2[s], c2);
+                    const float ddx = dx[s % NX], ddy = dyv[s / NX];
+                    const float zx = z * ddx, zy = z * ddy;
+                    m0 += z; mx += zx; my += zy;
+                    mxx = fmaf(zx, ddx, mxx); mxy = fmaf(zx, ddy, mxy); myy = fmaf(zy, ddy, myy);
+                    any_valid |= valid;
+                }
+                if (!__any_sync(FULL, any_valid)) continue;
+                // per-lane linear maps first (they commute with the sum over lanes), then ONE transposed
+                // butterfly; lane L ends up holding the strip total of value L >> 2, the ninth value takes
+                // a plain butterfly.
+                const float A = -2.0f * b.x, B = b.y, C = -2.0f * b.z;
+                const float q0 = -(A * mx + B * my), q1 = -(C * my + B * mx);
+                const float q2 = -0.5f * mxx, q3 = -mxy, q4 = -0.5f * myy, q5 = m0 * fast_rcp(c.x);
+                float w0 = (up16 ? q4 : q0) + __shfl_xor_sync(FULL, up16 ? q0 : q4, 16);
+                float w1 = (up16 ? q5 : q1) + __shfl_xor_sync(FULL, up16 ? q1 : q5, 16);
+                float w2 = (up16 ? c0 : q2) + __shfl_xor_sync(FULL, up16 ? q2 : c0, 16);
+                float w3 = (up16 ? c1 : q3) + __shfl_xor_sync(FULL, up16 ? q3 : c1, 16);
+                float u0 = (up8 ? w2 : w0) + __shfl_xor_sync(FULL, up8 ? w0 : w2, 8);
+                float u1 = (up8 ? w3 : w1) + __shfl_xor_sync(FULL, up8 ? w1 : w3, 8);
+                float t0 = (up4 ? u1 : u0) + __shfl_xor_sync(FULL, up4 ? u0 : u1, 4);
+                t0 += __shfl_xor_sync(FULL, t0, 2);
+                t0 += __shfl_xor_sync(FULL, t0, 1);
+                c2 = warp_sum(c2);
+                // component slot of acc held by lane L (L & 3 == 0): L >> 2 ->
+                //   0 dpx  1 dpy  2 dA  3 dB  4 dC  5 do  6 dr  7 dg ; slot 8 (db) from lane 1
+                float* dst = acc + 12 * (size_t)s_id[j];
+                if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), t0);
+                else if (lane == 1) atomicAdd(dst + 8, c2);
+            }
+        }
+    }
+}
+
+// Inspection only (b200splat_render_stats): workload counters of the render stage of one view, used for
+// the FP32-issue roofline -- not on the hot path.  One block per tile, one thread per pixel.
+//   out[0..4]  pairs by number of 16x4 strips their {alpha >= 1/255} box reaches (0 = skipped outright)
+//   out[9]     pairs visited (list positions below the tile's deepest contributor)
+//   out[10]    pixel evaluations (pixels of reached strips, position below the pixel's last contributor)
+//   out[11]    of those, power inside [thr, 0] (an exp is executed)
+//   out[12]    of those, alpha >= 1/255 (a blend / a gradient contribution)
+//   out[13]    (strip, Gaussian) pairs with at least one contribution (one reduction + nine red.global)
+__global__ void __launch_bounds__(256) render_stats_kernel(const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                                                           const float4* __restrict__ rec, int W, int H, int gx,
+                                                           const uint32_t* __restrict__ n_contrib,
+                                                           unsigned long long* __restrict__ out) {
+    __shared__ int s_max;
+    __shared__ unsigned long long s_cnt[14];
+    __shared__ int s_strip[4];
+    const int tile = blockIdx.x, t = threadIdx.x;
+    const int ox = (tile % gx) * TILE, oy = (tile / gx) * TILE;
+    const int px = ox + (t & 15), py = oy + (t >> 4);
+    const bool inside = px < W && py < H;
+    const int last = inside ? (int)n_contrib[(size_t)py * W + px] : 0;
+    if (t == 0) s_max = 0;
+    if (t < 14) s_cnt[t] = 0ull;
+    __syncthreads();
+    atomicMax(&s_max, last);
+    __syncthreads();
+    const int2 range = ranges[tile];
+    const int n = min(range.y - range.x, s_max);
+    const int strip = t >> 6;                     // rows 4*strip .. 4*strip+3
+    unsigned long long ev = 0, ex = 0, co = 0;
+    for (int j = 0; j < n; j++) {
+        const uint32_t id = point_list[range.x + j];
+        const float4 a = rec[3 * (size_t)id], b = rec[3 * (size_t)id + 1], c = rec[3 * (size_t)id + 2];
+        const unsigned m = strip_mask<4>(a.x - (float)ox, a.y - (float)oy, a.z, a.w);
+        bool contrib = false;
+        if (t < 4) s_strip[t] = 0;
+        __syncthreads();
+        if (((m >> strip) & 1u) && j < last) {
+            ev++;
+            const float dx = csub(a.x, (float)px), dy = csub(a.y, (float)py);
+            const float power = cfma(dx, cfma(b.x, dx, -cmul(b.y, dy)), cmul(cmul(b.z, dy), dy));
+            if (power <= 0.0f && power >= b.w) {
+                ex++;
+                if (fminf(ALPHA_MAX, cmul(c.x, expf(power))) >= ALPHA_MIN) { co++; contrib = true; }
+            }
+        }
+        if (contrib) s_strip[strip] = 1;
+        __syncthreads();
+        if (t == 0) { s_cnt[__popc(m)]++; s_cnt[9]++; s_cnt[13] += s_strip[0] + s_strip[1] + s_strip[2] + s_strip[3]; }
+        __syncthreads();
+    }
+    atomicAdd(&s_cnt[10], ev); atomicAdd(&s_cnt[11], ex); atomicAdd(&s_cnt[12], co);
+    __syncthreads();
+    if (t < 14 && s_cnt[t]) atomicAdd(out + t, s_cnt[t]);
+}
+
+}  // namespace
+
+cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, ImgView iv, float* out_color,
+                              float* out_invdepth, cudaStream_t s) {
+    const int W = v.image_width, H = v.image_height;
+    const int gx = (W + TILE - 1) / TILE;
+    const int T = tiles_of(W, H);
+    if (T == 0) return cudaSuccess;
+    if (out_invdepth)
+        render_fwd_kernel<FWD_NW, true><<<T, FWD_NW * 32, 0, s>>>(iv.ranges, bv.vals_sorted, gv.rec, gv.depths, W, H, gx, iv.tile_order, v.bg,
+                                                 out_color, out_invdepth, iv.final_T, iv.n_contrib);
+    else
+        render_fwd_kernel<FWD_NW, false><<<T, FWD_NW * 32, 0, s>>>(iv.ranges, bv.vals_sorted, gv.rec, gv.depths, W, H, gx, iv.tile_order, v.bg,
+                                                  out_color, nullptr, iv.final_T, iv.n_contrib);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
+                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
+    (void)dL_dinvdepth;
+    const int W = v.image_width, H = v.image_height;
+    const int gx = (W + TILE - 1) / TILE;
+    const int T = tiles_of(W, H);
+    if (T == 0) return cudaSuccess;
+    render_bwd_kernel<BWD_NW><<<T, BWD_NW * 32, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, gx, iv.tile_order, v.bg, iv.final_T,
+                                       iv.n_contrib, dL_dpix, acc);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
+                                unsigned long long* out14, cudaStream_t s) {
+    const int gx = (W + TILE - 1) / TILE;
+    const int T = tiles_of(W, H);
+    cudaError_t e = cudaMemsetAsync(out14, 0, 14 * sizeof(unsigned long long), s);
+    if (e != cudaSuccess || T == 0) return e;
+    render_stats_kernel<<<T, 256, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, gx, iv.n_contrib, out14);
+    return cudaGetLastError();
+}
+
+}  // namespace b200splat

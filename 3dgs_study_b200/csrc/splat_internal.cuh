@@ -56,7 +56,10 @@ struct BinView {
     void* sort_tmp; size_t sort_tmp_bytes; size_t total; int key_bytes;
 };
 struct ImgView {
-    int2* ranges; float* final_T; uint32_t* n_contrib; unsigned int* counters; size_t total;
+    int2* ranges; float* final_T; uint32_t* n_contrib; unsigned int* counters;
+    uint32_t* tile_order;       // tiles by decreasing list length (NULL: index order)
+    uint32_t* tile_len; uint32_t* tile_iota; uint32_t* tile_len_sorted; void* order_tmp; size_t order_tmp_bytes;
+    size_t total;
 };
 
 GeomView carve_geom(void* base, int P);
@@ -81,6 +84,8 @@ cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32
                               const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s);
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
                                   GeomView gv, const float* acc, const b200splat_grads& out, cudaStream_t s);
+cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
+                                unsigned long long* out14, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
 cudaError_t launch_export_geom(int P, const int32_t* radii, GeomView gv, const b200splat_state_out& o, cudaStream_t s);
 cudaError_t launch_export_binning(int P, int R, GeomView gv, BinView bv, const b200splat_state_out& o, cudaStream_t s);

@@ -18,7 +18,8 @@ from typing import Optional, Tuple
 import torch
 
 _PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(_PKG_DIR, "libb200splat.so")
+# B200SPLAT_LIB selects another build of the same library (kernel-variant experiments); never a fallback
+LIB_PATH = os.environ.get("B200SPLAT_LIB") or os.path.join(_PKG_DIR, "libb200splat.so")
 
 _alloc_fn_t = ctypes.CFUNCTYPE(ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t)
 
@@ -100,6 +101,10 @@ def lib():
         L.b200splat_mark_visible.restype = ctypes.c_int
         L.b200splat_mark_visible.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_render_stats.restype = ctypes.c_int
+        L.b200splat_render_stats.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
+                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_void_p]
         L.b200splat_export_state.restype = ctypes.c_int
         L.b200splat_export_state.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -279,6 +284,19 @@ def mark_visible(means3D, viewmatrix, projmatrix):
                                           _stream_ptr(dev))
     _check(rc, "mark_visible")
     return present
+
+
+def render_stats(P, W, H, num_rendered, geomBuffer, binningBuffer, imageBuffer):
+    """Inspection: workload counters of the render stage (see b200splat_render_stats in the header)."""
+    dev = geomBuffer.device
+    out = torch.zeros(14, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_render_stats(int(P), int(W), int(H), int(num_rendered), _ptr(geomBuffer), _ptr(binningBuffer),
+                                          _ptr(imageBuffer), _ptr(out), _stream_ptr(dev))
+    _check(rc, "render_stats")
+    v = [int(x) for x in out.cpu().tolist()]
+    return {"pairs_by_subblocks": v[0:9], "pairs_visited": v[9], "pixel_evals": v[10], "exp_evals": v[11],
+            "contributions": v[12], "pairs_contributing": v[13]}
 
 
 def export_state(P, W, H, num_rendered, radii, geomBuffer, binningBuffer, imageBuffer):

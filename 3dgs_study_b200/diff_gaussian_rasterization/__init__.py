@@ -53,15 +53,19 @@ def cpu_deep_copy_tuple(input_tuple):
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                        raster_settings):
+                        raster_settings, want_invdepth: Optional[bool] = None):
+    """-> (color, radii, invdepth).  `want_invdepth=False` (the default in LEGACY_OUTPUTS mode, i.e. for the
+    reference's own two-output call site) skips the inverse-depth channel: invdepth is then None."""
+    if want_invdepth is None:
+        want_invdepth = not LEGACY_OUTPUTS
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings)
+                                     cov3Ds_precomp, raster_settings, bool(want_invdepth))
 
 
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                raster_settings):
+                raster_settings, want_invdepth=True):
         rs = raster_settings
         args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
@@ -70,20 +74,23 @@ class _RasterizeGaussians(torch.autograd.Function):
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args)  # copy first: a failing kernel may corrupt them
             try:
-                res = _C.rasterize_gaussians(*args, antialiasing=aa, want_invdepth=True)
+                res = _C.rasterize_gaussians(*args, antialiasing=aa, want_invdepth=want_invdepth)
             except Exception as ex:
                 torch.save(cpu_args, "snapshot_fw.dump")
                 print("\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.")
                 raise ex
         else:
-            res = _C.rasterize_gaussians(*args, antialiasing=aa, want_invdepth=True)
+            res = _C.rasterize_gaussians(*args, antialiasing=aa, want_invdepth=want_invdepth)
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, invdepth = res
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
         ctx.has_means2D = means2D is not None
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
                               geomBuffer, binningBuffer, imgBuffer)
-        ctx.mark_non_differentiable(radii, invdepth)
+        if invdepth is None:
+            ctx.mark_non_differentiable(radii)
+        else:
+            ctx.mark_non_differentiable(radii, invdepth)
         return color, radii, invdepth
 
     @staticmethod
@@ -111,7 +118,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             g_opac = g_opac.reshape(opacities.shape)
         if not ctx.has_means2D:
             g_means2D = None
-        return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None)
+        return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, None)
 
 
 class GaussianRasterizer(nn.Module):

@@ -65,8 +65,10 @@ class ViewParallelStep:
                                                self.scale_modifier, cam.world_view_transform, cam.full_proj_transform,
                                                self.sh_degree, cam.camera_center, False, False)
         lv = self.leaves
+        # the training step consumes (color, radii) only, like the reference's call site
+        # (/root/reference/gaussian_renderer/__init__.py:98): the inverse-depth channel is not requested
         color, radii, _ = dgr.rasterize_gaussians(lv.means3D, means2D, lv.shs, None, lv.opacities, lv.scales,
-                                                  lv.rotations, None, rs)
+                                                  lv.rotations, None, rs, want_invdepth=False)
         return color, radii
 
     # -- one step -------------------------------------------------------------------------------------
