@@ -14,6 +14,9 @@ namespace {
 
 constexpr int PRE_THREADS = 256;
 
+// row stride (floats) of an SH row staged in shared memory: an odd number of 16-byte words
+__device__ __forceinline__ int sh_row_stride(int M3) { return ((M3 >> 2) & 1) ? M3 : M3 + 4; }
+
 struct PreParams {
     int P, D, M, W, H, gx, gy;
     float tanfovx, tanfovy, focal_x, focal_y, mod;
@@ -103,7 +106,9 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
                                                                      uint2* __restrict__ rect,
                                                                      uint32_t* __restrict__ iota,
                                                                      int32_t* __restrict__ radii,
-                                                                     unsigned long long* __restrict__ pair_counter) {
+                                                                     unsigned long long* __restrict__ pair_counter,
+                                                                     int coop) {
+    extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
     __shared__ uint32_t s_pairs[PRE_THREADS / 32];
     load_view_consts(vc, p.view, p.proj, p.campos);
@@ -117,6 +122,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
     }
     int radius = 0;
     uint32_t area = 0;
+    float o_eff = 0.f;
     uint2 rc = make_uint2(0u, 0u);
     if (in_range && tz > NEAR_Z) {
         const float tx = cadd(cfma(vc.view[8], z, cfma(vc.view[4], y, cmul(vc.view[0], x))), vc.view[12]);
@@ -159,15 +165,6 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
             get_rect(px, py, rad, p.gx, p.gy, minx, miny, maxx, maxy);
             const int ar = (maxx - minx) * (maxy - miny);
             if (ar != 0) {
-                float rgb[3];
-                if (p.colors_precomp) {
-                    rgb[0] = __ldg(p.colors_precomp + 3 * i); rgb[1] = __ldg(p.colors_precomp + 3 * i + 1);
-                    rgb[2] = __ldg(p.colors_precomp + 3 * i + 2);
-                } else {
-                    unsigned cl;
-                    eval_color_sh(p.shs + (size_t)i * p.M * 3, p.M, p.D, csub(x, vc.campos[0]), csub(y, vc.campos[1]),
-                                  csub(z, vc.campos[2]), rgb, cl);
-                }
                 const float o = cmul(__ldg(p.opacities + i), hconv);
                 // conservative early-out data for the render kernels (not part of the canonical result):
                 //   thr: power below which o*exp(power) is certainly < 1/255
@@ -184,11 +181,42 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
                 rc = make_uint2((uint32_t)minx | ((uint32_t)miny << 16), (uint32_t)(maxx - minx) | ((uint32_t)(maxy - miny) << 16));
                 rec[3 * (size_t)i + 0] = make_float4(px, py, ex, ey);
                 rec[3 * (size_t)i + 1] = make_float4(cmul(-0.5f, conA), conB, cmul(-0.5f, conC), thr);
-                rec[3 * (size_t)i + 2] = make_float4(o, rgb[0], rgb[1], rgb[2]);
+                o_eff = o;
                 radius = rad;
                 area = (uint32_t)ar;
             }
         }
+    }
+    // ---- colour (after the cull, so the 12*M-byte SH row of a culled Gaussian is never touched) ----
+    if (coop) {   // coalesced load of the warp's visible rows into shared memory (see preprocess_bwd_kernel)
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const int M3 = 3 * p.M, nq = M3 >> 2, RS4 = sh_row_stride(M3) >> 2;
+        float4* wrows = s_sh4 + (size_t)warp * 32 * RS4;
+        const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
+        const unsigned vmask = __ballot_sync(0xffffffffu, area != 0);
+        const float4* src = reinterpret_cast<const float4*>(p.shs) + (size_t)i0 * nq;
+        for (int c = lane; c < 32 * nq; c += 32) {
+            const int row = c / nq, q = c - row * nq;
+            if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + c);
+        }
+        __syncwarp();
+        if (area) {
+            float rgb[3]; unsigned cl;
+            eval_color_sh<false>(reinterpret_cast<const float*>(wrows + lane * RS4), p.M, p.D, csub(x, vc.campos[0]),
+                                 csub(y, vc.campos[1]), csub(z, vc.campos[2]), rgb, cl);
+            rec[3 * (size_t)i + 2] = make_float4(o_eff, rgb[0], rgb[1], rgb[2]);
+        }
+    } else if (area) {
+        float rgb[3];
+        if (p.colors_precomp) {
+            rgb[0] = __ldg(p.colors_precomp + 3 * i); rgb[1] = __ldg(p.colors_precomp + 3 * i + 1);
+            rgb[2] = __ldg(p.colors_precomp + 3 * i + 2);
+        } else {
+            unsigned cl;
+            eval_color_sh<true>(p.shs + (size_t)i * p.M * 3, p.M, p.D, csub(x, vc.campos[0]), csub(y, vc.campos[1]),
+                                csub(z, vc.campos[2]), rgb, cl);
+        }
+        rec[3 * (size_t)i + 2] = make_float4(o_eff, rgb[0], rgb[1], rgb[2]);
     }
     if (in_range) {
         radii[i] = radius;
@@ -221,15 +249,36 @@ __device__ __forceinline__ void store3(float* base, size_t i, float a, float b, 
     base[3 * i] = a; base[3 * i + 1] = b; base[3 * i + 2] = c;
 }
 
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp) {
+// SH rows are staged per warp through shared memory (COOP): the 32 rows of a warp's Gaussians are
+// contiguous in HBM, so the warp loads them with fully coalesced 16-byte accesses (12 independent loads
+// in flight per lane at SH3), each lane then works on ITS row in shared memory (row stride padded to an
+// odd number of 16-byte words: conflict-free), overwrites it in place with the dL/dsh row, and the warp
+// streams the 32 result rows back with coalesced 16-byte stores (zeros for culled Gaussians).
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp, int coop) {
+    extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
     const PreParams& p = bp.p;
     load_view_consts(vc, p.view, p.proj, p.campos);
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
-    if (i >= p.P) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool in_range = i < p.P;
     const b200splat_grads& o = bp.out;
-    const bool visible = bp.radii[i] > 0;
+    const bool visible = in_range && bp.radii[i] > 0;
     const int M3 = 3 * p.M;
+    // ---- COOP: coalesced load of the visible rows of this warp ----
+    const int nq = M3 >> 2, RS4 = sh_row_stride(M3) >> 2;
+    float4* wrows = s_sh4 + (size_t)warp * 32 * RS4;
+    const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
+    if (coop) {
+        const unsigned vmask = __ballot_sync(0xffffffffu, visible);
+        const float4* src = reinterpret_cast<const float4*>(p.shs) + (size_t)i0 * nq;
+        for (int c = lane; c < 32 * nq; c += 32) {
+            const int row = c / nq, q = c - row * nq;
+            if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + c);
+        }
+        __syncwarp();
+    }
+    float* my_row = reinterpret_cast<float*>(wrows + lane * RS4);
 
     float dmean[3] = {0.f, 0.f, 0.f};
     float dsc[3] = {0.f, 0.f, 0.f}, drot[4] = {0.f, 0.f, 0.f, 0.f}, dc6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -334,7 +383,8 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
             // recompute the clamp mask with the forward's exact arithmetic
             float rgbf[3]; unsigned cl;
             const float* sh_row = p.shs + (size_t)i * M3;
-            eval_color_sh(sh_row, p.M, p.D, ddx, ddy, ddz, rgbf, cl);
+            if (coop) eval_color_sh<false>(my_row, p.M, p.D, ddx, ddy, ddz, rgbf, cl);
+            else eval_color_sh<true>(sh_row, p.M, p.D, ddx, ddy, ddz, rgbf, cl);
             const float g0 = (cl & 1u) ? 0.f : dcol[0], g1 = (cl & 2u) ? 0.f : dcol[1], g2 = (cl & 4u) ? 0.f : dcol[2];
             float bb[16], bx[16], by[16], bz[16];
 #pragma unroll
@@ -373,14 +423,13 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
             const int nb = (p.D + 1) * (p.D + 1);
             float dRx = 0.f, dRy = 0.f, dRz = 0.f;
             float* dsh_row = o.dL_dsh + (size_t)i * M3;
-            if ((p.M & 3) == 0 && p.M <= 16) {
-                const float4* v = reinterpret_cast<const float4*>(sh_row);
-                float4* w = reinterpret_cast<float4*>(dsh_row);
+            if (coop) {
+                float4* w = reinterpret_cast<float4*>(my_row);      // in place: row in, dL/dsh row out
                 const int nvec = M3 >> 2;
 #pragma unroll
                 for (int kv = 0; kv < 12; kv++) {
                     if (kv < nvec) {
-                        const float4 t = __ldg(v + kv);
+                        const float4 t = w[kv];
                         const float f[4] = {t.x, t.y, t.z, t.w};
                         float out[4];
 #pragma unroll
@@ -395,18 +444,24 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
                     }
                 }
             } else {
-                for (int k = 0; k < p.M; k++) {
-                    const bool act = k < nb;
-                    const float bk = act ? bb[k < 16 ? k : 15] : 0.f;
-                    for (int ch = 0; ch < 3; ch++) {
-                        const float gch = ch == 0 ? g0 : (ch == 1 ? g1 : g2);
-                        dsh_row[3 * k + ch] = bk * gch;
-                        if (act) {
-                            const float sg = __ldg(sh_row + 3 * k + ch) * gch;
-                            dRx += bx[k] * sg; dRy += by[k] * sg; dRz += bz[k] * sg;
+                // static indices only: a dynamic index would push the basis arrays into local memory
+#pragma unroll
+                for (int k = 0; k < 16; k++) {
+                    if (k < p.M) {
+                        const bool act = k < nb;
+                        const float bk = act ? bb[k] : 0.f;
+#pragma unroll
+                        for (int ch = 0; ch < 3; ch++) {
+                            const float gch = ch == 0 ? g0 : (ch == 1 ? g1 : g2);
+                            dsh_row[3 * k + ch] = bk * gch;
+                            if (act) {
+                                const float sg = __ldg(sh_row + 3 * k + ch) * gch;
+                                dRx += bx[k] * sg; dRy += by[k] * sg; dRz += bz[k] * sg;
+                            }
                         }
                     }
                 }
+                for (int k = 16 * 3; k < M3; k++) dsh_row[k] = 0.f;
             }
             const float dotp = ux * dRx + uy * dRy + uz * dRz;
             const float il = 1.0f / len;
@@ -449,7 +504,12 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
             drot[3] = 2.f * (-2.f * qz * g[0][0] - r * g[0][1] + qx * g[0][2] + r * g[1][0] - 2.f * qz * g[1][1] +
                              qy * g[1][2] + qx * g[2][0] + qy * g[2][1]);
         }
-    } else if (p.shs && o.dL_dsh) {
+    } else if (coop) {
+        if (in_range) {
+            float4* w = reinterpret_cast<float4*>(my_row);
+            for (int k = 0; k < nq; k++) w[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    } else if (in_range && p.shs && o.dL_dsh) {
         float* dsh_row = o.dL_dsh + (size_t)i * M3;
         if ((M3 & 3) == 0) {
             float4* w = reinterpret_cast<float4*>(dsh_row);
@@ -459,6 +519,16 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
         }
     }
 
+    if (coop) {   // coalesced store of the warp's 32 dL/dsh rows
+        __syncwarp();
+        float4* dst = reinterpret_cast<float4*>(o.dL_dsh) + (size_t)i0 * nq;
+        const int rows = min(32, p.P - i0);
+        for (int c = lane; c < rows * nq; c += 32) {
+            const int row = c / nq, q = c - row * nq;
+            dst[c] = wrows[row * RS4 + q];
+        }
+    }
+    if (!in_range) return;
     store3(o.dL_dmeans3D, i, dmean[0], dmean[1], dmean[2]);
     if (o.dL_dmeans2D) store3(o.dL_dmeans2D, i, dndc[0], dndc[1], 0.f);
     if (o.dL_dcolors) store3(o.dL_dcolors, i, dcol[0], dcol[1], dcol[2]);
@@ -516,8 +586,15 @@ cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gauss
                                   int32_t* radii, unsigned long long* pair_counter, cudaStream_t s) {
     if (g.P == 0) return cudaSuccess;
     PreParams p = make_params(v, g);
-    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(p, gv.depths, gv.rec, gv.rect, gv.iota,
-                                                                                      radii, pair_counter);
+    const int M3 = 3 * g.M;
+    const int coop = (g.shs && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
+    const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(p, gv.depths, gv.rec, gv.rect, gv.iota,
+                                                                                         radii, pair_counter, coop);
     return cudaGetLastError();
 }
 
@@ -528,7 +605,14 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
     BwdParams bp;
     bp.p = make_params(v, g);
     bp.radii = radii; bp.acc = acc; bp.out = out;
-    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, s>>>(bp);
+    const int M3 = 3 * g.M;
+    const int coop = (g.shs && out.dL_dsh && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
+    const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop);
     return cudaGetLastError();
 }
 
