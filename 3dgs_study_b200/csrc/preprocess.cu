@@ -12,7 +12,10 @@ namespace b200splat {
 
 namespace {
 
-constexpr int PRE_THREADS = 256;
+#ifndef PRE_T
+#define PRE_T 128
+#endif
+constexpr int PRE_THREADS = PRE_T;
 
 // row stride (floats) of an SH row staged in shared memory: an odd number of 16-byte words
 __device__ __forceinline__ int sh_row_stride(int M3) { return ((M3 >> 2) & 1) ? M3 : M3 + 4; }

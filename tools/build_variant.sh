@@ -5,7 +5,7 @@ cd "$(dirname "$0")/../3dgs_study_b200/csrc"
 NAME=$1; shift
 OUT=../variants; mkdir -p $OUT/obj_$NAME
 NV="/usr/local/cuda/bin/nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC,-fvisibility=hidden -Xptxas -v --expt-relaxed-constexpr -ccbin /usr/bin/g++ $*"
-for f in api preprocess binning render_tiles; do
+for f in api preprocess binning render_tiles; do rm -f $OUT/obj_$NAME/$f.o;
   $NV -c $f.cu -o $OUT/obj_$NAME/$f.o 2> $OUT/obj_$NAME/$f.log &
 done
 wait
