@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
                                                                      uint32_t* __restrict__ iota,
                                                                      int32_t* __restrict__ radii,
                                                                      unsigned long long* __restrict__ pair_counter,
-                                                                     int coop) {
+                                                                     int coop, int qs) {
     extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
     __shared__ uint32_t s_pairs[PRE_THREADS / 32];
@@ -198,10 +198,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p
         const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
         const unsigned vmask = __ballot_sync(0xffffffffu, area != 0);
         const float4* src = reinterpret_cast<const float4*>(p.shs) + (size_t)i0 * nq;
-        for (int c = lane; c < 32 * nq; c += 32) {
-            const int row = c / nq, q = c - row * nq;
-            if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + c);
-        }
+        // 2^qs >= nq lanes per row, 32 >> qs rows per instruction: no division, every request contiguous
+        const int q = lane & ((1 << qs) - 1), rstep = 32 >> qs;
+        if (q < nq)
+            for (int row = lane >> qs; row < 32; row += rstep)
+                if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + row * nq + q);
         __syncwarp();
         if (area) {
             float rgb[3]; unsigned cl;
@@ -257,7 +258,7 @@ __device__ __forceinline__ void store3(float* base, size_t i, float a, float b, 
 // in flight per lane at SH3), each lane then works on ITS row in shared memory (row stride padded to an
 // odd number of 16-byte words: conflict-free), overwrites it in place with the dL/dsh row, and the warp
 // streams the 32 result rows back with coalesced 16-byte stores (zeros for culled Gaussians).
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp, int coop) {
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp, int coop, int qs) {
     extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
     const PreParams& p = bp.p;
@@ -275,10 +276,10 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
     if (coop) {
         const unsigned vmask = __ballot_sync(0xffffffffu, visible);
         const float4* src = reinterpret_cast<const float4*>(p.shs) + (size_t)i0 * nq;
-        for (int c = lane; c < 32 * nq; c += 32) {
-            const int row = c / nq, q = c - row * nq;
-            if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + c);
-        }
+        const int q = lane & ((1 << qs) - 1), rstep = 32 >> qs;
+        if (q < nq)
+            for (int row = lane >> qs; row < 32; row += rstep)
+                if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + row * nq + q);
         __syncwarp();
     }
     float* my_row = reinterpret_cast<float*>(wrows + lane * RS4);
@@ -526,10 +527,9 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
         __syncwarp();
         float4* dst = reinterpret_cast<float4*>(o.dL_dsh) + (size_t)i0 * nq;
         const int rows = min(32, p.P - i0);
-        for (int c = lane; c < rows * nq; c += 32) {
-            const int row = c / nq, q = c - row * nq;
-            dst[c] = wrows[row * RS4 + q];
-        }
+        const int q = lane & ((1 << qs) - 1), rstep = 32 >> qs;
+        if (q < nq)
+            for (int row = lane >> qs; row < rows; row += rstep) dst[row * nq + q] = wrows[row * RS4 + q];
     }
     if (!in_range) return;
     store3(o.dL_dmeans3D, i, dmean[0], dmean[1], dmean[2]);
@@ -569,6 +569,12 @@ __global__ void export_geom_kernel(int P, const int32_t* __restrict__ radii, Geo
     if (o.rgb) { o.rgb[3 * i] = c.y; o.rgb[3 * i + 1] = c.z; o.rgb[3 * i + 2] = c.w; }
 }
 
+int coop_shift(int nq) {   // smallest qs with 2^qs >= nq (nq <= 12)
+    int qs = 0;
+    while ((1 << qs) < nq) qs++;
+    return qs;
+}
+
 PreParams make_params(const b200splat_view& v, const b200splat_gaussians& g) {
     PreParams p;
     p.P = g.P; p.D = v.sh_degree; p.M = g.M; p.W = v.image_width; p.H = v.image_height;
@@ -597,7 +603,7 @@ cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gauss
         if (e != cudaSuccess) return e;
     }
     preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(p, gv.depths, gv.rec, gv.rect, gv.iota,
-                                                                                         radii, pair_counter, coop);
+                                                                                         radii, pair_counter, coop, coop_shift(M3 >> 2));
     return cudaGetLastError();
 }
 
@@ -615,7 +621,7 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
         cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop);
+    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop, coop_shift(M3 >> 2));
     return cudaGetLastError();
 }
 

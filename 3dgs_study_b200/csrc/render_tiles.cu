@@ -149,9 +149,9 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
                     bits &= bits - 1;
                     const float4 a = s_rec[3 * j], b = s_rec[3 * j + 1], c = s_rec[3 * j + 2];
                     float dx[NX], pw[NP];
-                    bool ok[NP], any_ok = false;
 #pragma unroll
                     for (int k = 0; k < NX; k++) dx[k] = csub(a.x, pxf[k]);
+                    float pmax = -3.0e38f;
 #pragma unroll
                     for (int ky = 0; ky < NY; ky++) {
                         const float dy = csub(a.y, pyf[ky]);
@@ -161,25 +161,25 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
                         for (int kx = 0; kx < NX; kx++) {
                             const float p = cfma(dx[kx], cfma(b.x, dx[kx], -bdy), t2);
                             pw[ky * NX + kx] = p;
-                            ok[ky * NX + kx] = p <= 0.0f && p >= b.w;
-                            any_ok |= ok[ky * NX + kx];
+                            pmax = fmaxf(pmax, p);
                         }
                     }
-                    if (!__any_sync(FULL, any_ok)) continue;
+                    // below thr no pixel of the strip can reach alpha >= 1/255: skip the exps
+                    if (!__any_sync(FULL, pmax >= b.w)) continue;
                     const uint32_t contributor = (uint32_t)(base + j + 1);
                     const float invd = DEPTH ? s_invd[j] : 0.f;
 #pragma unroll
                     for (int s = 0; s < NP; s++) {
-                        const float e = fminf(ALPHA_MAX, cmul(c.x, expf(pw[s])));
-                        const float alpha = ok[s] ? e : 0.0f;
+                        // exact tests: power <= 0, alpha >= 1/255, T (1 - alpha) >= 1e-4; a finished pixel has T < 0
+                        const float alpha = fminf(ALPHA_MAX, cmul(c.x, expf(pw[s])));
                         const float test_T = cmul(T[s], csub(1.0f, alpha));
-                        const bool valid = alpha >= ALPHA_MIN;
+                        const bool valid = alpha >= ALPHA_MIN && pw[s] <= 0.0f;
                         const bool blend = valid && !(test_T < T_EPS);
-                        const float w = cmul(alpha, T[s]);
-                        C0[s] = blend ? cfma(c.y, w, C0[s]) : C0[s];
-                        C1[s] = blend ? cfma(c.z, w, C1[s]) : C1[s];
-                        C2[s] = blend ? cfma(c.w, w, C2[s]) : C2[s];
-                        if (DEPTH) Dp[s] = blend ? cfma(invd, w, Dp[s]) : Dp[s];
+                        const float w = blend ? cmul(alpha, T[s]) : 0.0f;     // adding c * 0 leaves the sums unchanged
+                        C0[s] = cfma(c.y, w, C0[s]);
+                        C1[s] = cfma(c.z, w, C1[s]);
+                        C2[s] = cfma(c.w, w, C2[s]);
+                        if (DEPTH) Dp[s] = cfma(invd, w, Dp[s]);
                         T[s] = blend ? test_T : (valid ? -fabsf(T[s]) : T[s]);
                         last[s] = blend ? contributor : last[s];
                     }
@@ -331,16 +331,19 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
                 bool any_valid = false;
 #pragma unroll
                 for (int s = 0; s < NP; s++) {
-                    const float G = expf(pw[s]);
-                    const float alpha = fminf(ALPHA_MAX, cmul(c.x, G));
-                    const bool valid = ok[s] && alpha >= ALPHA_MIN;
+                    // au = o G (unclamped alpha), gated ONCE: with au = 0 every term below is an exact no-op
+                    // (alpha = 0, 1 / (1 - 0) = 1, T unchanged, w = 0, z = 0)
+                    const float au0 = cmul(c.x, expf(pw[s]));
+                    const bool valid = ok[s] && fminf(ALPHA_MAX, au0) >= ALPHA_MIN;
+                    const float au = valid ? au0 : 0.0f;
+                    const float alpha = fminf(ALPHA_MAX, au);
                     const float r = fast_rcp(1.0f - alpha);
                     const float Ti = T[s] * r;
                     const float cg = c.y * g0[s] + c.z * g1[s] + c.w * g2[s];
-                    const float w = valid ? alpha * Ti : 0.0f;
+                    const float w = alpha * Ti;
                     const float dLda = Ti * cg - S[s] * r;
-                    const float z = valid ? G * c.x * dLda : 0.0f;
-                    T[s] = valid ? Ti : T[s];
+                    const float z = au * dLda;
+                    T[s] = Ti;
                     S[s] = fmaf(w, cg, S[s]);
                     c0 = fmaf(w, g0[s], c0); c1 = fmaf(w, g1[s], c1); c2 = fmaf(w, g2[s], c2);
                     const float ddx = dx[s % NX], ddy = dyv[s / NX];

@@ -72,7 +72,9 @@ class ViewParallelStep:
         return color, radii
 
     # -- one step -------------------------------------------------------------------------------------
-    def step(self, cams: Sequence, dL_images: Sequence[torch.Tensor], reduce: bool = True) -> torch.Tensor:
+    def step(self, cams: Sequence, dL_images: Sequence[torch.Tensor], reduce: bool = True, on_forward=None) -> torch.Tensor:
+        """`on_forward(image)` (optional) is called right after each view's forward has been enqueued, before its
+        backward: the hook a caller uses to start consuming the image (e.g. a device->host copy on another stream)."""
         for t in self.leaves:
             t.grad = None
         self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
@@ -80,6 +82,8 @@ class ViewParallelStep:
         for cam, dL in zip(cams, dL_images):
             means2D = torch.zeros_like(self.leaves.means3D, requires_grad=True)
             color, radii = self._render(cam, means2D)
+            if on_forward is not None:
+                on_forward(color.detach())
             torch.autograd.backward([color], [dL])
             with torch.no_grad():
                 vis = radii > 0

@@ -39,8 +39,8 @@ UNIT = "views/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--width", type=int, default=1920)
@@ -65,46 +65,68 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    """Samples SM clock / throttle reasons DURING the timed region (B200_PROFILING.md "clocks line").
+    In-process NVML (nvidia_ml_py) on a 25 ms period: spawning nvidia-smi next to a 3 ms step perturbs the
+    step itself (driver lock + a competing process); nvidia-smi is only the fallback when NVML is missing."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index=0):
-        self.index, self.samples, self._stop, self._th = index, [], threading.Event(), None
+        self.index, self._stop, self._th = index, threading.Event(), None
+        self.sm, self.mx, self.reasons, self.source = [], [], set(), None
+        self._h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self._nv, self._h, self.source = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys), "nvml"
+        except Exception:
+            self.source = "nvidia-smi"
+
+    def _sample_nvml(self):
+        nv, h = self._nv, self._h
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+        self.mx.append(float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)))
+        r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h)) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+        for name, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        f = [x.strip() for x in out.split(",")]
+        self.sm.append(float(f[0])); self.mx.append(float(f[1]))
+        for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[3:7]):
+            if v.lower().startswith("active"):
+                self.reasons.add(name)
 
     def _run(self):
+        period = 0.025 if self._h is not None else 0.5
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                self._sample_nvml() if self._h is not None else self._sample_smi()
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(period)
 
     def __enter__(self):
+        if os.environ.get("BENCH_NO_CLOCKS"):
+            return self
         self._th = threading.Thread(target=self._run, daemon=True)
         self._th.start()
         return self
 
     def __exit__(self, *exc):
         self._stop.set()
-        self._th.join(timeout=10)
+        if self._th is not None:
+            self._th.join(timeout=10)
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for s in self.samples:
-            try:
-                sm.append(float(s[0])); mx.append(float(s[1]))
-                for nme, v in zip(names, s[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(nme)
-            except Exception:
-                continue
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": self.source}
 
 
 def dist_setup(n):
@@ -183,25 +205,54 @@ def run_ours(a):
     h2d = cam_host[0].numel() * 4 + dL_cpu.numel() * 4
     d2h = img_host.numel() * 4 + 4
 
-    def step_e2e(i):
-        k = view_of(i)
-        cm = cam_host[k].to(dev, non_blocking=True)
-        g_img = dL_cpu.to(dev, non_blocking=True)
-        cam = cams_cpu[k]._replace(world_view_transform=cm[:16].view(4, 4), full_proj_transform=cm[16:32].view(4, 4),
-                                   camera_center=cm[32:35])
-        img = stepper.step([cam], [g_img])
-        img_host.copy_(img, non_blocking=True)
+    # Software pipeline over two streams: the copy stream brings step i+1's inputs from pinned host memory while
+    # step i computes, and takes step i's image back to the host while step i's backward runs.  Every byte of
+    # every step still crosses PCIe inside the timed region; the host consumes step i's results at the end of step i.
+    copy_stream = torch.cuda.Stream(device=dev)
+    main_stream = torch.cuda.current_stream(dev)
+    slots = [{"cm": torch.empty(35, device=dev), "g": torch.empty(3, H, W, device=dev), "ready": torch.cuda.Event()} for _ in range(2)]
+    img_done, fwd_done = torch.cuda.Event(), torch.cuda.Event()
+
+    def prefetch(i):
+        sl = slots[i % 2]
+        with torch.cuda.stream(copy_stream):
+            sl["cm"].copy_(cam_host[view_of(i)], non_blocking=True)
+            sl["g"].copy_(dL_cpu, non_blocking=True)
+            sl["ready"].record(copy_stream)
+
+    def step_e2e(i, first=False):
+        if first:
+            prefetch(i)
+        sl = slots[i % 2]
+        main_stream.wait_event(sl["ready"])
+        copy_stream.wait_event(img_done)              # slot (i+1)%2 was last read by step i-1, which has completed
+        prefetch(i + 1)
+        cm = sl["cm"]
+        cam = cams_cpu[view_of(i)]._replace(world_view_transform=cm[:16].view(4, 4), full_proj_transform=cm[16:32].view(4, 4),
+                                            camera_center=cm[32:35])
+
+        def on_forward(img):
+            fwd_done.record(main_stream)
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(fwd_done)
+                img.record_stream(copy_stream)
+                img_host.copy_(img, non_blocking=True)
+
+        stepper.step([cam], [sl["g"]], on_forward=on_forward)
         chk_host.copy_(stepper.grad_checksum().reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()      # the host consumes the result every step
+        img_done.record(main_stream)
+        main_stream.synchronize()                      # the host consumes the results every step
+        copy_stream.synchronize()
 
     for i in range(max(3, a.warmup // 2)):
-        step_e2e(i)
+        step_e2e(i, first=(i == 0))
     torch.cuda.synchronize()
+    e2e_base = max(3, a.warmup // 2)
     if world > 1:
         dist.barrier()
     ev0.record()
     for i in range(a.steps):
-        step_e2e(i)
+        step_e2e(e2e_base + i)
     ev1.record()
     torch.cuda.synchronize()
     ms_e2e = ev0.elapsed_time(ev1)
