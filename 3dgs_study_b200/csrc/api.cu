@@ -196,7 +196,8 @@ int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g,
     int rc = validate(view, g);
     if (rc) return rc;
     if (!grads || !grads->dL_dmeans3D) return fail(B200SPLAT_ERR_INVALID_ARG, "grads->dL_dmeans3D is required");
-    if (g->shs && !grads->dL_dsh) return fail(B200SPLAT_ERR_INVALID_ARG, "grads->dL_dsh is required with shs");
+    if (g->shs && !grads->dL_dsh && !grads->dL_dcolors)
+        return fail(B200SPLAT_ERR_INVALID_ARG, "with shs, grads->dL_dsh (or dL_dcolors for the masked colour gradient) is required");
     if (grads->dL_dsh && !aligned16(grads->dL_dsh)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dsh must be 16-byte aligned");
     if (grads->dL_drotations && !aligned16(grads->dL_drotations))
         return fail(B200SPLAT_ERR_INVALID_ARG, "dL_drotations must be 16-byte aligned");
@@ -236,6 +237,20 @@ int b200splat_mark_visible(int32_t P, const float* means3D, const float* viewmat
     (void)projmatrix;
     if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return fail(B200SPLAT_ERR_INVALID_ARG, "bad arguments");
     CU(launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream_), "mark_visible");
+    return B200SPLAT_OK;
+}
+
+int b200splat_sh_grad_from_views(int32_t P, int32_t M, int32_t sh_degree, const float* means3D, int32_t n_views,
+                                 const float* const* dcol, const float* campos, float* dL_dsh, void* stream_) {
+    if (P < 0 || M <= 0 || sh_degree < 0 || sh_degree > 3 || M < (sh_degree + 1) * (sh_degree + 1))
+        return fail(B200SPLAT_ERR_INVALID_ARG, "bad P / M / sh_degree");
+    if (n_views < 1 || n_views > B200SPLAT_MAX_VIEWS) return fail(B200SPLAT_ERR_INVALID_ARG, "n_views must be in [1, B200SPLAT_MAX_VIEWS]");
+    if (P == 0) return B200SPLAT_OK;
+    if (!means3D || !dcol || !campos || !dL_dsh) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
+    for (int v = 0; v < n_views; v++)
+        if (!dcol[v]) return fail(B200SPLAT_ERR_INVALID_ARG, "null dcol pointer");
+    if (!aligned16(dL_dsh)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dsh must be 16-byte aligned");
+    CU(launch_sh_grad_from_views(P, M, sh_degree, means3D, n_views, dcol, campos, dL_dsh, (cudaStream_t)stream_), "sh_grad_from_views");
     return B200SPLAT_OK;
 }
 

@@ -258,7 +258,9 @@ __device__ __forceinline__ void store3(float* base, size_t i, float a, float b, 
 // in flight per lane at SH3), each lane then works on ITS row in shared memory (row stride padded to an
 // odd number of 16-byte words: conflict-free), overwrites it in place with the dL/dsh row, and the warp
 // streams the 32 result rows back with coalesced 16-byte stores (zeros for culled Gaussians).
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp, int coop, int qs) {
+// write_dsh = 0 (view-parallel exchange, see sh_grad_from_views_kernel): the dL/dsh rows are NOT written; the
+// colour gradient, already multiplied by the SH clamp mask, goes to out.dL_dcolors instead.
+__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp, int coop, int qs, int write_dsh) {
     extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
     const PreParams& p = bp.p;
@@ -444,7 +446,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
                             out[e] = act ? bb[k] * gch : 0.f;
                             if (act) { const float sg = f[e] * gch; dRx += bx[k] * sg; dRy += by[k] * sg; dRz += bz[k] * sg; }
                         }
-                        w[kv] = make_float4(out[0], out[1], out[2], out[3]);
+                        if (write_dsh) w[kv] = make_float4(out[0], out[1], out[2], out[3]);
                     }
                 }
             } else {
@@ -457,7 +459,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
 #pragma unroll
                         for (int ch = 0; ch < 3; ch++) {
                             const float gch = ch == 0 ? g0 : (ch == 1 ? g1 : g2);
-                            dsh_row[3 * k + ch] = bk * gch;
+                            if (write_dsh) dsh_row[3 * k + ch] = bk * gch;
                             if (act) {
                                 const float sg = __ldg(sh_row + 3 * k + ch) * gch;
                                 dRx += bx[k] * sg; dRy += by[k] * sg; dRz += bz[k] * sg;
@@ -465,8 +467,9 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
                         }
                     }
                 }
-                for (int k = 16 * 3; k < M3; k++) dsh_row[k] = 0.f;
+                if (write_dsh) for (int k = 16 * 3; k < M3; k++) dsh_row[k] = 0.f;
             }
+            if (!write_dsh) { dcol[0] = g0; dcol[1] = g1; dcol[2] = g2; }
             const float dotp = ux * dRx + uy * dRy + uz * dRz;
             const float il = 1.0f / len;
             dmean[0] += (dRx - ux * dotp) * il;
@@ -509,11 +512,11 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
                              qy * g[1][2] + qx * g[2][0] + qy * g[2][1]);
         }
     } else if (coop) {
-        if (in_range) {
+        if (in_range && write_dsh) {
             float4* w = reinterpret_cast<float4*>(my_row);
             for (int k = 0; k < nq; k++) w[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-    } else if (in_range && p.shs && o.dL_dsh) {
+    } else if (in_range && p.shs && write_dsh) {
         float* dsh_row = o.dL_dsh + (size_t)i * M3;
         if ((M3 & 3) == 0) {
             float4* w = reinterpret_cast<float4*>(dsh_row);
@@ -523,7 +526,7 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
         }
     }
 
-    if (coop) {   // coalesced store of the warp's 32 dL/dsh rows
+    if (coop && write_dsh) {   // coalesced store of the warp's 32 dL/dsh rows
         __syncwarp();
         float4* dst = reinterpret_cast<float4*>(o.dL_dsh) + (size_t)i0 * nq;
         const int rows = min(32, p.P - i0);
@@ -541,6 +544,75 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
     if (o.dL_dcov3D) {
 #pragma unroll
         for (int k = 0; k < 6; k++) o.dL_dcov3D[6 * (size_t)i + k] = dc6[k];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// View-parallel exchange (DESIGN.md "Multi-GPU"): dL/dsh of one view is the outer product
+//   dL/dsh[i][k][c] = Y_k(dir(mean_i - campos_v)) * dcol_v[i][c]        (dcol already clamp-masked)
+// and every rank holds the means and can be told every view's camera centre, so the ranks exchange the
+// 12-byte colour gradients (all-gather, or peer loads) instead of all-reducing the 12*M-byte rows, and
+// each rank rebuilds sum_v dL/dsh_v locally.  dcol[v] may point into a peer GPU's memory (NVLink loads).
+// ------------------------------------------------------------------------------------------------
+struct ViewGrads {
+    int n;
+    const float* dcol[B200SPLAT_MAX_VIEWS];   // [P,3] each
+};
+
+__global__ void __launch_bounds__(PRE_THREADS) sh_grad_from_views_kernel(int P, int M, int D, const float* __restrict__ means3D,
+                                                                         ViewGrads vg, const float* __restrict__ campos,
+                                                                         float* __restrict__ dL_dsh, int coop, int qs) {
+    extern __shared__ float4 s_sh4[];
+    __shared__ float s_cam[B200SPLAT_MAX_VIEWS * 3];
+    if (threadIdx.x < vg.n * 3) s_cam[threadIdx.x] = campos[threadIdx.x];
+    __syncthreads();
+    const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool in_range = i < P;
+    const int M3 = 3 * M, nb = (D + 1) * (D + 1);
+    float acc[48];
+#pragma unroll
+    for (int k = 0; k < 48; k++) acc[k] = 0.f;
+    if (in_range) {
+        const float x = __ldg(means3D + 3 * i), y = __ldg(means3D + 3 * i + 1), z = __ldg(means3D + 3 * i + 2);
+        for (int v = 0; v < vg.n; v++) {
+            const float* dc = vg.dcol[v] + 3 * (size_t)i;
+            const float g0 = dc[0], g1 = dc[1], g2 = dc[2];
+            if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;     // culled or clamped in that view
+            const float ddx = csub(x, s_cam[3 * v]), ddy = csub(y, s_cam[3 * v + 1]), ddz = csub(z, s_cam[3 * v + 2]);
+            const float len = csqrt(cfma(ddz, ddz, cfma(ddy, ddy, cmul(ddx, ddx))));
+            float b[16];
+            sh_basis(D, cdiv(ddx, len), cdiv(ddy, len), cdiv(ddz, len), b);
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                if (k < nb) {
+                    acc[3 * k] = fmaf(b[k], g0, acc[3 * k]);
+                    acc[3 * k + 1] = fmaf(b[k], g1, acc[3 * k + 1]);
+                    acc[3 * k + 2] = fmaf(b[k], g2, acc[3 * k + 2]);
+                }
+            }
+        }
+    }
+    if (coop) {
+        const int nq = M3 >> 2, RS4 = sh_row_stride(M3) >> 2;
+        float4* wrows = s_sh4 + (size_t)warp * 32 * RS4;
+        float4* w = wrows + lane * RS4;
+#pragma unroll
+        for (int kv = 0; kv < 12; kv++)
+            if (kv < nq) w[kv] = make_float4(acc[4 * kv], acc[4 * kv + 1], acc[4 * kv + 2], acc[4 * kv + 3]);
+        __syncwarp();
+        const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
+        float4* dst = reinterpret_cast<float4*>(dL_dsh) + (size_t)i0 * nq;
+        const int rows = min(32, P - i0);
+        const int q = lane & ((1 << qs) - 1), rstep = 32 >> qs;
+        if (q < nq)
+            for (int row = lane >> qs; row < rows; row += rstep) dst[row * nq + q] = wrows[row * RS4 + q];
+    } else if (in_range) {
+        float* row = dL_dsh + (size_t)i * M3;
+#pragma unroll
+        for (int k = 0; k < 48; k++)
+            if (k < M3) row[k] = acc[k];
+        for (int k = 48; k < M3; k++) row[k] = 0.f;
     }
 }
 
@@ -615,13 +687,31 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
     bp.p = make_params(v, g);
     bp.radii = radii; bp.acc = acc; bp.out = out;
     const int M3 = 3 * g.M;
-    const int coop = (g.shs && out.dL_dsh && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
+    const int coop = (g.shs && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
     const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop, coop_shift(M3 >> 2));
+    preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop, coop_shift(M3 >> 2), out.dL_dsh ? 1 : 0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sh_grad_from_views(int P, int M, int D, const float* means3D, int n_views, const float* const* dcol,
+                                      const float* campos, float* dL_dsh, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    ViewGrads vg;
+    vg.n = n_views;
+    for (int v = 0; v < B200SPLAT_MAX_VIEWS; v++) vg.dcol[v] = v < n_views ? dcol[v] : nullptr;
+    const int M3 = 3 * M;
+    const int coop = (M > 0 && (M3 & 3) == 0 && M <= 16) ? 1 : 0;
+    const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(sh_grad_from_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    sh_grad_from_views_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(P, M, D, means3D, vg, campos, dL_dsh,
+                                                                                          coop, coop_shift(M3 >> 2));
     return cudaGetLastError();
 }
 

@@ -101,6 +101,10 @@ def lib():
         L.b200splat_mark_visible.restype = ctypes.c_int
         L.b200splat_mark_visible.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_sh_grad_from_views.restype = ctypes.c_int
+        L.b200splat_sh_grad_from_views.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p,
+                                                   ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                   ctypes.c_void_p]
         L.b200splat_render_stats.restype = ctypes.c_int
         L.b200splat_render_stats.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -230,8 +234,13 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, opacities=None, antialiasing=False,
-                                 image_height=None, image_width=None, stage_times: StageTimes = None):
-    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)"""
+                                 image_height=None, image_width=None, stage_times: StageTimes = None,
+                                 masked_colors: bool = False, out: Optional[dict] = None):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+
+    masked_colors=True (SH mode only): dL_dsh is not produced (None); dL_dcolors is the colour gradient times the
+    SH clamp mask, the quantity the view-parallel exchange ships (see sh_grad_from_views).
+    out: optional preallocated fp32 CUDA outputs by name (e.g. views into one flat all-reduce buffer)."""
     dev = means3D.device
     P = means3D.shape[0]
     dL_dout_color = _f32c(dL_dout_color, "dL_dout_color", dev)
@@ -252,17 +261,24 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     campos = _f32c(campos, "campos", dev)
     M = int(sh.shape[1]) if sh is not None else 0
 
-    def new(*shape):
+    def new(name, *shape):
+        if out is not None and name in out:
+            t = out[name]
+            if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == int(torch.Size(shape).numel())):
+                raise RuntimeError(f"out[{name!r}] must be a contiguous fp32 CUDA tensor with {shape} elements")
+            return t.view(shape)
         return torch.empty(shape, dtype=torch.float32, device=dev)
 
-    dL_dmeans2D = new(P, 3)
-    dL_dcolors = new(P, 3) if colors is not None else None
-    dL_dopacity = new(P, 1)
-    dL_dmeans3D = new(P, 3)
-    dL_dcov3D = new(P, 6) if cov3D_precomp is not None else None
-    dL_dsh = new(P, M, 3) if sh is not None else None
-    dL_dscales = new(P, 3) if scales is not None else None
-    dL_drotations = new(P, 4) if rotations is not None else None
+    if masked_colors and sh is None:
+        raise RuntimeError("masked_colors needs shs")
+    dL_dmeans2D = new("dL_dmeans2D", P, 3)
+    dL_dcolors = new("dL_dcolors", P, 3) if (colors is not None or masked_colors) else None
+    dL_dopacity = new("dL_dopacity", P, 1)
+    dL_dmeans3D = new("dL_dmeans3D", P, 3)
+    dL_dcov3D = new("dL_dcov3D", P, 6) if cov3D_precomp is not None else None
+    dL_dsh = new("dL_dsh", P, M, 3) if (sh is not None and not masked_colors) else None
+    dL_dscales = new("dL_dscales", P, 3) if scales is not None else None
+    dL_drotations = new("dL_drotations", P, 4) if rotations is not None else None
 
     view = _View(H, W, float(tan_fovx), float(tan_fovy), float(scale_modifier), int(degree), 0, int(bool(debug)),
                  int(bool(antialiasing)), _ptr(background), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos))
@@ -299,6 +315,36 @@ def mark_visible(means3D, viewmatrix, projmatrix):
                                           _stream_ptr(dev))
     _check(rc, "mark_visible")
     return present
+
+
+def sh_grad_from_views(means3D, dcols, campos, M: int, degree: int, out: Optional[torch.Tensor] = None):
+    """dL_dsh[P,M,3] = sum_v Y(normalize(means3D - campos[v])) (x) dcols[v]  (b200splat_sh_grad_from_views).
+    dcols: sequence of [P,3] fp32 CUDA tensors, or raw device addresses (ints) of such arrays -- e.g. peer-GPU
+    buffers mapped through symmetric memory.  campos: [n_views,3] fp32 CUDA tensor."""
+    dev = means3D.device
+    P = means3D.shape[0]
+    means3D = _f32c(means3D, "means3D", dev)
+    campos = _f32c(campos, "campos", dev)
+    n = len(dcols)
+    keep = []
+    ptrs = (ctypes.c_void_p * n)()
+    for v, d in enumerate(dcols):
+        if isinstance(d, torch.Tensor):
+            d = _f32c(d, "dcol", dev)
+            if d is None or d.numel() != 3 * P:
+                raise RuntimeError("every dcol must be a [P,3] tensor")
+            keep.append(d)
+            ptrs[v] = d.data_ptr()
+        else:
+            ptrs[v] = int(d)
+    if campos is None or campos.numel() != 3 * n:
+        raise RuntimeError("campos must be [n_views,3]")
+    dL_dsh = out if out is not None else torch.empty((P, int(M), 3), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_sh_grad_from_views(P, int(M), int(degree), _ptr(means3D), n, ptrs, _ptr(campos), _ptr(dL_dsh),
+                                                _stream_ptr(dev))
+    _check(rc, "sh_grad_from_views")
+    return dL_dsh
 
 
 def render_stats(P, W, H, num_rendered, geomBuffer, binningBuffer, imageBuffer):

@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sh-degree", type=int, default=3)
+    ap.add_argument("--exchange", default=None, choices=["allreduce", "factorized"],
+                    help="N>1 gradient exchange (default: factorized); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-tile-stride", type=int, default=16, help="CPU legs render 1/stride of the tiles")
     ap.add_argument("--stages", action="store_true", help="print the per-stage table to stderr")
@@ -166,7 +168,7 @@ def run_ours(a):
     dL_cpu = synth.make_grad_image(W, H).pin_memory()
     dL = dL_cpu.to(dev)
     params = vp.GaussianParams(scene.means3D, scene.shs, scene.opacities, scene.scales, scene.rotations)
-    stepper = vp.ViewParallelStep(params, D, bg, world_size=world)
+    stepper = vp.ViewParallelStep(params, D, bg, world_size=world, exchange=a.exchange)
 
     def view_of(step):   # rank r renders view (step * world + r) of the orbit
         return (step * world + rank) % n_views
@@ -281,7 +283,8 @@ def run_ours(a):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a), "gaussians": P, "sh_degree": D, "width": W, "height": H,
                    "visible": stats.get("visible"), "tile_pairs_R": stats.get("R"), "views_per_rank_per_step": 1,
-                   "parallelism": f"view-parallel x{world}, Gaussians replicated" + (", NCCL sum-allreduce of 59 f32/Gaussian grads" if world > 1 else ""),
+                   "parallelism": f"view-parallel x{world}, Gaussians replicated" + ((", exchange=" + stepper.exchange + (": NCCL all-gather of [P,3] masked colour grads + all-reduce of 11 f32/Gaussian, dL/dsh rebuilt locally"
+                                                                          if stepper.exchange == "factorized" else ": NCCL sum-allreduce of 59 f32/Gaussian grads")) if world > 1 else ""),
                    "l2_note": "inputs (0.7 GB of Gaussians + 0.2 GB of keys per view) exceed the 126 MB L2; a different view every step"},
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": round(ms_e2e / a.steps, 4),

@@ -131,11 +131,12 @@ B200SPLAT_API int b200splat_forward(const b200splat_view* view, const b200splat_
  * need not clear them. */
 typedef struct b200splat_grads {
     float* dL_dmeans2D;   /* [P,3]  xy = dL/d(NDC xy) (pixel gradient x 0.5W, 0.5H), z = 0      */
-    float* dL_dcolors;    /* [P,3]  gradient of colors_precomp                                   */
+    float* dL_dcolors;    /* [P,3]  gradient of colors_precomp; with shs and dL_dsh == NULL: the colour
+                           *        gradient times the SH clamp mask (see b200splat_sh_grad_from_views)   */
     float* dL_dopacity;   /* [P]                                                                  */
     float* dL_dmeans3D;   /* [P,3]                                                                */
     float* dL_dcov3D;     /* [P,6]  gradient of cov3D_precomp                                    */
-    float* dL_dsh;        /* [P,M,3]                                                              */
+    float* dL_dsh;        /* [P,M,3] (may be NULL with shs if dL_dcolors is given)                        */
     float* dL_dscales;    /* [P,3]                                                                */
     float* dL_drotations; /* [P,4]                                                                */
 } b200splat_grads;
@@ -173,6 +174,20 @@ typedef struct b200splat_state_out {
 B200SPLAT_API int b200splat_export_state(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
                            const int32_t* radii, const void* geom, const void* binning,
                            const void* image, const b200splat_state_out* out, void* stream);
+
+/* View-parallel gradient exchange (one view per GPU, Gaussians replicated; the reference itself is single-GPU,
+ * /root/reference/train.py:86-98).  The SH gradient of a view is an outer product,
+ *   dL/dsh[i][k][c] = Y_k(normalize(mean_i - campos_v)) * dcol_v[i][c],
+ * with dcol_v the colour gradient of view v already multiplied by the SH clamp mask -- what b200splat_backward
+ * writes to grads->dL_dcolors when called with shs != NULL and grads->dL_dsh == NULL.  Ranks therefore exchange
+ * the [P,3] colour gradients (12 B per Gaussian and view instead of 12*M B) and each rebuilds
+ *   dL_dsh[P,M,3] = sum_v Y(dir_v) (x) dcol_v
+ * with this call.  dcol[v] are n_views DEVICE pointers (host array), which may address peer GPUs' memory
+ * mapped into this process (NVLink loads); campos is a device array [n_views,3].  dL_dsh is fully written. */
+#define B200SPLAT_MAX_VIEWS 16
+B200SPLAT_API int b200splat_sh_grad_from_views(int32_t P, int32_t M, int32_t sh_degree, const float* means3D,
+                           int32_t n_views, const float* const* dcol, const float* campos,
+                           float* dL_dsh, void* stream);
 
 /* Inspection: workload counters of the render stage of the view whose forward state is given, written
  * to out14 (device, 14 x u64): [0..8] (tile, Gaussian) pairs by number of 8x4-pixel sub-blocks the splat's

@@ -70,3 +70,65 @@ def test_two_rank_step_matches_single_process():
     assert torch.allclose(r0["accum"], single.xyz_gradient_accum, rtol=1e-4, atol=1e-9)
     assert torch.equal(r0["denom"], single.denom) and torch.equal(r0["maxr"], single.max_radii2D)
     assert float(single.denom.max()) > 1                              # some Gaussian seen from several views
+
+
+# ---- factorized exchange (all-gather of masked colour gradients + local SH rebuild) ---------------------------
+class _TorchBackend:
+    """CPU stand-in for the CUDA backend of the factorized exchange, built on the PyTorch oracle."""
+
+    def __init__(self, sh_degree, bg):
+        self.D, self.bg = sh_degree, bg
+
+    def view_fwd_bwd(self, cam, dL, lv, out, on_forward=None):
+        leaves = vp.GaussianParams(*[t.detach().clone().requires_grad_(True) for t in lv])
+        m2d = torch.zeros_like(leaves.means3D, requires_grad=True)
+        color, radii = _oracle_rasterize(cam, leaves, m2d, self.D, self.bg, 1.0)
+        torch.autograd.backward([color], [dL])
+        out["dL_dmeans3D"].copy_(leaves.means3D.grad); out["dL_dopacity"].copy_(leaves.opacities.grad.view(-1, 1))
+        out["dL_dscales"].copy_(leaves.scales.grad); out["dL_drotations"].copy_(leaves.rotations.grad)
+        out["dL_dcolors"].copy_(leaves.shs.grad[:, 0, :] / 0.28209479177387814)   # Y_0 is constant: dcol = dL/dsh_0 / Y_0
+        return color.detach(), radii, m2d.grad
+
+    def sh_grad_from_views(self, means3D, dcols, campos, M, degree):
+        from oracle import torch_ref as tr
+        nb = (degree + 1) ** 2
+        out = torch.zeros(means3D.shape[0], M, 3)
+        for v, dc in enumerate(dcols):
+            dirs = means3D - campos[v]
+            dirs = dirs / dirs.norm(dim=1, keepdim=True)
+            for k in range(nb):
+                onehot = torch.zeros(means3D.shape[0], 1, nb); onehot[:, 0, k] = 1.0
+                out[:, k, :] += tr.eval_sh(degree, onehot, dirs)[:, :1] * dc
+        return out
+
+
+def _worker_fact(rank, world, initfile, outdir):
+    dist.init_process_group("gloo", init_method=f"file://{initfile}", rank=rank, world_size=world)
+    torch.set_num_threads(2)
+    params, cams, dLs = _setup()
+    mine = vp.shard_views(NV, rank, world)
+    st = vp.ViewParallelStep(params, D, torch.zeros(3), world_size=world, exchange="factorized",
+                             backend=_TorchBackend(D, torch.zeros(3)))
+    st.step([cams[k] for k in mine], [dLs[k] for k in mine])
+    local_accum = st.xyz_gradient_accum.clone()
+    st.reduce_densification_stats()
+    torch.save({"grads": [t.clone() for t in st.grads()], "accum": st.xyz_gradient_accum.clone(), "local_accum": local_accum,
+                "denom": st.denom.clone(), "maxr": st.max_radii2D.clone()}, os.path.join(outdir, f"f{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_factorized_exchange_matches_single_process():
+    with tempfile.TemporaryDirectory() as d:
+        initfile = os.path.join(d, "init")
+        mp.spawn(_worker_fact, args=(2, initfile, d), nprocs=2, join=True)
+        r0, r1 = torch.load(os.path.join(d, "f0.pt")), torch.load(os.path.join(d, "f1.pt"))
+    params, cams, dLs = _setup()
+    single = vp.ViewParallelStep(params, D, torch.zeros(3), world_size=1, rasterize=_oracle_rasterize)
+    single.step(cams, dLs)
+    for a, b, c in zip(r0["grads"], r1["grads"], single.grads()):
+        assert float((a - b).abs().max()) <= 1e-6 * max(float(c.abs().max()), 1e-12)     # ranks agree
+        assert float((a - c).abs().max()) <= 1e-3 * max(float(c.abs().max()), 1e-12)     # == sum over all views
+    assert not torch.equal(r0["local_accum"], r0["accum"])                               # stats were rank-local until reduced
+    assert torch.allclose(r0["accum"], single.xyz_gradient_accum, rtol=1e-4, atol=1e-9)
+    assert torch.equal(r0["denom"], single.denom) and torch.equal(r0["maxr"], single.max_radii2D)
