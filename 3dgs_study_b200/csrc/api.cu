@@ -193,10 +193,21 @@ int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g,
                        const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
                        b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times,
                        void* stream_) {
+    return b200splat_backward_ex(view, g, radii, geom, binning, image, num_rendered, dL_dout_color, dL_dout_invdepth, grads,
+                                 nullptr, scratch_alloc, scratch_ctx, times, stream_);
+}
+
+int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
+                          const void* geom, const void* binning, const void* image, int32_t num_rendered,
+                          const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
+                          const b200splat_backward_hooks* hooks, b200splat_alloc_fn scratch_alloc, void* scratch_ctx,
+                          b200splat_stage_times* times, void* stream_) {
     int rc = validate(view, g);
     if (rc) return rc;
     if (!grads || !grads->dL_dmeans3D) return fail(B200SPLAT_ERR_INVALID_ARG, "grads->dL_dmeans3D is required");
-    if (g->shs && !grads->dL_dsh && !grads->dL_dcolors)
+    float* early_colors = hooks ? hooks->masked_colors : nullptr;
+    if (early_colors && !g->shs) return fail(B200SPLAT_ERR_INVALID_ARG, "hooks->masked_colors needs shs");
+    if (g->shs && !grads->dL_dsh && !grads->dL_dcolors && !early_colors)
         return fail(B200SPLAT_ERR_INVALID_ARG, "with shs, grads->dL_dsh (or dL_dcolors for the masked colour gradient) is required");
     if (grads->dL_dsh && !aligned16(grads->dL_dsh)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dsh must be 16-byte aligned");
     if (grads->dL_drotations && !aligned16(grads->dL_drotations))
@@ -207,7 +218,10 @@ int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g,
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool debug = view->debug != 0;
     const int P = g->P, W = view->image_width, H = view->image_height;
-    if (P == 0) return B200SPLAT_OK;
+    if (P == 0) {
+        if (early_colors && hooks->after_masked_colors) hooks->after_masked_colors(hooks->ctx);
+        return B200SPLAT_OK;
+    }
 
     GeomView gv = carve_geom(const_cast<void*>(geom), P);
     BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, tiles_of(W, H));
@@ -223,6 +237,10 @@ int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g,
     if (num_rendered > 0)
         STAGE(launch_render_bwd(*view, gv, bv.vals_sorted, iv, dL_dout_color, dL_dout_invdepth, acc, stream), "render backward");
     tm.mark();
+    if (early_colors) {
+        STAGE(launch_masked_colour_grad(P, radii, gv, acc, early_colors, stream), "masked colour gradient");
+        if (hooks->after_masked_colors) hooks->after_masked_colors(hooks->ctx);
+    }
     STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, *grads, stream), "preprocess backward");
     tm.mark();
     if (times) {

@@ -67,7 +67,10 @@ __device__ __forceinline__ void eval_color_sh(const float* __restrict__ sh_row, 
     }
     r0 = cadd(r0, 0.5f); r1 = cadd(r1, 0.5f); r2 = cadd(r2, 0.5f);
     clamped = (r0 < 0.0f ? 1u : 0u) | (r1 < 0.0f ? 2u : 0u) | (r2 < 0.0f ? 4u : 0u);
-    rgb[0] = fmaxf(r0, 0.0f); rgb[1] = fmaxf(r1, 0.0f); rgb[2] = fmaxf(r2, 0.0f);
+    // a clamped channel is stored as -0.0f: blending with it is bit-identical to +0.0f, and the sign bit
+    // carries the clamp flag to the backward pass (masked_colour_grad_kernel) for free
+    const float nz = __int_as_float(0x80000000);
+    rgb[0] = r0 < 0.0f ? nz : r0; rgb[1] = r1 < 0.0f ? nz : r1; rgb[2] = r2 < 0.0f ? nz : r2;
 }
 
 // Geometry shared by forward and backward: everything up to the 2D covariance.
@@ -547,6 +550,25 @@ __global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams b
     }
 }
 
+// Colour gradient of every Gaussian times the SH clamp mask, straight from the render backward's sums: the
+// quantity the view-parallel exchange ships.  Runs BEFORE the per-Gaussian backward so that the exchange
+// overlaps it.
+__global__ void __launch_bounds__(256) masked_colour_grad_kernel(int P, const int32_t* __restrict__ radii,
+                                                                 const float4* __restrict__ rec, const float4* __restrict__ acc,
+                                                                 float* __restrict__ dcol) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    float d0 = 0.f, d1 = 0.f, d2 = 0.f;
+    if (radii[i] > 0) {
+        const float4 c = __ldg(rec + 3 * (size_t)i + 2);
+        const float4 a1 = __ldg(acc + 3 * (size_t)i + 1), a2 = __ldg(acc + 3 * (size_t)i + 2);
+        d0 = signbit(c.y) ? 0.f : a1.z;
+        d1 = signbit(c.z) ? 0.f : a1.w;
+        d2 = signbit(c.w) ? 0.f : a2.x;
+    }
+    dcol[3 * (size_t)i] = d0; dcol[3 * (size_t)i + 1] = d1; dcol[3 * (size_t)i + 2] = d2;
+}
+
 // ------------------------------------------------------------------------------------------------
 // View-parallel exchange (DESIGN.md "Multi-GPU"): dL/dsh of one view is the outer product
 //   dL/dsh[i][k][c] = Y_k(dir(mean_i - campos_v)) * dcol_v[i][c]        (dcol already clamp-masked)
@@ -694,6 +716,12 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
         if (e != cudaSuccess) return e;
     }
     preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop, coop_shift(M3 >> 2), out.dL_dsh ? 1 : 0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_masked_colour_grad(int P, const int32_t* radii, GeomView gv, const float* acc, float* dcol, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    masked_colour_grad_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, gv.rec, reinterpret_cast<const float4*>(acc), dcol);
     return cudaGetLastError();
 }
 

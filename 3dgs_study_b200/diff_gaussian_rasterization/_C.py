@@ -68,6 +68,13 @@ class _Grads(ctypes.Structure):
         "dL_drotations")]
 
 
+_hook_fn_t = ctypes.CFUNCTYPE(None, ctypes.c_void_p)
+
+
+class _BackwardHooks(ctypes.Structure):
+    _fields_ = [("masked_colors", ctypes.c_void_p), ("after_masked_colors", _hook_fn_t), ("ctx", ctypes.c_void_p)]
+
+
 class _StateOut(ctypes.Structure):
     _fields_ = [(n, ctypes.c_void_p) for n in (
         "means2D", "depths", "conic_opacity", "rgb", "tiles_touched", "point_offsets", "keys_sorted",
@@ -98,6 +105,11 @@ def lib():
                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p,
                                          ctypes.c_void_p, ctypes.c_void_p, _alloc_fn_t, ctypes.c_void_p,
                                          ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_backward_ex.restype = ctypes.c_int
+        L.b200splat_backward_ex.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p,
+                                            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, _alloc_fn_t, ctypes.c_void_p,
+                                            ctypes.c_void_p, ctypes.c_void_p]
         L.b200splat_mark_visible.restype = ctypes.c_int
         L.b200splat_mark_visible.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.c_void_p, ctypes.c_void_p]
@@ -235,12 +247,16 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, opacities=None, antialiasing=False,
                                  image_height=None, image_width=None, stage_times: StageTimes = None,
-                                 masked_colors: bool = False, out: Optional[dict] = None):
+                                 masked_colors: bool = False, out: Optional[dict] = None,
+                                 early_colors: Optional[torch.Tensor] = None, after_early_colors=None):
     """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
 
     masked_colors=True (SH mode only): dL_dsh is not produced (None); dL_dcolors is the colour gradient times the
     SH clamp mask, the quantity the view-parallel exchange ships (see sh_grad_from_views).
-    out: optional preallocated fp32 CUDA outputs by name (e.g. views into one flat all-reduce buffer)."""
+    out: optional preallocated fp32 CUDA outputs by name (e.g. views into one flat all-reduce buffer).
+    early_colors ([P,3] fp32 CUDA, SH mode): receives the masked colour gradient right after the render backward;
+    `after_early_colors()` is then called on the host, before the per-Gaussian backward is enqueued, so the caller
+    can start exchanging the buffer on another stream (b200splat_backward_ex).  Implies no dL_dsh / dL_dcolors."""
     dev = means3D.device
     P = means3D.shape[0]
     dL_dout_color = _f32c(dL_dout_color, "dL_dout_color", dev)
@@ -269,10 +285,15 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             return t.view(shape)
         return torch.empty(shape, dtype=torch.float32, device=dev)
 
-    if masked_colors and sh is None:
-        raise RuntimeError("masked_colors needs shs")
+    if (masked_colors or early_colors is not None) and sh is None:
+        raise RuntimeError("masked_colors / early_colors need shs")
+    if early_colors is not None:
+        if not (early_colors.is_cuda and early_colors.dtype == torch.float32 and early_colors.is_contiguous()
+                and early_colors.numel() == 3 * P):
+            raise RuntimeError("early_colors must be a contiguous fp32 CUDA tensor with 3 P elements")
+        masked_colors = True
     dL_dmeans2D = new("dL_dmeans2D", P, 3)
-    dL_dcolors = new("dL_dcolors", P, 3) if (colors is not None or masked_colors) else None
+    dL_dcolors = new("dL_dcolors", P, 3) if (colors is not None or (masked_colors and early_colors is None)) else None
     dL_dopacity = new("dL_dopacity", P, 1)
     dL_dmeans3D = new("dL_dmeans3D", P, 3)
     dL_dcov3D = new("dL_dcov3D", P, 6) if cov3D_precomp is not None else None
@@ -287,12 +308,25 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     grads = _Grads(_ptr(dL_dmeans2D), _ptr(dL_dcolors), _ptr(dL_dopacity), _ptr(dL_dmeans3D), _ptr(dL_dcov3D),
                    _ptr(dL_dsh), _ptr(dL_dscales), _ptr(dL_drotations))
     ta = _TensorAllocator(dev)
+    hooks, hook_err = None, []
+    if early_colors is not None:
+        def _after(_ctx):
+            try:
+                if after_early_colors is not None:
+                    after_early_colors()
+            except Exception as e:   # re-raised after the C call returns
+                hook_err.append(e)
+        hook_cb = _hook_fn_t(_after)
+        hooks = _BackwardHooks(_ptr(early_colors), hook_cb, None)
     with torch.cuda.device(dev):
-        rc = lib().b200splat_backward(ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer),
-                                      _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(dL_dout_color), None,
-                                      ctypes.addressof(grads), ta.cb, 1,
-                                      ctypes.addressof(stage_times) if stage_times is not None else None,
-                                      _stream_ptr(dev))
+        rc = lib().b200splat_backward_ex(ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer),
+                                         _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(dL_dout_color), None,
+                                         ctypes.addressof(grads), ctypes.addressof(hooks) if hooks is not None else None,
+                                         ta.cb, 1, ctypes.addressof(stage_times) if stage_times is not None else None,
+                                         _stream_ptr(dev))
+    if hook_err:
+        ta.release()
+        raise hook_err[0]
     ta.release()
     if ta.error is not None:
         raise ta.error

@@ -56,7 +56,7 @@ class _CudaBackend:
         import diff_gaussian_rasterization as dgr
         self.C, self.st = dgr._C, step
 
-    def view_fwd_bwd(self, cam, dL, lv, out, on_forward=None):
+    def view_fwd_bwd(self, cam, dL, lv, out, on_forward=None, on_colors=None):
         C, st = self.C, self.st
         R, color, radii, geom, binning, img, _ = C.rasterize_gaussians(
             st.bg, lv.means3D, None, lv.opacities, lv.scales, lv.rotations, st.scale_modifier, None,
@@ -68,7 +68,8 @@ class _CudaBackend:
             st.bg, lv.means3D, radii, None, lv.scales, lv.rotations, st.scale_modifier, None, cam.world_view_transform,
             cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, st.sh_degree, cam.camera_center, geom, R,
             binning, img, False, opacities=lv.opacities, image_height=cam.image_height, image_width=cam.image_width,
-            masked_colors=True, out=out)
+            out={k: v for k, v in out.items() if k != "dL_dcolors"}, early_colors=out["dL_dcolors"],
+            after_early_colors=on_colors)
         return color, radii, g[0]
 
     def sh_grad_from_views(self, means3D, dcols, campos, M, degree):
@@ -103,7 +104,7 @@ class ViewParallelStep:
         self.exchange = exchange
         self.stats_reduced = True
         self.last_radii = None
-        self._flat = None                    # [11 P] rotation 4P | mean 3P | scale 3P | opacity P
+        self._side = None                    # side stream of the factorized exchange
 
     # -- rasterizer call ------------------------------------------------------------------------------
     def _render(self, cam, means2D):
@@ -158,12 +159,45 @@ class ViewParallelStep:
         lv = GaussianParams(*[t.detach() for t in self.leaves])
         P, M = lv.means3D.shape[0], lv.shs.shape[1]
         dev = lv.means3D.device
+        cuda = dev.type == "cuda"
+        G = self.world_size
+        exchange = reduce and G > 1
         self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         flat = torch.empty(11 * P, dtype=torch.float32, device=dev)
         outs = self._flat_views(flat)
         nv = len(cams)
         dcols = torch.empty(nv, P, 3, dtype=torch.float32, device=dev)
         campos = torch.stack([c.camera_center.to(dev).float() for c in cams]).contiguous()
+        box = {}
+
+        def start_sh_exchange():
+            """Runs as soon as the LAST local view's masked colour gradient is enqueued, i.e. before its per-Gaussian
+            backward: the all-gather and the local rebuild of dL/dsh go to a side stream and overlap that kernel."""
+            if cuda:
+                main = torch.cuda.current_stream(dev)
+                if self._side is None:
+                    self._side = torch.cuda.Stream(device=dev)
+                ready = torch.cuda.Event(); ready.record(main)
+                ctx = torch.cuda.stream(self._side)
+                self._side.wait_event(ready)
+            else:
+                import contextlib
+                ctx = contextlib.nullcontext()
+            with ctx:
+                if exchange:
+                    all_dcols = torch.empty(G * nv, P, 3, dtype=torch.float32, device=dev)
+                    all_campos = torch.empty(G * nv, 3, dtype=torch.float32, device=dev)
+                    if cuda:
+                        dcols.record_stream(self._side); campos.record_stream(self._side)
+                    dist.all_gather_into_tensor(all_campos, campos, group=self.group)
+                    dist.all_gather_into_tensor(all_dcols, dcols, group=self.group)
+                    views, cp = [all_dcols[v] for v in range(G * nv)], all_campos
+                else:
+                    views, cp = [dcols[v] for v in range(nv)], campos
+                box["dsh"] = be.sh_grad_from_views(lv.means3D, views, cp, M, self.sh_degree)
+                if cuda:
+                    box["done"] = torch.cuda.Event(); box["done"].record(self._side)
+
         color = None
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
             if k == 0:
@@ -171,7 +205,8 @@ class ViewParallelStep:
             else:
                 tmp = torch.empty_like(flat)
                 tgt = dict(self._flat_views(tmp), dL_dcolors=dcols[k])
-            color, radii, dmeans2D = be.view_fwd_bwd(cam, dL, lv, tgt, on_forward)
+            color, radii, dmeans2D = be.view_fwd_bwd(cam, dL, lv, tgt, on_forward,
+                                                     start_sh_exchange if k == nv - 1 else None)
             if k > 0:
                 flat += tmp
             vis = radii > 0
@@ -179,22 +214,14 @@ class ViewParallelStep:
             self.denom += vis[:, None].to(self.denom.dtype)
             self.max_radii2D = torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype))
             self.last_radii = radii
-        self.stats_reduced = self.world_size == 1
-        if reduce and self.world_size > 1:
-            G = self.world_size
-            all_dcols = torch.empty(G * nv, P, 3, dtype=torch.float32, device=dev)
-            all_campos = torch.empty(G * nv, 3, dtype=torch.float32, device=dev)
-            w_cam = dist.all_gather_into_tensor(all_campos, campos, group=self.group, async_op=True)
-            w_col = dist.all_gather_into_tensor(all_dcols, dcols, group=self.group, async_op=True)
-            w_flat = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-            w_cam.wait(); w_col.wait()
-            # rebuilds the summed SH gradient while the all-reduce of the 11 f32 / Gaussian is still in flight
-            dsh = be.sh_grad_from_views(lv.means3D, [all_dcols[v] for v in range(G * nv)], all_campos, M, self.sh_degree)
-            w_flat.wait()
-        else:
-            dsh = be.sh_grad_from_views(lv.means3D, [dcols[v] for v in range(nv)], campos, M, self.sh_degree)
+        self.stats_reduced = G == 1
+        if exchange:   # the remaining 11 f32 / Gaussian: one flat all-reduce, concurrent with the SH rebuild
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+        if cuda:
+            torch.cuda.current_stream(dev).wait_event(box["done"])
+            box["dsh"].record_stream(torch.cuda.current_stream(dev))
         self.leaves.means3D.grad = outs["dL_dmeans3D"]
-        self.leaves.shs.grad = dsh
+        self.leaves.shs.grad = box["dsh"]
         self.leaves.opacities.grad = outs["dL_dopacity"].view_as(self.leaves.opacities)
         self.leaves.scales.grad = outs["dL_dscales"]
         self.leaves.rotations.grad = outs["dL_drotations"]

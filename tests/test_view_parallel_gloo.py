@@ -79,7 +79,7 @@ class _TorchBackend:
     def __init__(self, sh_degree, bg):
         self.D, self.bg = sh_degree, bg
 
-    def view_fwd_bwd(self, cam, dL, lv, out, on_forward=None):
+    def view_fwd_bwd(self, cam, dL, lv, out, on_forward=None, on_colors=None):
         leaves = vp.GaussianParams(*[t.detach().clone().requires_grad_(True) for t in lv])
         m2d = torch.zeros_like(leaves.means3D, requires_grad=True)
         color, radii = _oracle_rasterize(cam, leaves, m2d, self.D, self.bg, 1.0)
@@ -87,6 +87,8 @@ class _TorchBackend:
         out["dL_dmeans3D"].copy_(leaves.means3D.grad); out["dL_dopacity"].copy_(leaves.opacities.grad.view(-1, 1))
         out["dL_dscales"].copy_(leaves.scales.grad); out["dL_drotations"].copy_(leaves.rotations.grad)
         out["dL_dcolors"].copy_(leaves.shs.grad[:, 0, :] / 0.28209479177387814)   # Y_0 is constant: dcol = dL/dsh_0 / Y_0
+        if on_colors is not None:
+            on_colors()
         return color.detach(), radii, m2d.grad
 
     def sh_grad_from_views(self, means3D, dcols, campos, M, degree):
