@@ -272,6 +272,15 @@ int b200splat_sh_grad_from_views(int32_t P, int32_t M, int32_t sh_degree, const 
     return B200SPLAT_OK;
 }
 
+int b200splat_densify_stats(int32_t P, const float* dL_dmeans2D, const int32_t* radii, float* xyz_gradient_accum,
+                            float* denom, float* max_radii2D, void* stream_) {
+    if (P < 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad P");
+    if (P == 0) return B200SPLAT_OK;
+    if (!dL_dmeans2D || !radii || !xyz_gradient_accum || !denom || !max_radii2D) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
+    CU(launch_densify_stats(P, dL_dmeans2D, radii, xyz_gradient_accum, denom, max_radii2D, (cudaStream_t)stream_), "densify_stats");
+    return B200SPLAT_OK;
+}
+
 int b200splat_render_stats(int32_t P, int32_t width, int32_t height, int32_t num_rendered, const void* geom,
                            const void* binning, const void* image, uint64_t* out14, void* stream_) {
     if (!out14 || P < 0 || width <= 0 || height <= 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad arguments");

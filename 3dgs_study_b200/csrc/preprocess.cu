@@ -638,6 +638,22 @@ __global__ void __launch_bounds__(PRE_THREADS) sh_grad_from_views_kernel(int P, 
     }
 }
 
+// Densification statistics of one view in ONE pass (the reference does this with five torch ops,
+// /root/reference/scene/gaussian_model.py:576-581 and /root/reference/train.py:127):
+//   accum[i] += ||dL_dmeans2D[i, :2]||  and  denom[i] += 1   for visible Gaussians,  max_radii[i] = max(., radii[i])
+__global__ void densify_stats_kernel(int P, const float* __restrict__ dmeans2D, const int32_t* __restrict__ radii,
+                                     float* __restrict__ accum, float* __restrict__ denom, float* __restrict__ max_radii) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const int r = radii[i];
+    if (r > 0) {
+        const float gx = dmeans2D[3 * (size_t)i], gy = dmeans2D[3 * (size_t)i + 1];
+        accum[i] += sqrtf(gx * gx + gy * gy);
+        denom[i] += 1.0f;
+        max_radii[i] = fmaxf(max_radii[i], (float)r);
+    }
+}
+
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
                                     uint8_t* __restrict__ present) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -740,6 +756,13 @@ cudaError_t launch_sh_grad_from_views(int P, int M, int D, const float* means3D,
     }
     sh_grad_from_views_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(P, M, D, means3D, vg, campos, dL_dsh,
                                                                                           coop, coop_shift(M3 >> 2));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_densify_stats(int P, const float* dmeans2D, const int32_t* radii, float* accum, float* denom,
+                                 float* max_radii, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    densify_stats_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, dmeans2D, radii, accum, denom, max_radii);
     return cudaGetLastError();
 }
 

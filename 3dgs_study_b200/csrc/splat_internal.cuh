@@ -89,6 +89,8 @@ cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_
 cudaError_t launch_masked_colour_grad(int P, const int32_t* radii, GeomView gv, const float* acc, float* dcol, cudaStream_t s);
 cudaError_t launch_sh_grad_from_views(int P, int M, int D, const float* means3D, int n_views, const float* const* dcol,
                                       const float* campos, float* dL_dsh, cudaStream_t s);
+cudaError_t launch_densify_stats(int P, const float* dmeans2D, const int32_t* radii, float* accum, float* denom,
+                                 float* max_radii, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
 cudaError_t launch_export_geom(int P, const int32_t* radii, GeomView gv, const b200splat_state_out& o, cudaStream_t s);
 cudaError_t launch_export_binning(int P, int R, GeomView gv, BinView bv, const b200splat_state_out& o, cudaStream_t s);

@@ -117,6 +117,8 @@ def lib():
         L.b200splat_sh_grad_from_views.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p,
                                                    ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                                    ctypes.c_void_p]
+        L.b200splat_densify_stats.restype = ctypes.c_int
+        L.b200splat_densify_stats.argtypes = [ctypes.c_int32] + [ctypes.c_void_p] * 6
         L.b200splat_render_stats.restype = ctypes.c_int
         L.b200splat_render_stats.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -379,6 +381,21 @@ def sh_grad_from_views(means3D, dcols, campos, M: int, degree: int, out: Optiona
                                                 _stream_ptr(dev))
     _check(rc, "sh_grad_from_views")
     return dL_dsh
+
+
+def densify_stats(dL_dmeans2D, radii, xyz_gradient_accum, denom, max_radii2D):
+    """In place, one kernel: accum += ||dL_dmeans2D[:, :2]||, denom += 1 (visible only), max_radii2D = max(., radii)."""
+    dev = radii.device
+    P = radii.shape[0]
+    for t, n in ((dL_dmeans2D, 3 * P), (xyz_gradient_accum, P), (denom, P), (max_radii2D, P)):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == n):
+            raise RuntimeError("densify_stats: contiguous fp32 CUDA tensors of matching size required")
+    if radii.dtype != torch.int32:
+        raise RuntimeError("radii must be int32")
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_densify_stats(P, _ptr(dL_dmeans2D), _ptr(radii), _ptr(xyz_gradient_accum), _ptr(denom),
+                                           _ptr(max_radii2D), _stream_ptr(dev))
+    _check(rc, "densify_stats")
 
 
 def render_stats(P, W, H, num_rendered, geomBuffer, binningBuffer, imageBuffer):

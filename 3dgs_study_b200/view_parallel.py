@@ -106,6 +106,18 @@ class ViewParallelStep:
         self.last_radii = None
         self._side = None                    # side stream of the factorized exchange
 
+    def _accumulate_stats(self, dmeans2D, radii):
+        """Densification statistics of one view (reference semantics: norm per view, then summed)."""
+        if dmeans2D.is_cuda and self._rasterize is None and self._backend is None:
+            import diff_gaussian_rasterization as dgr
+            dgr._C.densify_stats(dmeans2D.contiguous(), radii, self.xyz_gradient_accum.view(-1), self.denom.view(-1),
+                                 self.max_radii2D)
+            return
+        vis = radii > 0
+        self.xyz_gradient_accum += torch.norm(dmeans2D[:, :2], dim=-1, keepdim=True) * vis[:, None]
+        self.denom += vis[:, None].to(self.denom.dtype)
+        self.max_radii2D = torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype))
+
     # -- rasterizer call ------------------------------------------------------------------------------
     def _render(self, cam, means2D):
         if self._rasterize is not None:
@@ -138,10 +150,7 @@ class ViewParallelStep:
                 on_forward(color.detach())
             torch.autograd.backward([color], [dL])
             with torch.no_grad():
-                vis = radii > 0
-                self.xyz_gradient_accum += torch.norm(means2D.grad[:, :2], dim=-1, keepdim=True) * vis[:, None]
-                self.denom += vis[:, None].to(self.denom.dtype)
-                self.max_radii2D = torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype))
+                self._accumulate_stats(means2D.grad, radii)
             self.last_radii = radii
         if reduce and self.world_size > 1:
             self.all_reduce_grads()
@@ -176,27 +185,39 @@ class ViewParallelStep:
             if cuda:
                 main = torch.cuda.current_stream(dev)
                 if self._side is None:
-                    self._side = torch.cuda.Stream(device=dev)
+                    # collectives on a HIGH-priority stream (their few CTAs must get SM slots while a full-grid
+                    # kernel is running), the rebuild kernel on a normal-priority one (it must not starve them)
+                    self._side = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
+                comm, rebuild = self._side
                 ready = torch.cuda.Event(); ready.record(main)
-                ctx = torch.cuda.stream(self._side)
-                self._side.wait_event(ready)
+                comm.wait_event(ready)
+                with torch.cuda.stream(comm):
+                    if exchange:
+                        all_dcols = torch.empty(G * nv, P, 3, dtype=torch.float32, device=dev)
+                        all_campos = torch.empty(G * nv, 3, dtype=torch.float32, device=dev)
+                        dcols.record_stream(comm); campos.record_stream(comm)
+                        dist.all_gather_into_tensor(all_campos, campos, group=self.group)
+                        dist.all_gather_into_tensor(all_dcols, dcols, group=self.group)
+                        all_dcols.record_stream(rebuild); all_campos.record_stream(rebuild)
+                        views, cp = [all_dcols[v] for v in range(G * nv)], all_campos
+                    else:
+                        views, cp = [dcols[v] for v in range(nv)], campos
+                        dcols.record_stream(rebuild); campos.record_stream(rebuild)
+                    gathered = torch.cuda.Event(); gathered.record(comm)
+                rebuild.wait_event(gathered)
+                with torch.cuda.stream(rebuild):
+                    box["dsh"] = be.sh_grad_from_views(lv.means3D, views, cp, M, self.sh_degree)
+                    box["done"] = torch.cuda.Event(); box["done"].record(rebuild)
             else:
-                import contextlib
-                ctx = contextlib.nullcontext()
-            with ctx:
                 if exchange:
                     all_dcols = torch.empty(G * nv, P, 3, dtype=torch.float32, device=dev)
                     all_campos = torch.empty(G * nv, 3, dtype=torch.float32, device=dev)
-                    if cuda:
-                        dcols.record_stream(self._side); campos.record_stream(self._side)
                     dist.all_gather_into_tensor(all_campos, campos, group=self.group)
                     dist.all_gather_into_tensor(all_dcols, dcols, group=self.group)
                     views, cp = [all_dcols[v] for v in range(G * nv)], all_campos
                 else:
                     views, cp = [dcols[v] for v in range(nv)], campos
                 box["dsh"] = be.sh_grad_from_views(lv.means3D, views, cp, M, self.sh_degree)
-                if cuda:
-                    box["done"] = torch.cuda.Event(); box["done"].record(self._side)
 
         color = None
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
@@ -209,15 +230,14 @@ class ViewParallelStep:
                                                      start_sh_exchange if k == nv - 1 else None)
             if k > 0:
                 flat += tmp
-            vis = radii > 0
-            self.xyz_gradient_accum += torch.norm(dmeans2D[:, :2], dim=-1, keepdim=True) * vis[:, None]
-            self.denom += vis[:, None].to(self.denom.dtype)
-            self.max_radii2D = torch.maximum(self.max_radii2D, radii.to(self.max_radii2D.dtype))
+            if k == nv - 1:
+                flat_done = self._reduce_flat(flat, exchange, cuda, dev)   # before the statistics: off the critical path
+            self._accumulate_stats(dmeans2D, radii)
             self.last_radii = radii
         self.stats_reduced = G == 1
-        if exchange:   # the remaining 11 f32 / Gaussian: one flat all-reduce, concurrent with the SH rebuild
-            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
         if cuda:
+            if flat_done is not None:
+                torch.cuda.current_stream(dev).wait_event(flat_done)
             torch.cuda.current_stream(dev).wait_event(box["done"])
             box["dsh"].record_stream(torch.cuda.current_stream(dev))
         self.leaves.means3D.grad = outs["dL_dmeans3D"]
@@ -226,6 +246,21 @@ class ViewParallelStep:
         self.leaves.scales.grad = outs["dL_dscales"]
         self.leaves.rotations.grad = outs["dL_drotations"]
         return color
+
+    def _reduce_flat(self, flat, exchange, cuda, dev):
+        import torch.distributed as dist
+        if exchange:   # the remaining 11 f32 / Gaussian: one flat all-reduce, concurrent with the SH rebuild
+            if cuda:
+                main, comm = torch.cuda.current_stream(dev), self._side[0]
+                ev = torch.cuda.Event(); ev.record(main)
+                comm.wait_event(ev)
+                with torch.cuda.stream(comm):
+                    flat.record_stream(comm)
+                    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+                    ev2 = torch.cuda.Event(); ev2.record(comm)
+                return ev2                    # the caller makes the main stream wait at the END of the step
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+        return None
 
     def reduce_densification_stats(self):
         """Factorized mode keeps xyz_gradient_accum / denom / max_radii2D rank-local; call this before they are

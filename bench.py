@@ -140,7 +140,10 @@ def dist_setup(n):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29511")
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
+        # NCCL on a HIGH-PRIORITY stream: the exchange's all-gather is launched while the per-Gaussian backward still
+        # fills every SM; at equal priority its CTAs would only be scheduled once that kernel has drained
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local), pg_options=opts)
     return rank, world, local
 
 
@@ -263,6 +266,30 @@ def run_ours(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_e2e = float(t.item())
     e2e_value = world * 1000.0 / (ms_e2e / a.steps)
+
+    # ---------------- optional: GPU timeline of 3 steps (diagnostic; BENCH_TRACE=1) ----------------
+    if os.environ.get("BENCH_TRACE"):
+        from torch.profiler import profile, ProfilerActivity
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(3):
+                step_resident(i)
+            torch.cuda.synchronize()
+        if rank in (0, world - 1):
+            tr = os.path.join(ROOT, "gpurun_out", f"trace_n{world}_r{rank}.json")
+            prof.export_chrome_trace(tr)
+            ev = [e for e in json.load(open(tr))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset")]
+            ev.sort(key=lambda e: e["ts"])
+            t0 = ev[0]["ts"]
+            with open(os.path.join(ROOT, "gpurun_out", f"timeline_n{world}_r{rank}.txt"), "w") as f:
+                for e in ev:
+                    if e["dur"] >= 8:
+                        f.write(f"{e['ts'] - t0:10.1f} us  dur {e['dur']:8.1f}  stream {e['args'].get('stream')}  {e['name'][:80]}\n")
+            os.remove(tr)
+        if world > 1:
+            dist.barrier()
 
     # ---------------- per-stage times + roofline (rank 0, CUDA events inside the library) ----------
     stages, roof, launches, stats = {}, None, None, {}

@@ -209,6 +209,14 @@ B200SPLAT_API int b200splat_sh_grad_from_views(int32_t P, int32_t M, int32_t sh_
                            int32_t n_views, const float* const* dcol, const float* campos,
                            float* dL_dsh, void* stream);
 
+/* Densification statistics of one rendered view, fused (consumers of the operator's outputs in the reference:
+ * add_densification_stats, /root/reference/scene/gaussian_model.py:576-581, and the max_radii2D update,
+ * /root/reference/train.py:127).  For every Gaussian with radii > 0:
+ *   xyz_gradient_accum[i] += ||dL_dmeans2D[i, :2]||, denom[i] += 1, max_radii2D[i] = max(max_radii2D[i], radii[i]).
+ * All arrays are device pointers of P (dL_dmeans2D: [P,3]) elements. */
+B200SPLAT_API int b200splat_densify_stats(int32_t P, const float* dL_dmeans2D, const int32_t* radii,
+                           float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
+
 /* Inspection: workload counters of the render stage of the view whose forward state is given, written
  * to out14 (device, 14 x u64): [0..8] (tile, Gaussian) pairs by number of 8x4-pixel sub-blocks the splat's
  * {alpha >= 1/255} box reaches, [9] pairs visited, [10] pixel evaluations, [11] of those with an exp,
