@@ -583,7 +583,7 @@ struct ViewGrads {
 
 __global__ void __launch_bounds__(PRE_THREADS) sh_grad_from_views_kernel(int P, int M, int D, const float* __restrict__ means3D,
                                                                          ViewGrads vg, const float* __restrict__ campos,
-                                                                         float* __restrict__ dL_dsh, int coop, int qs) {
+                                                                         float* __restrict__ dL_dsh, int coop, int qs, int dc_off4, int vec_ok) {
     extern __shared__ float4 s_sh4[];
     __shared__ float s_cam[B200SPLAT_MAX_VIEWS * 3];
     if (threadIdx.x < vg.n * 3) s_cam[threadIdx.x] = campos[threadIdx.x];
@@ -592,14 +592,30 @@ __global__ void __launch_bounds__(PRE_THREADS) sh_grad_from_views_kernel(int P, 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool in_range = i < P;
     const int M3 = 3 * M, nb = (D + 1) * (D + 1);
+    const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
+    // Colour gradients of the warp's 32 Gaussians, all views: 384 contiguous bytes per view, fetched as 24 16-byte
+    // loads per view, all views in flight together (what matters when dcol[v] is a PEER pointer: one NVLink round
+    // trip per warp instead of 3 x n dependent 4-byte loads per lane), then handed to the lanes through shared memory.
+    float* s_dc = reinterpret_cast<float*>(s_sh4 + dc_off4) + (size_t)warp * vg.n * 96;
+    const bool full = vec_ok && i0 + 32 <= P;
+    if (full) {
+        if (lane < 24) {
+#pragma unroll 4
+            for (int v = 0; v < vg.n; v++)
+                reinterpret_cast<float4*>(s_dc + v * 96)[lane] = reinterpret_cast<const float4*>(vg.dcol[v] + 3 * (size_t)i0)[lane];
+        }
+    } else if (in_range) {
+        for (int v = 0; v < vg.n; v++)
+            for (int c = 0; c < 3; c++) s_dc[v * 96 + 3 * lane + c] = vg.dcol[v][3 * (size_t)i + c];
+    }
+    __syncwarp();
     float acc[48];
 #pragma unroll
     for (int k = 0; k < 48; k++) acc[k] = 0.f;
     if (in_range) {
         const float x = __ldg(means3D + 3 * i), y = __ldg(means3D + 3 * i + 1), z = __ldg(means3D + 3 * i + 2);
         for (int v = 0; v < vg.n; v++) {
-            const float* dc = vg.dcol[v] + 3 * (size_t)i;
-            const float g0 = dc[0], g1 = dc[1], g2 = dc[2];
+            const float g0 = s_dc[v * 96 + 3 * lane], g1 = s_dc[v * 96 + 3 * lane + 1], g2 = s_dc[v * 96 + 3 * lane + 2];
             if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;     // culled or clamped in that view
             const float ddx = csub(x, s_cam[3 * v]), ddy = csub(y, s_cam[3 * v + 1]), ddz = csub(z, s_cam[3 * v + 2]);
             const float len = csqrt(cfma(ddz, ddz, cfma(ddy, ddy, cmul(ddx, ddx))));
@@ -623,7 +639,6 @@ __global__ void __launch_bounds__(PRE_THREADS) sh_grad_from_views_kernel(int P, 
         for (int kv = 0; kv < 12; kv++)
             if (kv < nq) w[kv] = make_float4(acc[4 * kv], acc[4 * kv + 1], acc[4 * kv + 2], acc[4 * kv + 3]);
         __syncwarp();
-        const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
         float4* dst = reinterpret_cast<float4*>(dL_dsh) + (size_t)i0 * nq;
         const int rows = min(32, P - i0);
         const int q = lane & ((1 << qs) - 1), rstep = 32 >> qs;
@@ -746,16 +761,22 @@ cudaError_t launch_sh_grad_from_views(int P, int M, int D, const float* means3D,
     if (P == 0) return cudaSuccess;
     ViewGrads vg;
     vg.n = n_views;
-    for (int v = 0; v < B200SPLAT_MAX_VIEWS; v++) vg.dcol[v] = v < n_views ? dcol[v] : nullptr;
+    int vec_ok = 1;   // 16-byte loads need every view's array 16-byte aligned
+    for (int v = 0; v < B200SPLAT_MAX_VIEWS; v++) {
+        vg.dcol[v] = v < n_views ? dcol[v] : nullptr;
+        if (v < n_views && (reinterpret_cast<uintptr_t>(dcol[v]) & 15u)) vec_ok = 0;
+    }
     const int M3 = 3 * M;
     const int coop = (M > 0 && (M3 & 3) == 0 && M <= 16) ? 1 : 0;
-    const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
+    const size_t rows_bytes = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
+    const size_t smem = rows_bytes + (size_t)(PRE_THREADS / 32) * n_views * 96 * sizeof(float);
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(sh_grad_from_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
     sh_grad_from_views_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(P, M, D, means3D, vg, campos, dL_dsh,
-                                                                                          coop, coop_shift(M3 >> 2));
+                                                                                          coop, coop_shift(M3 >> 2),
+                                                                                          (int)(rows_bytes / 16), vec_ok);
     return cudaGetLastError();
 }
 

@@ -81,7 +81,7 @@ class ViewParallelStep:
 
     def __init__(self, params: GaussianParams, sh_degree: int, bg: torch.Tensor, world_size: int = 1,
                  process_group=None, rasterize: Optional[Callable] = None, scale_modifier: float = 1.0,
-                 exchange: Optional[str] = None, backend=None):
+                 exchange: Optional[str] = None, backend=None, peer_memory: Optional[bool] = None):
         self.world_size = world_size
         self.group = process_group
         self.sh_degree = sh_degree
@@ -104,7 +104,16 @@ class ViewParallelStep:
         self.exchange = exchange
         self.stats_reduced = True
         self.last_radii = None
-        self._side = None                    # side stream of the factorized exchange
+        self._side = None                    # side streams of the factorized exchange
+        # peer_memory (factorized, CUDA, world_size > 1): exchange through NVLink peer / multicast mappings
+        # (torch symmetric memory) instead of NCCL -- the SH rebuild kernel then READS every peer's colour gradients
+        # itself (all-gather fused into the kernel) and the 11 f32 / Gaussian go through an in-switch (NVLS
+        # multimem) all-reduce.  True = require it, None = try and fall back to NCCL, False (default) = NCCL.
+        # Measured on 8 x B200 (tools/comm_bench.py, profiles/): the exchange is bound by NVLink wire time either
+        # way (all-gather 0.43 ms + all-reduce 0.40 ms vs fused peer rebuild 0.58 ms + multimem all-reduce 0.34 ms)
+        # and the NCCL flavour overlaps better with the per-Gaussian backward, so NCCL is the default.
+        self.peer_memory = False if peer_memory is None else peer_memory
+        self._symm = None
 
     def _accumulate_stats(self, dmeans2D, radii):
         """Densification statistics of one view (reference semantics: norm per view, then summed)."""
@@ -157,6 +166,35 @@ class ViewParallelStep:
         return color.detach()
 
     # -- factorized exchange --------------------------------------------------------------------------------
+    def _setup_symm(self, P, nv, dev):
+        """Symmetric (peer-mapped) buffers: flat gradients [11 P, padded] and masked colour gradients [nv, P, 3]."""
+        if self._symm is not None:
+            return self._symm if self._symm.get("nv") == nv else None
+        if not self.peer_memory or self.world_size == 1 or dev.type != "cuda" or self._backend is not None:
+            self._symm = {}
+            return None
+        try:
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm_mem
+            group = self.group if self.group is not None else dist.group.WORLD
+            pad = 1024 * self.world_size
+            nflat = (11 * P + pad - 1) // pad * pad
+            flat = symm_mem.empty(nflat, dtype=torch.float32, device=dev)
+            hf = symm_mem.rendezvous(flat, group)
+            dcol = symm_mem.empty(nv * P * 3, dtype=torch.float32, device=dev)
+            hd = symm_mem.rendezvous(dcol, group)
+            flat.zero_()
+            if not getattr(hf, "multicast_ptr", 0):
+                raise RuntimeError("no multicast mapping")
+            self._symm = {"nv": nv, "flat": flat, "dcol": dcol.view(nv, P, 3), "hd": hd, "group_name": group.group_name,
+                          "ptrs": [int(p) for p in hd.buffer_ptrs]}
+        except Exception as e:          # no peer mappings on this system
+            if self.peer_memory is True:
+                raise
+            self._symm = {"error": repr(e)}
+            return None
+        return self._symm
+
     def _flat_views(self, flat):
         P = self.leaves.means3D.shape[0]
         return {"dL_drotations": flat[0:4 * P].view(P, 4), "dL_dmeans3D": flat[4 * P:7 * P].view(P, 3),
@@ -172,25 +210,53 @@ class ViewParallelStep:
         G = self.world_size
         exchange = reduce and G > 1
         self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
-        flat = torch.empty(11 * P, dtype=torch.float32, device=dev)
-        outs = self._flat_views(flat)
         nv = len(cams)
-        dcols = torch.empty(nv, P, 3, dtype=torch.float32, device=dev)
+        sy = self._setup_symm(P, nv, dev) if exchange else None
+        if sy:
+            flat, dcols = sy["flat"], sy["dcol"]          # peer-mapped, persistent: valid until the next step
+        else:
+            flat = torch.empty(11 * P, dtype=torch.float32, device=dev)
+            dcols = torch.empty(nv, P, 3, dtype=torch.float32, device=dev)
+        outs = self._flat_views(flat)
         campos = torch.stack([c.camera_center.to(dev).float() for c in cams]).contiguous()
-        box = {}
+        box = {"symm": sy}
+        if cuda and self._side is None:
+            # collectives on a HIGH-priority stream (their few CTAs must get SM slots while a full-grid kernel is
+            # running), the rebuild kernel on a normal-priority one (it must not starve them)
+            self._side = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
+        if sy:   # camera centres of all views: tiny, gathered at step start, off the critical path
+            main, comm = torch.cuda.current_stream(dev), self._side[0]
+            ev0 = torch.cuda.Event(); ev0.record(main)
+            comm.wait_event(ev0)
+            with torch.cuda.stream(comm):
+                campos.record_stream(comm)
+                box["all_campos"] = torch.empty(G * nv, 3, dtype=torch.float32, device=dev)
+                dist.all_gather_into_tensor(box["all_campos"], campos, group=self.group)
 
         def start_sh_exchange():
             """Runs as soon as the LAST local view's masked colour gradient is enqueued, i.e. before its per-Gaussian
             backward: the all-gather and the local rebuild of dL/dsh go to a side stream and overlap that kernel."""
             if cuda:
                 main = torch.cuda.current_stream(dev)
-                if self._side is None:
-                    # collectives on a HIGH-priority stream (their few CTAs must get SM slots while a full-grid
-                    # kernel is running), the rebuild kernel on a normal-priority one (it must not starve them)
-                    self._side = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
                 comm, rebuild = self._side
                 ready = torch.cuda.Event(); ready.record(main)
                 comm.wait_event(ready)
+                if box["symm"]:
+                    # peer-memory path: barrier (every rank's colour gradients are written), then the rebuild kernel
+                    # loads all G x nv views straight from the peers' memory over NVLink, then a second barrier
+                    # (every rank has finished reading) before anyone may overwrite its buffer in the next step
+                    sy_ = box["symm"]
+                    with torch.cuda.stream(comm):
+                        sy_["hd"].barrier(channel=0)
+                        gathered = torch.cuda.Event(); gathered.record(comm)
+                    rebuild.wait_event(gathered)
+                    with torch.cuda.stream(rebuild):
+                        box["all_campos"].record_stream(rebuild)
+                        ptrs = [sy_["ptrs"][r] + v * P * 12 for r in range(G) for v in range(nv)]
+                        box["dsh"] = be.sh_grad_from_views(lv.means3D, ptrs, box["all_campos"], M, self.sh_degree)
+                        sy_["hd"].barrier(channel=1)
+                        box["done"] = torch.cuda.Event(); box["done"].record(rebuild)
+                    return
                 with torch.cuda.stream(comm):
                     if exchange:
                         all_dcols = torch.empty(G * nv, P, 3, dtype=torch.float32, device=dev)
@@ -255,8 +321,11 @@ class ViewParallelStep:
                 ev = torch.cuda.Event(); ev.record(main)
                 comm.wait_event(ev)
                 with torch.cuda.stream(comm):
-                    flat.record_stream(comm)
-                    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+                    if self._symm and self._symm.get("flat") is flat:
+                        torch.ops.symm_mem.multimem_all_reduce_(flat, "sum", self._symm["group_name"])   # in-switch (NVLS)
+                    else:
+                        flat.record_stream(comm)
+                        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
                     ev2 = torch.cuda.Event(); ev2.record(comm)
                 return ev2                    # the caller makes the main stream wait at the END of the step
             dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)

@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--exchange", default=None, choices=["allreduce", "factorized"],
                     help="N>1 gradient exchange (default: factorized); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
+    ap.add_argument("--peer-memory", action="store_true", help="factorized exchange through NVLink peer mappings (fused rebuild kernel + multimem all-reduce) instead of NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-tile-stride", type=int, default=16, help="CPU legs render 1/stride of the tiles")
     ap.add_argument("--stages", action="store_true", help="print the per-stage table to stderr")
@@ -171,7 +172,7 @@ def run_ours(a):
     dL_cpu = synth.make_grad_image(W, H).pin_memory()
     dL = dL_cpu.to(dev)
     params = vp.GaussianParams(scene.means3D, scene.shs, scene.opacities, scene.scales, scene.rotations)
-    stepper = vp.ViewParallelStep(params, D, bg, world_size=world, exchange=a.exchange)
+    stepper = vp.ViewParallelStep(params, D, bg, world_size=world, exchange=a.exchange, peer_memory="try" if a.peer_memory else False)
 
     def view_of(step):   # rank r renders view (step * world + r) of the orbit
         return (step * world + rank) % n_views

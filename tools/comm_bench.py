@@ -52,6 +52,31 @@ try:
                 all_dcol[r].view(-1).copy_(hdl.get_buffer(r, (P * 3,), torch.float32))
     timeit(f"pull all peers {world - 1} x 36 MB (copies)", pull_all, nbytes=(world - 1) * P * 12)
     hdl.barrier()
+    gname = dist.group.WORLD.group_name
+    fs = symm.empty(11 * P, dtype=torch.float32, device=dev); symm.rendezvous(fs, dist.group.WORLD); fs.copy_(flat)
+    for name in ("multimem_all_reduce_", "two_shot_all_reduce_"):
+        try:
+            op = getattr(torch.ops.symm_mem, name)
+            timeit(f"symm_mem.{name} 11P f32 (132 MB)", lambda: op(fs, "sum", gname), nbytes=11 * P * 4)
+        except Exception as e:
+            if rank == 0: print(name, "failed:", repr(e)[:200], flush=True)
+    try:
+        ag_out = symm.empty(world * P * 3, dtype=torch.float32, device=dev); symm.rendezvous(ag_out, dist.group.WORLD)
+        timeit("symm_mem.multimem_all_gather_out 36 MB/rank", lambda: torch.ops.symm_mem.multimem_all_gather_out(t, gname, ag_out), nbytes=world * P * 12)
+    except Exception as e:
+        if rank == 0: print("multimem_all_gather_out failed:", repr(e)[:200], flush=True)
+    # fused all-gather -> SH rebuild: the rebuild kernel reads every peer's [P,3] colour gradients over NVLink
+    import importlib
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    pkg = importlib.import_module("3dgs_study_b200"); pkg.ensure_on_path()
+    import diff_gaussian_rasterization as dgr
+    means = torch.randn(P, 3, device=dev); cp = torch.randn(world, 3, device=dev) * 5
+    dsh = torch.empty(P, 16, 3, device=dev)
+    timeit("sh_grad_from_views, LOCAL copies of 8 views", lambda: dgr._C.sh_grad_from_views(means, [all_dcol[v] for v in range(world)], cp, 16, 3, out=dsh), nbytes=P * 192)
+    timeit("sh_grad_from_views, PEER pointers (fused all-gather)", lambda: dgr._C.sh_grad_from_views(means, ptrs, cp, 16, 3, out=dsh), nbytes=(world - 1) * P * 12)
+    def fused_with_barriers():
+        hdl.barrier(channel=1); dgr._C.sh_grad_from_views(means, ptrs, cp, 16, 3, out=dsh); hdl.barrier(channel=2)
+    timeit("  same + symm_mem barriers before/after", fused_with_barriers)
 except Exception as e:
     if rank == 0:
         print("symm_mem unavailable:", repr(e)[:300], flush=True)
