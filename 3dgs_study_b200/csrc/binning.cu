@@ -125,13 +125,6 @@ ImgView carve_image(void* base, int W, int H) {
     v.counters = (unsigned int*)(b + off); off += align256(64 * sizeof(unsigned int));
     const size_t Tn = T > 0 ? T : 1;
     v.tile_order = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
-    v.tile_len = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
-    v.tile_iota = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
-    v.tile_len_sorted = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
-    v.order_tmp_bytes = 0;
-    cub::DeviceRadixSort::SortPairsDescending(nullptr, v.order_tmp_bytes, (uint32_t*)nullptr, (uint32_t*)nullptr,
-                                              (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Tn, 0, 32);
-    v.order_tmp = (void*)(b + off); off += align256(v.order_tmp_bytes);
     v.total = off;
     return v;
 }
@@ -181,26 +174,62 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int P, int gx, 
     }
 }
 
+// identifyTileRanges: each thread owns EPT consecutive sorted keys (one 16-byte load) plus the key before them.
 template <typename KeyT>
 __global__ void __launch_bounds__(256) identify_tile_ranges_kernel(int R, const KeyT* __restrict__ keys,
                                                                    int2* __restrict__ ranges) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= R) return;
-    const uint32_t t = (uint32_t)keys[j];
-    if (j == 0) ranges[t].x = 0;
-    else {
-        const uint32_t tp = (uint32_t)keys[j - 1];
-        if (tp != t) { ranges[tp].y = j; ranges[t].x = j; }
+    constexpr int EPT = 16 / sizeof(KeyT);
+    const int j0 = (blockIdx.x * blockDim.x + threadIdx.x) * EPT;
+    if (j0 >= R) return;
+    KeyT k[EPT];
+    if (j0 + EPT <= R) {
+        *reinterpret_cast<uint4*>(k) = *reinterpret_cast<const uint4*>(keys + j0);
+    } else {
+#pragma unroll
+        for (int e = 0; e < EPT; e++) k[e] = j0 + e < R ? keys[j0 + e] : (KeyT)0;
     }
-    if (j == R - 1) ranges[t].y = R;
+    uint32_t prev = j0 > 0 ? (uint32_t)keys[j0 - 1] : 0u;
+    if (j0 == 0) ranges[(uint32_t)k[0]].x = 0;
+#pragma unroll
+    for (int e = 0; e < EPT; e++) {
+        const int j = j0 + e;
+        if (j < R) {
+            const uint32_t t = (uint32_t)k[e];
+            if (j > 0 && t != prev) { ranges[prev].y = j; ranges[t].x = j; }
+            if (j == R - 1) ranges[t].y = R;
+            prev = t;
+        }
+    }
 }
 
-__global__ void tile_len_kernel(int T, const int2* __restrict__ ranges, uint32_t* __restrict__ len, uint32_t* __restrict__ iota) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= T) return;
-    const int2 r = ranges[t];
-    len[t] = (uint32_t)(r.y - r.x);
-    iota[t] = (uint32_t)t;
+// Tile order for the render kernels: longest list first, to the nearest half power of two (the order only
+// shapes the schedule, never the result).  One block: bucket = 2 log2(len) rounded down, histogram, scan,
+// scatter -- a few microseconds instead of a general sort.
+__global__ void __launch_bounds__(1024) tile_order_kernel(int T, const int2* __restrict__ ranges, uint32_t* __restrict__ order) {
+    __shared__ unsigned s_count[64], s_base[64];
+    const int t = threadIdx.x;
+    if (t < 64) s_count[t] = 0;
+    __syncthreads();
+    auto bucket = [](unsigned len) -> int {
+        if (len == 0) return 63;
+        const int lg = 31 - __clz(len);
+        const int half = (lg > 0 && ((len >> (lg - 1)) & 1u)) ? 1 : 0;
+        return 62 - (2 * lg + half);          // longest lists -> smallest bucket index
+    };
+    for (int i = t; i < T; i += blockDim.x) {
+        const int2 r = ranges[i];
+        atomicAdd(&s_count[bucket((unsigned)(r.y - r.x))], 1u);
+    }
+    __syncthreads();
+    if (t == 0) {
+        unsigned run = 0;
+        for (int b = 0; b < 64; b++) { s_base[b] = run; run += s_count[b]; }
+    }
+    __syncthreads();
+    for (int i = t; i < T; i += blockDim.x) {
+        const int2 r = ranges[i];
+        order[atomicAdd(&s_base[bucket((unsigned)(r.y - r.x))], 1u)] = (uint32_t)i;
+    }
 }
 
 template <typename KeyT>
@@ -262,19 +291,15 @@ cudaError_t launch_ranges(BinView bv, int R, ImgView iv, int W, int H, cudaStrea
     if (e != cudaSuccess) return e;
     if (R > 0) {
         if (bv.key_bytes == 2)
-            identify_tile_ranges_kernel<uint16_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, iv.ranges);
+            identify_tile_ranges_kernel<uint16_t><<<(R + 256 * 8 - 1) / (256 * 8), 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, iv.ranges);
         else
-            identify_tile_ranges_kernel<uint32_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, iv.ranges);
+            identify_tile_ranges_kernel<uint32_t><<<(R + 256 * 4 - 1) / (256 * 4), 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, iv.ranges);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     // longest list first: the render kernels' critical path is their heaviest tile
-    tile_len_kernel<<<((int)T + 255) / 256, 256, 0, s>>>((int)T, iv.ranges, iv.tile_len, iv.tile_iota);
-    size_t bytes = iv.order_tmp_bytes;
-    int bits = 1;
-    while (bits < 32 && ((unsigned)R >> bits) != 0) bits++;
-    return cub::DeviceRadixSort::SortPairsDescending(iv.order_tmp, bytes, iv.tile_len, iv.tile_len_sorted, iv.tile_iota,
-                                                     iv.tile_order, (int)T, 0, bits, s);
+    tile_order_kernel<<<1, 1024, 0, s>>>((int)T, iv.ranges, iv.tile_order);
+    return cudaGetLastError();
 }
 
 // Parity / inspection only: rebuild the 64-bit keys, tiles touched and the index-order offsets.

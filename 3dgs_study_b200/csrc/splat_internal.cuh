@@ -58,7 +58,6 @@ struct BinView {
 struct ImgView {
     int2* ranges; float* final_T; uint32_t* n_contrib; unsigned int* counters;
     uint32_t* tile_order;       // tiles by decreasing list length (NULL: index order)
-    uint32_t* tile_len; uint32_t* tile_iota; uint32_t* tile_len_sorted; void* order_tmp; size_t order_tmp_bytes;
     size_t total;
 };
 
