@@ -16,6 +16,12 @@ namespace {
 #define PRE_T 128
 #endif
 constexpr int PRE_THREADS = PRE_T;
+#ifndef PRE_MINB_FWD
+#define PRE_MINB_FWD 8
+#endif
+#ifndef PRE_MINB_BWD
+#define PRE_MINB_BWD 1
+#endif
 
 // row stride (floats) of an SH row staged in shared memory: an odd number of 16-byte words
 __device__ __forceinline__ int sh_row_stride(int M3) { return ((M3 >> 2) & 1) ? M3 : M3 + 4; }
@@ -107,7 +113,7 @@ __device__ __forceinline__ void project_cov(const ViewConsts& vc, float tx, floa
     o.cov11 = cdot3(o.N1[0], o.M1[0], o.N1[1], o.M1[1], o.N1[2], o.M1[2]);
 }
 
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_fwd_kernel(PreParams p, float* __restrict__ depths,
+__global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_FWD) preprocess_fwd_kernel(PreParams p, float* __restrict__ depths,
                                                                      float4* __restrict__ rec,
                                                                      uint2* __restrict__ rect,
                                                                      uint32_t* __restrict__ iota,
@@ -263,7 +269,7 @@ __device__ __forceinline__ void store3(float* base, size_t i, float a, float b, 
 // streams the 32 result rows back with coalesced 16-byte stores (zeros for culled Gaussians).
 // write_dsh = 0 (view-parallel exchange, see sh_grad_from_views_kernel): the dL/dsh rows are NOT written; the
 // colour gradient, already multiplied by the SH clamp mask, goes to out.dL_dcolors instead.
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_bwd_kernel(BwdParams bp, int coop, int qs, int write_dsh) {
+__global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kernel(BwdParams bp, int coop, int qs, int write_dsh) {
     extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
     const PreParams& p = bp.p;
@@ -727,6 +733,7 @@ cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gauss
         cudaError_t e = cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
+    cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(p, gv.depths, gv.rec, gv.rect, gv.iota,
                                                                                          radii, pair_counter, coop, coop_shift(M3 >> 2));
     return cudaGetLastError();
@@ -746,6 +753,7 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
         cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
+    cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop, coop_shift(M3 >> 2), out.dL_dsh ? 1 : 0);
     return cudaGetLastError();
 }

@@ -363,10 +363,10 @@ class ViewParallelStep:
     # -- measurement helpers (CUDA path only) ------------------------------------------------------------
     @staticmethod
     def launches_per_view() -> int:
-        """Kernels of THIS library launched per view fwd+bwd: preprocess, duplicateWithKeys,
-        identifyTileRanges, render fwd, render bwd, per-Gaussian bwd (CUB scan/sort passes and memsets are
-        library / driver work and are not counted)."""
-        return 6
+        """Kernels of THIS library launched per view fwd+bwd (single GPU step): preprocess, duplicateWithKeys (emit),
+        identifyTileRanges, tile order, render fwd, render bwd, per-Gaussian bwd, densification statistics (CUB
+        scan / sort passes and memsets are library / driver work and are not counted)."""
+        return 8
 
     def stage_profile(self, cam, dL, iters: int = 5):
         """Per-stage device milliseconds (CUDA events on the launch stream, inside the library) averaged
@@ -389,6 +389,7 @@ class ViewParallelStep:
                                            image_height=cam.image_height, image_width=cam.image_width, stage_times=st)
             if it == 0:
                 stats = {"visible": int((radii > 0).sum().item()), "R": int(R)}
+                stats.update(C.render_stats(lv.means3D.shape[0], cam.image_width, cam.image_height, R, geom, binning, img))
                 continue   # first pass is warm-up
             for k, v in st.as_dict().items():
                 acc[k[:-3]] = acc.get(k[:-3], 0.0) + v / iters

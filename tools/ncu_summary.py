@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Per-kernel summary of an .ncu-rep (raw page): time, DRAM traffic, issue utilisation, occupancy, pipes, stalls."""
-import csv, subprocess, sys
+import csv, os, subprocess, sys
 rep = sys.argv[1]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
@@ -23,3 +23,30 @@ for r in rows[2:]:
     st = [(h, float(r[i])) for h, i in ix.items() if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio") and r[i] not in ("", "n/a")]
     st.sort(key=lambda x: -x[1])
     print("  stalls/issue: " + ", ".join(f"{h[34:-23]}={v:.2f}" for h, v in st[:7]))
+
+# machine-readable digest for bench.py's roofline (`traffic`, `issue`): profiles/<round>_ncu_kernels.json
+if len(sys.argv) > 2:
+    import json, re
+    digest = {"source": os.path.basename(rep) if 'os' in dir() else rep}
+    def num(r, k):
+        try:
+            return float(r[ix[k]].replace(",", ""))
+        except Exception:
+            return None
+    def to_bytes(r, k):
+        v, u = num(r, k), units[ix[k]]
+        return None if v is None else v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+    def to_us(r, k):
+        v, u = num(r, k), units[ix[k]]
+        return None if v is None else v * {"ns": 1e-3, "us": 1, "ms": 1e3, "s": 1e6}.get(u, 1)
+    for r in rows[2:]:
+        m = re.search(r"(\w+_kernel)", r[ix["Kernel Name"]])
+        if not m or m.group(1) in digest:
+            continue
+        digest[m.group(1)] = {"time_us": to_us(r, "gpu__time_duration.sum"),
+                              "dram_bytes": int((to_bytes(r, "dram__bytes_read.sum") or 0) + (to_bytes(r, "dram__bytes_write.sum") or 0)),
+                              "warp_inst": int(num(r, "smsp__inst_executed.sum") or 0),
+                              "issue_active_pct": num(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                              "warps_active_pct": num(r, "sm__warps_active.avg.pct_of_peak_sustained_active"),
+                              "registers": num(r, "launch__registers_per_thread")}
+    json.dump(digest, open(sys.argv[2], "w"), indent=1)
