@@ -153,24 +153,55 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int P, int gx, 
     s_end[tid] = __ldg(offsets + j);
     const uint32_t base = j0 == 0 ? 0u : __ldg(offsets + j0 - 1);
     __syncthreads();
-    const uint32_t total = s_end[EMIT_THREADS - 1] - base;
-    for (uint32_t k = tid; k < total; k += EMIT_THREADS) {
-        const uint32_t slot = base + k;
-        // first g with s_end[g] > slot
-        int lo = 0, hi = EMIT_THREADS - 1;
+    // Each thread owns four consecutive output slots (aligned to 4 so full groups go out as one vector store
+    // per array): one binary search and one division for the first slot, then a linear walk.
+    const uint32_t end = s_end[EMIT_THREADS - 1];
+    for (uint32_t gs = (base & ~3u) + 4u * tid; gs < end; gs += 4u * EMIT_THREADS) {
+        const uint32_t s0 = max(gs, base);
+        int lo = 0, hi = EMIT_THREADS - 1;          // first g with s_end[g] > s0
 #pragma unroll
         for (int it = 0; it < 8; it++) {
             const int mid = (lo + hi) >> 1;
-            if (s_end[mid] > slot) hi = mid; else lo = mid + 1;
+            if (s_end[mid] > s0) hi = mid; else lo = mid + 1;
         }
-        const int g = lo;
-        const uint2 r = s_rect[g];
-        const uint32_t w = r.y & 0xffffu;
-        const uint32_t first = s_end[g] - w * (r.y >> 16);
-        const uint32_t local = slot - first;
-        const uint32_t row = local / w, col = local - row * w;
-        keys[slot] = (KeyT)(((r.x >> 16) + row) * (uint32_t)gx + (r.x & 0xffffu) + col);
-        vals[slot] = s_id[g];
+        int g = lo;
+        uint2 r = s_rect[g];
+        uint32_t w = r.y & 0xffffu;
+        uint32_t gend = s_end[g];
+        uint32_t id = s_id[g];
+        const uint32_t local = s0 - (gend - w * (r.y >> 16));
+        const uint32_t row = local / w;
+        uint32_t col = local - row * w;
+        uint32_t tile = ((r.x >> 16) + row) * (uint32_t)gx + (r.x & 0xffffu) + col;
+        KeyT kk[4];
+        uint32_t vv[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const uint32_t sl = gs + e;
+            kk[e] = 0; vv[e] = 0;
+            if (sl >= s0 && sl < end) {
+                while (sl >= gend) {                 // next Gaussian with tiles: restart at its first tile
+                    g++;
+                    r = s_rect[g]; w = r.y & 0xffffu; gend = s_end[g]; id = s_id[g];
+                    col = 0;
+                    tile = (r.x >> 16) * (uint32_t)gx + (r.x & 0xffffu);
+                }
+                kk[e] = (KeyT)tile; vv[e] = id;
+                col++; tile++;
+                if (col == w) { col = 0; tile += (uint32_t)gx - w; }
+            }
+        }
+        if (gs >= base && gs + 4 <= end) {
+            if (sizeof(KeyT) == 2)
+                *reinterpret_cast<uint2*>(keys + gs) = make_uint2((uint32_t)kk[0] | ((uint32_t)kk[1] << 16), (uint32_t)kk[2] | ((uint32_t)kk[3] << 16));
+            else
+                *reinterpret_cast<uint4*>(keys + gs) = make_uint4(kk[0], kk[1], kk[2], kk[3]);
+            *reinterpret_cast<uint4*>(vals + gs) = make_uint4(vv[0], vv[1], vv[2], vv[3]);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 4; e++)
+                if (gs + e >= s0 && gs + e < end) { keys[gs + e] = kk[e]; vals[gs + e] = vv[e]; }
+        }
     }
 }
 
