@@ -65,10 +65,13 @@ __device__ __forceinline__ void eval_color_sh(const float* __restrict__ sh_row, 
         }
     } else {
         r0 = cmul(b[0], sh_row[0]); r1 = cmul(b[0], sh_row[1]); r2 = cmul(b[0], sh_row[2]);
-        for (int k = 1; k < nb; k++) {
-            r0 = cfma(b[k], sh_row[3 * k], r0);
-            r1 = cfma(b[k], sh_row[3 * k + 1], r1);
-            r2 = cfma(b[k], sh_row[3 * k + 2], r2);
+#pragma unroll
+        for (int k = 1; k < 16; k++) {       // static indices keep the basis in registers
+            if (k < nb) {
+                r0 = cfma(b[k], sh_row[3 * k], r0);
+                r1 = cfma(b[k], sh_row[3 * k + 1], r1);
+                r2 = cfma(b[k], sh_row[3 * k + 2], r2);
+            }
         }
     }
     r0 = cadd(r0, 0.5f); r1 = cadd(r1, 0.5f); r2 = cadd(r2, 0.5f);
@@ -258,6 +261,13 @@ struct BwdParams {
     b200splat_grads out;
 };
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 __device__ __forceinline__ void store3(float* base, size_t i, float a, float b, float c) {
     base[3 * i] = a; base[3 * i + 1] = b; base[3 * i + 2] = c;
 }
@@ -288,10 +298,11 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
         const unsigned vmask = __ballot_sync(0xffffffffu, visible);
         const float4* src = reinterpret_cast<const float4*>(p.shs) + (size_t)i0 * nq;
         const int q = lane & ((1 << qs) - 1), rstep = 32 >> qs;
+        // asynchronous copies: the rows land while the geometry part below runs
         if (q < nq)
             for (int row = lane >> qs; row < 32; row += rstep)
-                if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + row * nq + q);
-        __syncwarp();
+                if ((vmask >> row) & 1u) cp_async16(wrows + row * RS4 + q, src + row * nq + q);
+        cp_async_commit();
     }
     float* my_row = reinterpret_cast<float*>(wrows + lane * RS4);
 
@@ -299,6 +310,7 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
     float dsc[3] = {0.f, 0.f, 0.f}, drot[4] = {0.f, 0.f, 0.f, 0.f}, dc6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float dop = 0.f, dcol[3] = {0.f, 0.f, 0.f}, dndc[2] = {0.f, 0.f};
 
+    float x = 0.f, y = 0.f, z = 0.f;
     if (visible) {
         const float4 a0 = __ldg(reinterpret_cast<const float4*>(bp.acc) + 3 * (size_t)i);
         const float4 a1 = __ldg(reinterpret_cast<const float4*>(bp.acc) + 3 * (size_t)i + 1);
@@ -308,7 +320,7 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
         dcol[0] = a1.z; dcol[1] = a1.w; dcol[2] = a2.x;
         dndc[0] = a0.x * (0.5f * p.W); dndc[1] = a0.y * (0.5f * p.H);
 
-        const float x = __ldg(p.means3D + 3 * i), y = __ldg(p.means3D + 3 * i + 1), z = __ldg(p.means3D + 3 * i + 2);
+        x = __ldg(p.means3D + 3 * i); y = __ldg(p.means3D + 3 * i + 1); z = __ldg(p.means3D + 3 * i + 2);
         const float tx = cadd(cfma(vc.view[8], z, cfma(vc.view[4], y, cmul(vc.view[0], x))), vc.view[12]);
         const float ty = cadd(cfma(vc.view[9], z, cfma(vc.view[5], y, cmul(vc.view[1], x))), vc.view[13]);
         const float tz = cadd(cfma(vc.view[10], z, cfma(vc.view[6], y, cmul(vc.view[2], x))), vc.view[14]);
@@ -390,6 +402,46 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
             dmean[2] += (vc.proj[8] * mw - vc.proj[11] * mul1) * dndc[0] + (vc.proj[9] * mw - vc.proj[11] * mul2) * dndc[1];
         }
 
+        // cov3D -> scale, rotation
+        if (!p.cov3D_precomp) {
+            const float r = q.x, qx = q.y, qy = q.z, qz = q.w;
+            const float R[3][3] = {
+                {1.f - 2.f * (qy * qy + qz * qz), 2.f * (qx * qy - r * qz), 2.f * (qx * qz + r * qy)},
+                {2.f * (qx * qy + r * qz), 1.f - 2.f * (qx * qx + qz * qz), 2.f * (qy * qz - r * qx)},
+                {2.f * (qx * qz - r * qy), 2.f * (qy * qz + r * qx), 1.f - 2.f * (qx * qx + qy * qy)}};
+            const float s[3] = {p.mod * s3[0], p.mod * s3[1], p.mod * s3[2]};
+            const float G3[3][3] = {{dc6[0], 0.5f * dc6[1], 0.5f * dc6[2]},
+                                    {0.5f * dc6[1], dc6[3], 0.5f * dc6[4]},
+                                    {0.5f * dc6[2], 0.5f * dc6[4], dc6[5]}};
+            float g[3][3];
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                float ds = 0.f;
+#pragma unroll
+                for (int a2i = 0; a2i < 3; a2i++) {
+                    float vsum = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 3; k++) vsum += G3[a2i][k] * (R[k][j] * s[j]);
+                    const float dLm = 2.f * vsum;
+                    ds += R[a2i][j] * dLm;
+                    g[a2i][j] = dLm * s[j];
+                }
+                dsc[j] = p.mod * ds;
+            }
+            drot[0] = 2.f * (-qz * g[0][1] + qy * g[0][2] + qz * g[1][0] - qx * g[1][2] - qy * g[2][0] + qx * g[2][1]);
+            drot[1] = 2.f * (qy * g[0][1] + qz * g[0][2] + qy * g[1][0] - 2.f * qx * g[1][1] - r * g[1][2] + qz * g[2][0] +
+                             r * g[2][1] - 2.f * qx * g[2][2]);
+            drot[2] = 2.f * (-2.f * qy * g[0][0] + qx * g[0][1] + r * g[0][2] + qx * g[1][0] + qz * g[1][2] - r * g[2][0] +
+                             qz * g[2][1] - 2.f * qy * g[2][2]);
+            drot[3] = 2.f * (-2.f * qz * g[0][0] - r * g[0][1] + qx * g[0][2] + r * g[1][0] - 2.f * qz * g[1][1] +
+                             qy * g[1][2] + qx * g[2][0] + qy * g[2][1]);
+        }
+    }
+    if (coop) {   // the rows have landed; make every lane's copies visible to the warp
+        cp_async_wait_all();
+        __syncwarp();
+    }
+    if (visible) {
         // SH: dL/dsh rows and dL/dmean through the normalised view direction
         if (p.shs) {
             const float ddx = x - vc.campos[0], ddy = y - vc.campos[1], ddz = z - vc.campos[2];
@@ -484,41 +536,6 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
             dmean[0] += (dRx - ux * dotp) * il;
             dmean[1] += (dRy - uy * dotp) * il;
             dmean[2] += (dRz - uz * dotp) * il;
-        }
-
-        // cov3D -> scale, rotation
-        if (!p.cov3D_precomp) {
-            const float r = q.x, qx = q.y, qy = q.z, qz = q.w;
-            const float R[3][3] = {
-                {1.f - 2.f * (qy * qy + qz * qz), 2.f * (qx * qy - r * qz), 2.f * (qx * qz + r * qy)},
-                {2.f * (qx * qy + r * qz), 1.f - 2.f * (qx * qx + qz * qz), 2.f * (qy * qz - r * qx)},
-                {2.f * (qx * qz - r * qy), 2.f * (qy * qz + r * qx), 1.f - 2.f * (qx * qx + qy * qy)}};
-            const float s[3] = {p.mod * s3[0], p.mod * s3[1], p.mod * s3[2]};
-            const float G3[3][3] = {{dc6[0], 0.5f * dc6[1], 0.5f * dc6[2]},
-                                    {0.5f * dc6[1], dc6[3], 0.5f * dc6[4]},
-                                    {0.5f * dc6[2], 0.5f * dc6[4], dc6[5]}};
-            float g[3][3];
-#pragma unroll
-            for (int j = 0; j < 3; j++) {
-                float ds = 0.f;
-#pragma unroll
-                for (int a2i = 0; a2i < 3; a2i++) {
-                    float vsum = 0.f;
-#pragma unroll
-                    for (int k = 0; k < 3; k++) vsum += G3[a2i][k] * (R[k][j] * s[j]);
-                    const float dLm = 2.f * vsum;
-                    ds += R[a2i][j] * dLm;
-                    g[a2i][j] = dLm * s[j];
-                }
-                dsc[j] = p.mod * ds;
-            }
-            drot[0] = 2.f * (-qz * g[0][1] + qy * g[0][2] + qz * g[1][0] - qx * g[1][2] - qy * g[2][0] + qx * g[2][1]);
-            drot[1] = 2.f * (qy * g[0][1] + qz * g[0][2] + qy * g[1][0] - 2.f * qx * g[1][1] - r * g[1][2] + qz * g[2][0] +
-                             r * g[2][1] - 2.f * qx * g[2][2]);
-            drot[2] = 2.f * (-2.f * qy * g[0][0] + qx * g[0][1] + r * g[0][2] + qx * g[1][0] + qz * g[1][2] - r * g[2][0] +
-                             qz * g[2][1] - 2.f * qy * g[2][2]);
-            drot[3] = 2.f * (-2.f * qz * g[0][0] - r * g[0][1] + qx * g[0][2] + r * g[1][0] - 2.f * qz * g[1][1] +
-                             qy * g[1][2] + qx * g[2][0] + qy * g[2][1]);
         }
     } else if (coop) {
         if (in_range && write_dsh) {
