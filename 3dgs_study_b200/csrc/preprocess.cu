@@ -35,6 +35,13 @@ struct PreParams {
     const float* view; const float* proj; const float* campos;
 };
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 // colour of one Gaussian from its SH row (canonical chain: res = b0*sh0; res = fma(bk, shk, res))
 template <bool GLOBAL = true>
 __device__ __forceinline__ void eval_color_sh(const float* __restrict__ sh_row, int M, int D, float dx, float dy,
@@ -139,14 +146,36 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_FWD) preprocess_fwd_kern
     uint32_t area = 0;
     float o_eff = 0.f;
     uint2 rc = make_uint2(0u, 0u);
-    if (in_range && tz > NEAR_Z) {
-        const float tx = cadd(cfma(vc.view[8], z, cfma(vc.view[4], y, cmul(vc.view[0], x))), vc.view[12]);
-        const float ty = cadd(cfma(vc.view[9], z, cfma(vc.view[5], y, cmul(vc.view[1], x))), vc.view[13]);
+    float ndcx = 0.f, ndcy = 0.f;
+    const bool front = in_range && tz > NEAR_Z;
+    if (front) {
         const float hx = cadd(cfma(vc.proj[8], z, cfma(vc.proj[4], y, cmul(vc.proj[0], x))), vc.proj[12]);
         const float hy = cadd(cfma(vc.proj[9], z, cfma(vc.proj[5], y, cmul(vc.proj[1], x))), vc.proj[13]);
         const float hw = cadd(cfma(vc.proj[11], z, cfma(vc.proj[7], y, cmul(vc.proj[3], x))), vc.proj[15]);
         const float pw = __frcp_rn(cadd(hw, 0.0000001f));
-        const float ndcx = cmul(hx, pw), ndcy = cmul(hy, pw);
+        ndcx = cmul(hx, pw); ndcy = cmul(hy, pw);
+    }
+    // ---- SH rows, first wave: the rows of Gaussians whose centre is on or near the screen start their way to
+    // shared memory now (asynchronous copies) and land while the covariance work below runs.  The exact
+    // visibility is only known after that work; the few visible Gaussians this guess misses (large splats
+    // centred off screen) are fetched in a second wave, the few it over-fetches (2-3 %) are ignored. ----
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int M3 = 3 * p.M, nq = M3 >> 2, RS4 = sh_row_stride(M3) >> 2;
+    float4* wrows = s_sh4 + (size_t)warp * 32 * RS4;
+    const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
+    const float4* sh_src = reinterpret_cast<const float4*>(p.shs) + (size_t)i0 * nq;
+    const int cq = lane & ((1 << qs) - 1), rstep = 32 >> qs;   // 2^qs >= nq lanes per row: no division
+    unsigned emask = 0;
+    if (coop) {
+        emask = __ballot_sync(0xffffffffu, front && fabsf(ndcx) < 1.15f && fabsf(ndcy) < 1.15f);
+        if (cq < nq)
+            for (int row = lane >> qs; row < 32; row += rstep)
+                if ((emask >> row) & 1u) cp_async16(wrows + row * RS4 + cq, sh_src + row * nq + cq);
+        cp_async_commit();
+    }
+    if (front) {
+        const float tx = cadd(cfma(vc.view[8], z, cfma(vc.view[4], y, cmul(vc.view[0], x))), vc.view[12]);
+        const float ty = cadd(cfma(vc.view[9], z, cfma(vc.view[5], y, cmul(vc.view[1], x))), vc.view[13]);
 
         float c6[6];
         if (p.cov3D_precomp) {
@@ -203,18 +232,14 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_FWD) preprocess_fwd_kern
         }
     }
     // ---- colour (after the cull, so the 12*M-byte SH row of a culled Gaussian is never touched) ----
-    if (coop) {   // coalesced load of the warp's visible rows into shared memory (see preprocess_bwd_kernel)
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        const int M3 = 3 * p.M, nq = M3 >> 2, RS4 = sh_row_stride(M3) >> 2;
-        float4* wrows = s_sh4 + (size_t)warp * 32 * RS4;
-        const int i0 = blockIdx.x * PRE_THREADS + warp * 32;
+    if (coop) {   // second wave (rows the guess missed), then wait for everything and publish to the warp
         const unsigned vmask = __ballot_sync(0xffffffffu, area != 0);
-        const float4* src = reinterpret_cast<const float4*>(p.shs) + (size_t)i0 * nq;
-        // 2^qs >= nq lanes per row, 32 >> qs rows per instruction: no division, every request contiguous
-        const int q = lane & ((1 << qs) - 1), rstep = 32 >> qs;
-        if (q < nq)
+        const unsigned late = vmask & ~emask;
+        if (late && cq < nq)
             for (int row = lane >> qs; row < 32; row += rstep)
-                if ((vmask >> row) & 1u) wrows[row * RS4 + q] = __ldg(src + row * nq + q);
+                if ((late >> row) & 1u) cp_async16(wrows + row * RS4 + cq, sh_src + row * nq + cq);
+        cp_async_commit();
+        cp_async_wait_all();
         __syncwarp();
         if (area) {
             float rgb[3]; unsigned cl;
@@ -260,13 +285,6 @@ struct BwdParams {
     const float* acc;    // [P,12] packed render-backward sums
     b200splat_grads out;
 };
-
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
-                 : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 __device__ __forceinline__ void store3(float* base, size_t i, float a, float b, float c) {
     base[3 * i] = a; base[3 * i + 1] = b; base[3 * i + 2] = c;
