@@ -213,7 +213,6 @@ int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians*
     if (grads->dL_drotations && !aligned16(grads->dL_drotations))
         return fail(B200SPLAT_ERR_INVALID_ARG, "dL_drotations must be 16-byte aligned");
     if (!dL_dout_color || !scratch_alloc) return fail(B200SPLAT_ERR_INVALID_ARG, "null dL_dout_color / scratch allocator");
-    if (dL_dout_invdepth) return fail(B200SPLAT_ERR_INVALID_ARG, "inverse-depth gradients are not implemented");
     if (g->P > 0 && (!radii || !geom || !binning || !image)) return fail(B200SPLAT_ERR_INVALID_ARG, "null forward state");
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool debug = view->debug != 0;

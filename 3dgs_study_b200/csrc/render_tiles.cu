@@ -5,22 +5,23 @@
 // the 0.99 alpha clamp and the 1e-4 transmittance exit; reverse traversal with warp-level reduction
 // of the per-Gaussian sums before any global atomic.
 //
-// Mapping (DESIGN.md "Render kernels").  One 128-thread block per tile; warp w owns the 16x4 pixel
-// strip of rows 4w..4w+3, and lane l the two pixels (l & 7, l >> 3) and (8 + (l & 7), l >> 3) of it.
-//   * A tile's depth-sorted list is streamed through shared memory 128 packed 48-byte records at a
+// Mapping (DESIGN.md "Render kernels").  One block of NW warps per tile (NW = 2: 64 threads); warp w owns the
+// 16 x (16/NW) pixel strip of rows (16/NW) w .., and lane l the pixel (l & 7, l >> 3) of each 8x4 cell of it
+// (8/NW pixels per lane).
+//   * A tile's depth-sorted list is streamed through shared memory NW*32 packed 48-byte records at a
 //     time (one record per thread, three 16-byte loads, the next batch prefetched into registers).
 //   * Every record carries the bounding box of its {alpha >= 1/255} ellipse; the staging thread
-//     reduces it to a 4-bit strip mask, a ballot turns the masks into one 128-bit "reaches my strip"
+//     reduces it to an NW-bit strip mask, a ballot turns the masks into one "reaches my strip"
 //     bitmap per warp, and each warp walks ONLY the set bits of its bitmap (find-first-set), so
 //     a splat that cannot touch a strip costs that warp nothing.  Results are identical: a skipped
 //     pixel would have failed the exact alpha test.
-//   * Both pixels of a lane are evaluated in straight-line predicated code (two independent chains);
-//     the state per thread is ~12 registers, so ~12 warps per scheduler hide the exp / rcp latency.
+//   * The pixels of a lane are evaluated in straight-line predicated code (independent chains).
 //   * Backward: the per-Gaussian sums of a strip are finished with ONE transposed butterfly
 //     (8 values over 32 lanes in 4+2+1+1+1 shuffles) and nine red.global.add per (strip, Gaussian)
 //     instead of nine atomics per pixel.
-// The critical path of the kernel is one tile's list divided over four warps; tiles are issued
-// longest list first (tile_order) so the heavy ones do not start last.
+// Tiles are issued longest list first (tile_order) so the heavy ones do not start last.  Measured and
+// rejected (round 1): wider blocks for the heaviest tiles only (two launches side by side: slower, the
+// stage is throughput- not critical-path-bound), per-cell skipping in the backward.
 #include "splat_internal.cuh"
 
 namespace b200splat {
@@ -170,6 +171,10 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
                     const float invd = DEPTH ? s_invd[j] : 0.f;
 #pragma unroll
                     for (int s = 0; s < NP; s++) {
+                        // A slot is one 8x4 cell of the strip; a cell none of whose pixels can change (power outside
+                        // [thr, 0], or pixel finished) is skipped by the whole warp: most splats cover one or two of
+                        // a strip's cells.  (Measured: -9 % forward; the backward, tried the same way, gains nothing.)
+                        if (NP > 1 && !__any_sync(FULL, pw[s] >= b.w && pw[s] <= 0.0f && T[s] > 0.0f)) continue;
                         // exact tests: power <= 0, alpha >= 1/255, T (1 - alpha) >= 1e-4; a finished pixel has T < 0
                         const float alpha = fminf(ALPHA_MAX, cmul(c.x, expf(pw[s])));
                         const float test_T = cmul(T[s], csub(1.0f, alpha));
@@ -216,16 +221,19 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
 //   m0 = sum z, mx = sum z dx, my = sum z dy, mxx = sum z dx^2, mxy = sum z dx dy, myy = sum z dy^2
 //   dL/dpx = -(A mx + B my), dL/dpy = -(C my + B mx), dL/dA = -mxx/2, dL/dB = -mxy, dL/dC = -myy/2,
 //   dL/do = m0 / o, dL/dcolour = sum alpha T g.
-template <int NW>
+// DEPTH: the inverse-depth image is a fourth blended channel (value 1/depth_i, no background term) with its
+// own upstream gradient; it adds invd_i * gD to c_i . g and the sum of alpha T gD to acc[9].
+template <int NW, bool DEPTH>
 __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
     const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
-    int W, int H, int gx, const uint32_t* __restrict__ tile_order, const float* __restrict__ bg,
-    const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
-    float* __restrict__ acc) {
+    const float* __restrict__ depths, int W, int H, int gx, const uint32_t* __restrict__ tile_order,
+    const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
+    const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvd, float* __restrict__ acc) {
     using L = Layout<NW>;
     constexpr int TB = NW * 32, NX = L::NX, NY = L::NY, NP = L::NP;
     __shared__ float4 s_rec[TB * 3];
     __shared__ uint32_t s_id[TB];
+    __shared__ float s_invd[DEPTH ? TB : 1];
     __shared__ unsigned s_bits[NW][NW];
     __shared__ int s_wmax[NW];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -240,19 +248,21 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
     for (int k = 0; k < NX; k++) pxf[k] = (float)(ox + L::x(lane, k));
 #pragma unroll
     for (int k = 0; k < NY; k++) pyf[k] = (float)(oy + L::y(lane, warp, k));
-    float T[NP], S[NP], g0[NP], g1[NP], g2[NP];
+    float T[NP], S[NP], g0[NP], g1[NP], g2[NP], gd[DEPTH ? NP : 1];
     int last[NP];
     int lmax = 0;
 #pragma unroll
     for (int s = 0; s < NP; s++) {
         const int px = ox + L::x(lane, s % NX), py = oy + L::y(lane, warp, s / NX);
         T[s] = 1.f; S[s] = 0.f; g0[s] = 0.f; g1[s] = 0.f; g2[s] = 0.f; last[s] = 0;
+        if (DEPTH) gd[s] = 0.f;
         if (px < W && py < H) {
             const size_t pix = (size_t)py * W + px;
             T[s] = __ldg(final_T + pix);
             last[s] = (int)__ldg(n_contrib + pix);
             g0[s] = __ldg(dL_dpix + pix); g1[s] = __ldg(dL_dpix + HW + pix); g2[s] = __ldg(dL_dpix + 2 * HW + pix);
             S[s] = T[s] * (bg0 * g0[s] + bg1 * g1[s] + bg2 * g2[s]);
+            if (DEPTH) gd[s] = __ldg(dL_dinvd + pix);
         }
         lmax = max(lmax, last[s]);
     }
@@ -266,11 +276,13 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
 
     float4 ra = make_float4(0.f, 0.f, -1.f, -1.f), rb = ra, rc = ra;
     uint32_t rid = 0;
+    float rinvd = 0.f;
     {
         const int idx = max(0, maxc - TB) + tid;
         if (idx < maxc) {
             rid = __ldg(point_list + range.x + idx);
             ra = __ldg(rec + 3 * (size_t)rid); rb = __ldg(rec + 3 * (size_t)rid + 1); rc = __ldg(rec + 3 * (size_t)rid + 2);
+            if (DEPTH) rinvd = __frcp_rn(__ldg(depths + rid));
         }
     }
     for (int hi = maxc; hi > 0; hi -= TB) {
@@ -279,6 +291,7 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
         __syncthreads();                         // previous batch fully consumed
         s_rec[tid * 3 + 0] = ra; s_rec[tid * 3 + 1] = rb; s_rec[tid * 3 + 2] = rc;
         s_id[tid] = rid;
+        if (DEPTH) s_invd[tid] = rinvd;
         const unsigned m = tid < cnt ? strip_mask<NW>(ra.x - fox, ra.y - foy, ra.z, ra.w) : 0u;
 #pragma unroll
         for (int g = 0; g < NW; g++) {
@@ -292,6 +305,7 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
             if (idx < nhi) {
                 rid = __ldg(point_list + range.x + idx);
                 ra = __ldg(rec + 3 * (size_t)rid); rb = __ldg(rec + 3 * (size_t)rid + 1); rc = __ldg(rec + 3 * (size_t)rid + 2);
+                if (DEPTH) rinvd = __frcp_rn(__ldg(depths + rid));
             }
         }
         if (lo >= wmax) continue;                // this batch lies entirely behind this strip's deepest contributor
@@ -327,7 +341,8 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
                     }
                 }
                 if (!__any_sync(FULL, any_ok)) continue;
-                float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
+                float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, cd = 0.f;
+                const float invd = DEPTH ? s_invd[j] : 0.f;
                 bool any_valid = false;
 #pragma unroll
                 for (int s = 0; s < NP; s++) {
@@ -342,13 +357,15 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
                     const float alpha = fminf(ALPHA_MAX, au);
                     const float r = fast_rcp(1.0f - alpha);
                     const float Ti = T[s] * r;
-                    const float cg = c.y * g0[s] + c.z * g1[s] + c.w * g2[s];
+                    float cg = c.y * g0[s] + c.z * g1[s] + c.w * g2[s];
+                    if (DEPTH) cg = fmaf(invd, gd[s], cg);
                     const float w = alpha * Ti;
                     const float dLda = Ti * cg - S[s] * r;
                     const float z = au * dLda;
                     T[s] = Ti;
                     S[s] = fmaf(w, cg, S[s]);
                     c0 = fmaf(w, g0[s], c0); c1 = fmaf(w, g1[s], c1); c2 = fmaf(w, g2[s], c2);
+                    if (DEPTH) cd = fmaf(w, gd[s], cd);
                     const float ddx = dx[s % NX], ddy = dyv[s / NX];
                     const float zx = z * ddx, zy = z * ddy;
                     m0 += z; mx += zx; my += zy;
@@ -372,11 +389,13 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
                 t0 += __shfl_xor_sync(FULL, t0, 2);
                 t0 += __shfl_xor_sync(FULL, t0, 1);
                 c2 = warp_sum(c2);
+                if (DEPTH) cd = warp_sum(cd);
                 // component slot of acc held by lane L (L & 3 == 0): L >> 2 ->
                 //   0 dpx  1 dpy  2 dA  3 dB  4 dC  5 do  6 dr  7 dg ; slot 8 (db) from lane 1
                 float* dst = acc + 12 * (size_t)s_id[j];
                 if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), t0);
                 else if (lane == 1) atomicAdd(dst + 8, c2);
+                else if (DEPTH && lane == 2) atomicAdd(dst + 9, cd);
             }
         }
     }
@@ -456,13 +475,16 @@ cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, 
 
 cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
                               const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
-    (void)dL_dinvdepth;
     const int W = v.image_width, H = v.image_height;
     const int gx = (W + TILE - 1) / TILE;
     const int T = tiles_of(W, H);
     if (T == 0) return cudaSuccess;
-    render_bwd_kernel<BWD_NW><<<T, BWD_NW * 32, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, gx, iv.tile_order, v.bg, iv.final_T,
-                                       iv.n_contrib, dL_dpix, acc);
+    if (dL_dinvdepth)
+        render_bwd_kernel<BWD_NW, true><<<T, BWD_NW * 32, 0, s>>>(iv.ranges, vals_sorted, gv.rec, gv.depths, W, H, gx, iv.tile_order,
+                                                                 v.bg, iv.final_T, iv.n_contrib, dL_dpix, dL_dinvdepth, acc);
+    else
+        render_bwd_kernel<BWD_NW, false><<<T, BWD_NW * 32, 0, s>>>(iv.ranges, vals_sorted, gv.rec, gv.depths, W, H, gx, iv.tile_order,
+                                                                  v.bg, iv.final_T, iv.n_contrib, dL_dpix, nullptr, acc);
     return cudaGetLastError();
 }
 

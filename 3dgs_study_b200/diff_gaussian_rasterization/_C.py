@@ -250,8 +250,11 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, opacities=None, antialiasing=False,
                                  image_height=None, image_width=None, stage_times: StageTimes = None,
                                  masked_colors: bool = False, out: Optional[dict] = None,
-                                 early_colors: Optional[torch.Tensor] = None, after_early_colors=None):
+                                 early_colors: Optional[torch.Tensor] = None, after_early_colors=None,
+                                 dL_dout_invdepth: Optional[torch.Tensor] = None):
     """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+
+    dL_dout_invdepth ([1,H,W], optional): upstream gradient of the inverse-depth image (newer upstream API).
 
     masked_colors=True (SH mode only): dL_dsh is not produced (None); dL_dcolors is the colour gradient times the
     SH clamp mask, the quantity the view-parallel exchange ships (see sh_grad_from_views).
@@ -262,6 +265,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     dev = means3D.device
     P = means3D.shape[0]
     dL_dout_color = _f32c(dL_dout_color, "dL_dout_color", dev)
+    dL_dout_invdepth = _f32c(dL_dout_invdepth, "dL_dout_invdepth", dev)
     H = int(image_height) if image_height is not None else int(dL_dout_color.shape[1])
     W = int(image_width) if image_width is not None else int(dL_dout_color.shape[2])
     means3D = _f32c(means3D, "means3D", dev)
@@ -278,6 +282,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     projmatrix = _f32c(projmatrix, "projmatrix", dev)
     campos = _f32c(campos, "campos", dev)
     M = int(sh.shape[1]) if sh is not None else 0
+    if dL_dout_invdepth is not None and dL_dout_invdepth.numel() != H * W:
+        raise RuntimeError(f"dL_dout_invdepth must have {H}*{W} elements")
 
     def new(name, *shape):
         if out is not None and name in out:
@@ -322,7 +328,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         hooks = _BackwardHooks(_ptr(early_colors), hook_cb, None)
     with torch.cuda.device(dev):
         rc = lib().b200splat_backward_ex(ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer),
-                                         _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(dL_dout_color), None,
+                                         _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(dL_dout_color),
+                                         _ptr(dL_dout_invdepth),
                                          ctypes.addressof(grads), ctypes.addressof(hooks) if hooks is not None else None,
                                          ta.cb, 1, ctypes.addressof(stage_times) if stage_times is not None else None,
                                          _stream_ptr(dev))

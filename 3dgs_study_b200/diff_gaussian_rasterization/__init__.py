@@ -87,14 +87,12 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.has_means2D = means2D is not None
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
                               geomBuffer, binningBuffer, imgBuffer)
-        if invdepth is None:
-            ctx.mark_non_differentiable(radii)
-        else:
-            ctx.mark_non_differentiable(radii, invdepth)
+        ctx.mark_non_differentiable(radii)      # invdepth is differentiable (newer upstream API)
+        ctx.set_materialize_grads(False)        # an unused output arrives as None, not as an image of zeros
         return color, radii, invdepth
 
     @staticmethod
-    def backward(ctx, grad_out_color, _grad_radii, _grad_invdepth):
+    def backward(ctx, grad_out_color, _grad_radii, grad_invdepth):
         rs = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities, geomBuffer, binningBuffer,
          imgBuffer) = ctx.saved_tensors
@@ -102,7 +100,10 @@ class _RasterizeGaussians(torch.autograd.Function):
                 rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, sh, rs.sh_degree, rs.campos,
                 geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
         kw = dict(opacities=opacities, antialiasing=bool(getattr(rs, "antialiasing", False)),
-                  image_height=rs.image_height, image_width=rs.image_width)
+                  image_height=rs.image_height, image_width=rs.image_width, dL_dout_invdepth=grad_invdepth)
+        if grad_out_color is None:               # only the inverse-depth image fed the loss
+            grad_out_color = torch.zeros(3, rs.image_height, rs.image_width, dtype=torch.float32, device=means3D.device)
+            args = args[:12] + (grad_out_color,) + args[13:]
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:

@@ -50,7 +50,12 @@ class Case:
                           n(c.world_view_transform), n(c.full_proj_transform), n(c.camera_center), c.tanfovx, c.tanfovy,
                           antialiasing=self.aa, want_invdepth=want_invdepth)
 
-    def oracle_backward(self, fr):
+    def depth_grad_image(self):
+        """Upstream gradient of the inverse-depth image (seeded, same on both sides)."""
+        g = torch.Generator().manual_seed(1234 + self.W)
+        return (torch.rand(1, self.H, self.W, generator=g) - 0.3).contiguous()
+
+    def oracle_backward(self, fr, invdepth_grad=False):
         from oracle import c_oracle as co
         s, c = self.scene, self.cam
         return co.backward(fr, self.P, self.D, self.M, self.W, self.H, n(self.bg), n(s.means3D),
@@ -58,10 +63,11 @@ class Case:
                            None if self.cov3D is not None else n(s.scales), self.mod,
                            None if self.cov3D is not None else n(s.rotations), n(self.cov3D) if self.cov3D is not None else None,
                            n(c.world_view_transform), n(c.full_proj_transform), n(c.camera_center), c.tanfovx, c.tanfovy,
-                           n(self.dL), antialiasing=self.aa)
+                           n(self.dL), dL_dinvdepth=n(self.depth_grad_image()) if invdepth_grad else None,
+                           antialiasing=self.aa)
 
     # ---- CUDA path through the operator -------------------------------------------------------------
-    def cuda_run(self, device="cuda:0", backward=True):
+    def cuda_run(self, device="cuda:0", backward=True, invdepth_grad=False):
         import diff_gaussian_rasterization as dgr
         dev = torch.device(device)
         s, c = self.scene.to(dev), self.cam.to(dev)
@@ -88,7 +94,10 @@ class Case:
                                                          kw["cov3D_precomp"], rs)
         grads = {}
         if backward:
-            (color * self.dL.to(dev)).sum().backward()
+            loss = (color * self.dL.to(dev)).sum()
+            if invdepth_grad:
+                loss = loss + (invdepth * self.depth_grad_image().to(dev)).sum()
+            loss.backward()
             grads = {k: v.grad for k, v in leaves.items()}
             grads["means2D"] = m2d.grad
         torch.cuda.synchronize()

@@ -80,6 +80,27 @@ def test_backward_gradients(name):
         assert float(np.abs(n(g["means3D"])[culled]).max()) == 0.0
 
 
+@pytest.mark.parametrize("name", ["sh3_small", "dense_opaque", "precomp"])
+def test_backward_with_inverse_depth_gradient(name):
+    """The inverse-depth image is differentiable (newer upstream API): a loss on colour AND inverse depth."""
+    case = Case(**CASES[name])
+    fr = case.oracle_forward(want_invdepth=True)
+    pg = case.oracle_backward(fr, invdepth_grad=True)
+    pg0 = case.oracle_backward(fr)
+    assert rel_err(pg.dL_dmeans3D, pg0.dL_dmeans3D) > 1e-2      # the depth term is not negligible in this case
+    color, radii, invd, g = case.cuda_run(invdepth_grad=True)
+    errs = {"means3D": rel_err(n(g["means3D"]), pg.dL_dmeans3D),
+            "opacities": rel_err(n(g["opacities"]).reshape(-1), pg.dL_dopacity),
+            "means2D": rel_err(n(g["means2D"])[:, :2], pg.dL_dmean2D)}
+    if "scales" in g:
+        errs["scales"] = rel_err(n(g["scales"]), pg.dL_dscales)
+        errs["rotations"] = rel_err(n(g["rotations"]), pg.dL_drot)
+    else:
+        errs["cov3D"] = rel_err(n(g["cov3D_precomp"]), pg.dL_dcov3D)
+    bad = {k: v for k, v in errs.items() if not v <= GRAD_TOL}
+    assert not bad, f"gradient relative errors above {GRAD_TOL}: {bad} (all: {errs})"
+
+
 def test_empty_and_all_culled():
     import diff_gaussian_rasterization as dgr
     dev = torch.device("cuda:0")

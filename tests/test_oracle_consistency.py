@@ -16,7 +16,7 @@ CASES = {
 }
 
 
-def _torch_run(case):
+def _torch_run(case, invdepth_grad=False):
     s, c = case.scene, case.cam
     lv = {"means3D": s.means3D.clone().requires_grad_(), "opacities": s.opacities.clone().requires_grad_()}
     kw = dict(shs=None, colors_precomp=None, scales=None, rotations=None, cov3D_precomp=None)
@@ -34,7 +34,10 @@ def _torch_run(case):
         image_height=case.H, image_width=case.W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=case.bg, scale_modifier=case.mod,
         viewmatrix=c.world_view_transform, projmatrix=c.full_proj_transform, sh_degree=case.D, campos=c.camera_center,
         means3D=lv["means3D"], means2D=m2d, opacities=lv["opacities"], antialiasing=case.aa, **kw)
-    (color * case.dL).sum().backward()
+    loss = (color * case.dL).sum()
+    if invdepth_grad:
+        loss = loss + (invd * case.depth_grad_image()).sum()
+    loss.backward()
     return color, radii, invd, aux, lv, m2d
 
 
@@ -72,6 +75,23 @@ def test_c_oracle_vs_torch_oracle(name):
         assert rel_err(pg.dL_drot, n(lv["rotations"].grad)) <= tol
     else:
         assert rel_err(pg.dL_dcov3D, n(lv["cov3D_precomp"].grad)) <= tol
+
+
+@pytest.mark.parametrize("name", ["sh3", "dense"])
+def test_c_oracle_inverse_depth_gradient_vs_autograd(name):
+    """Loss on colour AND the inverse-depth image: the C oracle's hand-derived depth terms against autograd."""
+    case = Case(**CASES[name])
+    fr = case.oracle_forward(want_invdepth=True)
+    pg = case.oracle_backward(fr, invdepth_grad=True)
+    pg0 = case.oracle_backward(fr)
+    assert rel_err(pg.dL_dmeans3D, pg0.dL_dmeans3D) > 1e-2          # the depth terms matter in these cases
+    color, radii, invd, aux, lv, m2d = _torch_run(case, invdepth_grad=True)
+    tol = 1e-3
+    assert rel_err(pg.dL_dmeans3D, n(lv["means3D"].grad)) <= tol
+    assert rel_err(pg.dL_dopacity, n(lv["opacities"].grad).reshape(-1)) <= tol
+    assert rel_err(pg.dL_dmean2D, n(m2d.grad)[:, :2]) <= tol
+    assert rel_err(pg.dL_dscales, n(lv["scales"].grad)) <= tol
+    assert rel_err(pg.dL_drot, n(lv["rotations"].grad)) <= tol
 
 
 def test_sorted_order_and_ranges_properties():
