@@ -34,6 +34,9 @@ namespace {
 #ifndef BWD_NW
 #define BWD_NW 2                       // warps per tile, backward
 #endif
+#ifndef BWD_PACKED
+#define BWD_PACKED 1                   // backward pixel arithmetic on packed fp32 pairs (FFMA2)
+#endif
 constexpr unsigned FULL = 0xffffffffu;
 
 // NW-bit mask of the 16 x (16/NW) strips the box (rx +- ex, ry +- ey), tile-relative, can reach
@@ -66,6 +69,48 @@ template <int NW> struct Layout {
 __device__ __forceinline__ float fast_rcp(float x) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ float fast_ex2(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// Packed pairs of fp32 (sm_100 FFMA2 / FMUL2 / FADD2: two IEEE fp32 results per lane per issue slot).  The render
+// kernels are bound by the issue rate, and the pixels of a lane run the same straight-line arithmetic, so the two
+// pixels of a row go through one instruction stream.
+struct f2 { unsigned long long v; };
+__device__ __forceinline__ f2 mk2(float lo, float hi) {
+    f2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ f2 bc2(float s) { return mk2(s, s); }
+__device__ __forceinline__ float lo2(f2 a) {
+    float l, h;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a.v));
+    return l;
+}
+__device__ __forceinline__ float hi2(f2 a) {
+    float l, h;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(l), "=f"(h) : "l"(a.v));
+    return h;
+}
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    f2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+    return r;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    f2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+    return r;
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+    f2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
     return r;
 }
 
@@ -273,6 +318,19 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
 #pragma unroll
     for (int g = 0; g < NW; g++) maxc = max(maxc, s_wmax[g]);
     const bool up16 = lane & 16, up8 = lane & 8, up4 = lane & 4;
+    // packed state (PK: NW == 2, pair ky = the two pixels (kx = 0, 1) of row ky): T, -S, the upstream gradients
+    constexpr bool PK = BWD_PACKED && NP == 4;
+    f2 T2[2], Sn2[2], g0p[2], g1p[2], g2p[2], gdp[2], npx2, npy2;
+    if (PK) {
+#pragma unroll
+        for (int ky = 0; ky < 2; ky++) {
+            T2[ky] = mk2(T[2 * ky], T[2 * ky + 1]); Sn2[ky] = mk2(-S[2 * ky], -S[2 * ky + 1]);
+            g0p[ky] = mk2(g0[2 * ky], g0[2 * ky + 1]); g1p[ky] = mk2(g1[2 * ky], g1[2 * ky + 1]);
+            g2p[ky] = mk2(g2[2 * ky], g2[2 * ky + 1]);
+            gdp[ky] = DEPTH ? mk2(gd[2 * ky], gd[2 * ky + 1]) : bc2(0.f);
+        }
+        npx2 = mk2(-pxf[0], -pxf[NX - 1]); npy2 = mk2(-pyf[0], -pyf[NY - 1]);
+    }
 
     float4 ra = make_float4(0.f, 0.f, -1.f, -1.f), rb = ra, rc = ra;
     uint32_t rid = 0;
@@ -321,6 +379,66 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
                 const int j = sw * 32 + jb;
                 const int pos = lo + j;
                 const float4 a = s_rec[3 * j], b = s_rec[3 * j + 1], c = s_rec[3 * j + 2];
+                float m0, mx, my, mxx, mxy, myy, c0, c1, c2, cd = 0.f;
+                bool any_valid = false;
+                if constexpr (PK) {
+                    // the same arithmetic as the scalar path below, two pixels per instruction; alpha, S and every sum
+                    // are carried NEGATED so that no separate negation is ever needed (the signs return in the
+                    // per-lane maps).  An invalid pixel has -alpha = 0: 1 / (1 + 0) = 1, T and S unchanged, z = 0.
+                    const f2 dx2 = add2(bc2(a.x), npx2), dy2 = add2(bc2(a.y), npy2);
+                    const f2 nbdy = mul2(bc2(-b.y), dy2);
+                    const f2 t22 = mul2(mul2(bc2(b.z), dy2), dy2);
+                    f2 p2[2];
+                    p2[0] = fma2(dx2, fma2(bc2(b.x), dx2, bc2(lo2(nbdy))), bc2(lo2(t22)));
+                    p2[1] = fma2(dx2, fma2(bc2(b.x), dx2, bc2(hi2(nbdy))), bc2(hi2(t22)));
+                    const float pw[4] = {lo2(p2[0]), hi2(p2[0]), lo2(p2[1]), hi2(p2[1])};
+                    bool ok[4], any_ok = false;
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        ok[q] = pw[q] <= 0.0f && pw[q] >= b.w && pos < last[q];
+                        any_ok |= ok[q];
+                    }
+                    if (!__any_sync(FULL, any_ok)) continue;
+                    const float invd = DEPTH ? s_invd[j] : 0.f;
+                    f2 nm0, nmx, nmy, nmxx, nmxy, nmyy, nc0, nc1, nc2, ncd = bc2(0.f);
+#pragma unroll
+                    for (int ky = 0; ky < 2; ky++) {
+                        const f2 e2 = mul2(p2[ky], bc2(1.4426950408889634f));
+                        const f2 nau0 = mul2(bc2(-c.x), mk2(fast_ex2(lo2(e2)), fast_ex2(hi2(e2))));
+                        const bool v0 = ok[2 * ky] && lo2(nau0) <= -ALPHA_MIN, v1 = ok[2 * ky + 1] && hi2(nau0) <= -ALPHA_MIN;
+                        const float na0 = v0 ? lo2(nau0) : 0.0f, na1 = v1 ? hi2(nau0) : 0.0f;
+                        const f2 nau = mk2(na0, na1);
+                        const f2 nal = mk2(fmaxf(-ALPHA_MAX, na0), fmaxf(-ALPHA_MAX, na1));
+                        const f2 oma = add2(bc2(1.0f), nal);
+                        const f2 r = mk2(fast_rcp(lo2(oma)), fast_rcp(hi2(oma)));
+                        const f2 Ti = mul2(T2[ky], r);
+                        f2 cg = fma2(bc2(c.w), g2p[ky], fma2(bc2(c.z), g1p[ky], mul2(bc2(c.y), g0p[ky])));
+                        if (DEPTH) cg = fma2(bc2(invd), gdp[ky], cg);
+                        const f2 dLda = fma2(Sn2[ky], r, mul2(Ti, cg));
+                        const f2 nw = mul2(nal, Ti);
+                        Sn2[ky] = fma2(nw, cg, Sn2[ky]);
+                        T2[ky] = Ti;
+                        const f2 nz = mul2(nau, dLda);
+                        const f2 dyb = bc2(ky == 0 ? lo2(dy2) : hi2(dy2));
+                        const f2 nzx = mul2(nz, dx2), nzy = mul2(nz, dyb);
+                        if (ky == 0) {
+                            nc0 = mul2(nw, g0p[0]); nc1 = mul2(nw, g1p[0]); nc2 = mul2(nw, g2p[0]);
+                            if (DEPTH) ncd = mul2(nw, gdp[0]);
+                            nm0 = nz; nmx = nzx; nmy = nzy;
+                            nmxx = mul2(nzx, dx2); nmxy = mul2(nzx, dyb); nmyy = mul2(nzy, dyb);
+                        } else {
+                            nc0 = fma2(nw, g0p[1], nc0); nc1 = fma2(nw, g1p[1], nc1); nc2 = fma2(nw, g2p[1], nc2);
+                            if (DEPTH) ncd = fma2(nw, gdp[1], ncd);
+                            nm0 = add2(nm0, nz); nmx = add2(nmx, nzx); nmy = add2(nmy, nzy);
+                            nmxx = fma2(nzx, dx2, nmxx); nmxy = fma2(nzx, dyb, nmxy); nmyy = fma2(nzy, dyb, nmyy);
+                        }
+                        any_valid |= v0 | v1;
+                    }
+                    m0 = -lo2(nm0) - hi2(nm0); mx = -lo2(nmx) - hi2(nmx); my = -lo2(nmy) - hi2(nmy);
+                    mxx = -lo2(nmxx) - hi2(nmxx); mxy = -lo2(nmxy) - hi2(nmxy); myy = -lo2(nmyy) - hi2(nmyy);
+                    c0 = -lo2(nc0) - hi2(nc0); c1 = -lo2(nc1) - hi2(nc1); c2 = -lo2(nc2) - hi2(nc2);
+                    if (DEPTH) cd = -lo2(ncd) - hi2(ncd);
+                } else {
                 float dx[NX], dyv[NY], pw[NP];
                 bool ok[NP], any_ok = false;
 #pragma unroll
@@ -341,9 +459,8 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
                     }
                 }
                 if (!__any_sync(FULL, any_ok)) continue;
-                float m0 = 0.f, mx = 0.f, my = 0.f, mxx = 0.f, mxy = 0.f, myy = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, cd = 0.f;
+                m0 = 0.f; mx = 0.f; my = 0.f; mxx = 0.f; mxy = 0.f; myy = 0.f; c0 = 0.f; c1 = 0.f; c2 = 0.f;
                 const float invd = DEPTH ? s_invd[j] : 0.f;
-                bool any_valid = false;
 #pragma unroll
                 for (int s = 0; s < NP; s++) {
                     // au = o G (unclamped alpha), gated ONCE: with au = 0 every term below is an exact no-op
@@ -371,6 +488,7 @@ __global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
                     m0 += z; mx += zx; my += zy;
                     mxx = fmaf(zx, ddx, mxx); mxy = fmaf(zx, ddy, mxy); myy = fmaf(zy, ddy, myy);
                     any_valid |= valid;
+                }
                 }
                 if (!__any_sync(FULL, any_valid)) continue;
                 // per-lane linear maps first (they commute with the sum over lanes), then ONE transposed
