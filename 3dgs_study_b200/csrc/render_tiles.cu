@@ -34,6 +34,9 @@ namespace {
 #ifndef BWD_NW
 #define BWD_NW 2                       // warps per tile, backward
 #endif
+#ifndef FWD_PACKED
+#define FWD_PACKED 1                   // forward power on packed fp32 pairs
+#endif
 #ifndef BWD_PACKED
 #define BWD_PACKED 1                   // backward pixel arithmetic on packed fp32 pairs (FFMA2)
 #endif
@@ -158,6 +161,7 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
         any_in |= inside;
     }
     bool warp_live = __any_sync(FULL, any_in);
+    const f2 npx2 = mk2(-pxf[0], -pxf[NX - 1]), npy2 = mk2(-pyf[0], -pyf[NY - 1]);
 
     float4 ra = make_float4(0.f, 0.f, -1.f, -1.f), rb = ra, rc = ra;
     float rinvd = 0.f;
@@ -194,20 +198,34 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
                     const int j = sw * 32 + __ffs(bits) - 1;
                     bits &= bits - 1;
                     const float4 a = s_rec[3 * j], b = s_rec[3 * j + 1], c = s_rec[3 * j + 2];
-                    float dx[NX], pw[NP];
-#pragma unroll
-                    for (int k = 0; k < NX; k++) dx[k] = csub(a.x, pxf[k]);
+                    float pw[NP];
                     float pmax = -3.0e38f;
+                    if constexpr (FWD_PACKED && NP == 4) {
+                        // The canonical power, two pixels per instruction (FFMA2): every packed operation is the same
+                        // IEEE operation per half as its scalar twin below (a - p as a + (-p), -(b dy) as (-b) dy),
+                        // and no packed multiply feeds a packed add, so nothing can be contracted differently.
+                        const f2 dx2 = add2(bc2(a.x), npx2), dy2 = add2(bc2(a.y), npy2);
+                        const f2 nbdy = mul2(bc2(-b.y), dy2);
+                        const f2 t22 = mul2(mul2(bc2(b.z), dy2), dy2);
+                        const f2 p0 = fma2(dx2, fma2(bc2(b.x), dx2, bc2(lo2(nbdy))), bc2(lo2(t22)));
+                        const f2 p1 = fma2(dx2, fma2(bc2(b.x), dx2, bc2(hi2(nbdy))), bc2(hi2(t22)));
+                        pw[0] = lo2(p0); pw[1] = hi2(p0); pw[NP - 2] = lo2(p1); pw[NP - 1] = hi2(p1);
+                        pmax = fmaxf(fmaxf(pw[0], pw[1]), fmaxf(pw[NP - 2], pw[NP - 1]));
+                    } else {
+                        float dx[NX];
 #pragma unroll
-                    for (int ky = 0; ky < NY; ky++) {
-                        const float dy = csub(a.y, pyf[ky]);
-                        const float bdy = cmul(b.y, dy);
-                        const float t2 = cmul(cmul(b.z, dy), dy);
+                        for (int k = 0; k < NX; k++) dx[k] = csub(a.x, pxf[k]);
 #pragma unroll
-                        for (int kx = 0; kx < NX; kx++) {
-                            const float p = cfma(dx[kx], cfma(b.x, dx[kx], -bdy), t2);
-                            pw[ky * NX + kx] = p;
-                            pmax = fmaxf(pmax, p);
+                        for (int ky = 0; ky < NY; ky++) {
+                            const float dy = csub(a.y, pyf[ky]);
+                            const float bdy = cmul(b.y, dy);
+                            const float t2 = cmul(cmul(b.z, dy), dy);
+#pragma unroll
+                            for (int kx = 0; kx < NX; kx++) {
+                                const float p = cfma(dx[kx], cfma(b.x, dx[kx], -bdy), t2);
+                                pw[ky * NX + kx] = p;
+                                pmax = fmaxf(pmax, p);
+                            }
                         }
                     }
                     // below thr no pixel of the strip can reach alpha >= 1/255: skip the exps
