@@ -20,7 +20,7 @@ constexpr int PRE_THREADS = PRE_T;
 #define PRE_MINB_FWD 8
 #endif
 #ifndef PRE_MINB_BWD
-#define PRE_MINB_BWD 1
+#define PRE_MINB_BWD 5
 #endif
 
 // row stride (floats) of an SH row staged in shared memory: an odd number of 16-byte words

@@ -37,6 +37,9 @@ namespace {
 #ifndef FWD_PACKED
 #define FWD_PACKED 1                   // forward power on packed fp32 pairs
 #endif
+#ifndef BWD_MINB
+#define BWD_MINB 14                    // resident blocks per SM the backward is compiled for
+#endif
 #ifndef BWD_PACKED
 #define BWD_PACKED 1                   // backward pixel arithmetic on packed fp32 pairs (FFMA2)
 #endif
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
 // DEPTH: the inverse-depth image is a fourth blended channel (value 1/depth_i, no background term) with its
 // own upstream gradient; it adds invd_i * gD to c_i . g and the sum of alpha T gD to acc[9].
 template <int NW, bool DEPTH>
-__global__ void __launch_bounds__(NW * 32) render_bwd_kernel(
+__global__ void __launch_bounds__(NW * 32, BWD_MINB) render_bwd_kernel(
     const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
     const float* __restrict__ depths, int W, int H, int gx, const uint32_t* __restrict__ tile_order,
     const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
