@@ -188,6 +188,27 @@ int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g, 
     return B200SPLAT_OK;
 }
 
+// Internal side stream (per thread and device) for work that runs beside the caller's stream inside one call;
+// always forked from and joined back into the caller's stream, so the call stays stream-ordered for the caller.
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+static cudaError_t side_stream(SideStream** out) {
+    static thread_local SideStream per_device[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    SideStream& ss = per_device[dev & 63];
+    if (!ss.stream) {
+        if ((e = cudaStreamCreateWithFlags(&ss.stream, cudaStreamNonBlocking)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming)) != cudaSuccess) return e;
+    }
+    *out = &ss;
+    return cudaSuccess;
+}
+
 int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
                        const void* geom, const void* binning, const void* image, int32_t num_rendered,
                        const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
@@ -226,21 +247,51 @@ int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians*
     BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, tiles_of(W, H));
     ImgView iv = carve_image(const_cast<void*>(image), W, H);
 
+    // scratch: accumulator rows [P,12] f32 | touched flags [P] u8 + counter (cleared together) | touched indices [P] u32
     const size_t acc_bytes = (size_t)P * 12 * sizeof(float);
-    float* acc = (float*)scratch_alloc(scratch_ctx, acc_bytes);
-    if (!acc) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (backward scratch)");
+    const size_t flag_bytes = ((size_t)P + 255) / 256 * 256 + 256;
+    const size_t idx_bytes = (size_t)P * sizeof(uint32_t);
+    char* scratch = (char*)scratch_alloc(scratch_ctx, acc_bytes + flag_bytes + idx_bytes);
+    if (!scratch) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (backward scratch)");
+    float* acc = (float*)scratch;
+    uint8_t* touched = (uint8_t*)(scratch + acc_bytes);
+    unsigned* active_count = (unsigned*)(scratch + acc_bytes + flag_bytes - 256);
+    uint32_t* active_idx = (uint32_t*)(scratch + acc_bytes + flag_bytes);
+
+    // Every gradient of a Gaussian the render backward never touches is exactly zero, and on a real view that is
+    // most of them: the outputs are zero-filled on a side stream WHILE the render backward runs (it leaves HBM
+    // nearly idle), and the per-Gaussian backward then visits the touched ones only.
+    SideStream* ss = nullptr;
+    CU(side_stream(&ss), "side stream");
+    CU(cudaEventRecord(ss->fork, stream), "fork");
+    CU(cudaStreamWaitEvent(ss->stream, ss->fork, 0), "fork wait");
+    {
+        const size_t n = (size_t)P * sizeof(float);
+        const b200splat_grads& o = *grads;
+        if (o.dL_dmeans2D) CU(cudaMemsetAsync(o.dL_dmeans2D, 0, 3 * n, ss->stream), "zero dL_dmeans2D");
+        if (o.dL_dcolors) CU(cudaMemsetAsync(o.dL_dcolors, 0, 3 * n, ss->stream), "zero dL_dcolors");
+        if (o.dL_dopacity) CU(cudaMemsetAsync(o.dL_dopacity, 0, n, ss->stream), "zero dL_dopacity");
+        CU(cudaMemsetAsync(o.dL_dmeans3D, 0, 3 * n, ss->stream), "zero dL_dmeans3D");
+        if (o.dL_dcov3D) CU(cudaMemsetAsync(o.dL_dcov3D, 0, 6 * n, ss->stream), "zero dL_dcov3D");
+        if (o.dL_dsh) CU(cudaMemsetAsync(o.dL_dsh, 0, 3 * (size_t)g->M * n, ss->stream), "zero dL_dsh");
+        if (o.dL_dscales) CU(cudaMemsetAsync(o.dL_dscales, 0, 3 * n, ss->stream), "zero dL_dscales");
+        if (o.dL_drotations) CU(cudaMemsetAsync(o.dL_drotations, 0, 4 * n, ss->stream), "zero dL_drotations");
+    }
+    CU(cudaEventRecord(ss->join, ss->stream), "join");
 
     StageTimer tm(times != nullptr, stream);
     tm.mark();
-    CU(cudaMemsetAsync(acc, 0, acc_bytes, stream), "clear backward scratch");
+    CU(cudaMemsetAsync(scratch, 0, acc_bytes + flag_bytes, stream), "clear backward scratch");
     if (num_rendered > 0)
-        STAGE(launch_render_bwd(*view, gv, bv.vals_sorted, iv, dL_dout_color, dL_dout_invdepth, acc, stream), "render backward");
+        STAGE(launch_render_bwd(*view, gv, bv.vals_sorted, iv, dL_dout_color, dL_dout_invdepth, acc, touched, stream), "render backward");
     tm.mark();
     if (early_colors) {
         STAGE(launch_masked_colour_grad(P, radii, gv, acc, early_colors, stream), "masked colour gradient");
         if (hooks->after_masked_colors) hooks->after_masked_colors(hooks->ctx);
     }
-    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, *grads, stream), "preprocess backward");
+    STAGE(launch_compact_active(P, touched, active_idx, active_count, stream), "compact touched Gaussians");
+    CU(cudaStreamWaitEvent(stream, ss->join, 0), "join wait");
+    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, *grads, active_idx, active_count, stream), "preprocess backward");
     tm.mark();
     if (times) {
         CU(cudaStreamSynchronize(stream), "timing sync");

@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(BS) render_fwd_classic(
 __global__ void __launch_bounds__(BS) render_bwd_classic(
     const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list, const float4* __restrict__ rec, int W, int H,
     const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
-    const float* __restrict__ dL_dpix, float* __restrict__ acc) {
+    const float* __restrict__ dL_dpix, float* __restrict__ acc, uint8_t* __restrict__ touched) {
     __shared__ uint32_t s_id[BS];
     __shared__ float2 s_xy[BS];
     __shared__ float4 s_con[BS];
@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(BS) render_bwd_classic(
             atomicAdd(dst + 3, -z * dx * dy);
             atomicAdd(dst + 4, -0.5f * z * dy * dy);
             atomicAdd(dst + 5, G * dL_dalpha);
+            touched[id] = 1;
         }
     }
 }
@@ -152,12 +153,12 @@ cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, 
 }
 
 cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
-                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
+                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, uint8_t* touched, cudaStream_t s) {
     (void)dL_dinvdepth;
     const int W = v.image_width, H = v.image_height;
     const dim3 grid((W + TILE - 1) / TILE, (H + TILE - 1) / TILE), block(TILE, TILE);
     if (grid.x * grid.y == 0) return cudaSuccess;
-    render_bwd_classic<<<grid, block, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, v.bg, iv.final_T, iv.n_contrib, dL_dpix, acc);
+    render_bwd_classic<<<grid, block, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, v.bg, iv.final_T, iv.n_contrib, dL_dpix, acc, touched);
     return cudaGetLastError();
 }
 

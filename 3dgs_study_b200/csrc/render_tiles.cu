@@ -294,7 +294,8 @@ __global__ void __launch_bounds__(NW * 32, BWD_MINB) render_bwd_kernel(
     const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
     const float* __restrict__ depths, int W, int H, int gx, const uint32_t* __restrict__ tile_order,
     const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
-    const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvd, float* __restrict__ acc) {
+    const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvd, float* __restrict__ acc,
+    uint8_t* __restrict__ touched) {
     using L = Layout<NW>;
     constexpr int TB = NW * 32, NX = L::NX, NY = L::NY, NP = L::NP;
     __shared__ float4 s_rec[TB * 3];
@@ -535,6 +536,7 @@ __global__ void __launch_bounds__(NW * 32, BWD_MINB) render_bwd_kernel(
                 if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), t0);
                 else if (lane == 1) atomicAdd(dst + 8, c2);
                 else if (DEPTH && lane == 2) atomicAdd(dst + 9, cd);
+                else if (lane == 3) touched[s_id[j]] = 1;      // this Gaussian takes part in the per-Gaussian backward
             }
         }
     }
@@ -613,17 +615,17 @@ cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, 
 }
 
 cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
-                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s) {
+                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, uint8_t* touched, cudaStream_t s) {
     const int W = v.image_width, H = v.image_height;
     const int gx = (W + TILE - 1) / TILE;
     const int T = tiles_of(W, H);
     if (T == 0) return cudaSuccess;
     if (dL_dinvdepth)
         render_bwd_kernel<BWD_NW, true><<<T, BWD_NW * 32, 0, s>>>(iv.ranges, vals_sorted, gv.rec, gv.depths, W, H, gx, iv.tile_order,
-                                                                 v.bg, iv.final_T, iv.n_contrib, dL_dpix, dL_dinvdepth, acc);
+                                                                 v.bg, iv.final_T, iv.n_contrib, dL_dpix, dL_dinvdepth, acc, touched);
     else
         render_bwd_kernel<BWD_NW, false><<<T, BWD_NW * 32, 0, s>>>(iv.ranges, vals_sorted, gv.rec, gv.depths, W, H, gx, iv.tile_order,
-                                                                  v.bg, iv.final_T, iv.n_contrib, dL_dpix, nullptr, acc);
+                                                                  v.bg, iv.final_T, iv.n_contrib, dL_dpix, nullptr, acc, touched);
     return cudaGetLastError();
 }
 

@@ -79,10 +79,16 @@ cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, 
                               float* out_invdepth, cudaStream_t s);
 // packed per-Gaussian gradient accumulator written by the render backward, 12 floats / Gaussian:
 //   (d_ndc_x, d_ndc_y are produced later)   acc[12i+0..] = (dpx, dpy, dA, dB, dC, do, dr, dg, db, dinvd, -, -)
+// touched[P] (bytes, cleared by the caller): set to 1 for every Gaussian whose accumulator row received a sum
 cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
-                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, cudaStream_t s);
+                              const float* dL_dpix, const float* dL_dinvdepth, float* acc, uint8_t* touched, cudaStream_t s);
+// indices of the touched Gaussians, in no particular order; *count (cleared by the caller) receives their number
+cudaError_t launch_compact_active(int P, const uint8_t* touched, uint32_t* active_idx, unsigned* count, cudaStream_t s);
+// Per-Gaussian backward over the touched Gaussians only: writes the rows of `out` they own and nothing else --
+// the caller has zero-filled `out` (every gradient of an untouched Gaussian is exactly zero).
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
-                                  GeomView gv, const float* acc, const b200splat_grads& out, cudaStream_t s);
+                                  GeomView gv, const float* acc, const b200splat_grads& out, const uint32_t* active_idx,
+                                  const unsigned* active_count, cudaStream_t s);
 cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
                                 unsigned long long* out14, cudaStream_t s);
 cudaError_t launch_masked_colour_grad(int P, const int32_t* radii, GeomView gv, const float* acc, float* dcol, cudaStream_t s);
