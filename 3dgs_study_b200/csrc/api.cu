@@ -218,17 +218,65 @@ int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g,
                                  nullptr, scratch_alloc, scratch_ctx, times, stream_);
 }
 
+static int backward_impl(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
+                         const void* geom, const void* binning, const void* image, int32_t num_rendered,
+                         const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
+                         const b200splat_backward_hooks* hooks, float* packed_rows, uint32_t* packed_count,
+                         b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_);
+
 int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
                           const void* geom, const void* binning, const void* image, int32_t num_rendered,
                           const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
                           const b200splat_backward_hooks* hooks, b200splat_alloc_fn scratch_alloc, void* scratch_ctx,
                           b200splat_stage_times* times, void* stream_) {
+    if (!grads || !grads->dL_dmeans3D) return fail(B200SPLAT_ERR_INVALID_ARG, "grads->dL_dmeans3D is required");
+    return backward_impl(view, g, radii, geom, binning, image, num_rendered, dL_dout_color, dL_dout_invdepth, grads, hooks,
+                         nullptr, nullptr, scratch_alloc, scratch_ctx, times, stream_);
+}
+
+int b200splat_backward_packed(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
+                              const void* geom, const void* binning, const void* image, int32_t num_rendered,
+                              const float* dL_dout_color, const float* dL_dout_invdepth, float* dL_dmeans2D,
+                              float* packed_rows, uint32_t* packed_count, b200splat_alloc_fn scratch_alloc,
+                              void* scratch_ctx, b200splat_stage_times* times, void* stream_) {
+    if (!packed_rows || !packed_count) return fail(B200SPLAT_ERR_INVALID_ARG, "null packed_rows / packed_count");
+    if (!aligned16(packed_rows)) return fail(B200SPLAT_ERR_INVALID_ARG, "packed_rows must be 16-byte aligned");
+    if (g && (!g->shs || g->cov3D_precomp || g->colors_precomp))
+        return fail(B200SPLAT_ERR_INVALID_ARG, "packed rows carry SH-mode, scale/rotation-mode gradients only");
+    b200splat_grads only2d;
+    memset(&only2d, 0, sizeof(only2d));
+    only2d.dL_dmeans2D = dL_dmeans2D;
+    return backward_impl(view, g, radii, geom, binning, image, num_rendered, dL_dout_color, dL_dout_invdepth, &only2d, nullptr,
+                         packed_rows, packed_count, scratch_alloc, scratch_ctx, times, stream_);
+}
+
+int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D, int32_t n_src,
+                                const float* const* rows, const uint32_t* const* counts, const float* campos,
+                                float* dL_dsh, float* dL_dgeom, void* stream_) {
+    if (P < 0 || M <= 0 || M > 16 || sh_degree < 0 || sh_degree > 3 || M < (sh_degree + 1) * (sh_degree + 1))
+        return fail(B200SPLAT_ERR_INVALID_ARG, "bad P / M / sh_degree");
+    if (n_src < 1 || n_src > B200SPLAT_MAX_VIEWS) return fail(B200SPLAT_ERR_INVALID_ARG, "n_src must be in [1, B200SPLAT_MAX_VIEWS]");
+    if (P == 0) return B200SPLAT_OK;
+    if (!means3D || !rows || !counts || !campos || !dL_dsh || !dL_dgeom) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
+    if (!aligned16(dL_dgeom)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dgeom must be 16-byte aligned");
+    for (int v = 0; v < n_src; v++)
+        if (!rows[v] || !counts[v]) return fail(B200SPLAT_ERR_INVALID_ARG, "null source");
+    CU(launch_accumulate_packed(P, M, sh_degree, means3D, n_src, rows, reinterpret_cast<const unsigned* const*>(counts), campos,
+                                dL_dsh, dL_dgeom, (cudaStream_t)stream_), "accumulate_packed");
+    return B200SPLAT_OK;
+}
+
+static int backward_impl(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
+                         const void* geom, const void* binning, const void* image, int32_t num_rendered,
+                         const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
+                         const b200splat_backward_hooks* hooks, float* packed_rows, uint32_t* packed_count,
+                         b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_) {
     int rc = validate(view, g);
     if (rc) return rc;
-    if (!grads || !grads->dL_dmeans3D) return fail(B200SPLAT_ERR_INVALID_ARG, "grads->dL_dmeans3D is required");
+    const bool packed = packed_rows != nullptr;
     float* early_colors = hooks ? hooks->masked_colors : nullptr;
     if (early_colors && !g->shs) return fail(B200SPLAT_ERR_INVALID_ARG, "hooks->masked_colors needs shs");
-    if (g->shs && !grads->dL_dsh && !grads->dL_dcolors && !early_colors)
+    if (!packed && g->shs && !grads->dL_dsh && !grads->dL_dcolors && !early_colors)
         return fail(B200SPLAT_ERR_INVALID_ARG, "with shs, grads->dL_dsh (or dL_dcolors for the masked colour gradient) is required");
     if (grads->dL_dsh && !aligned16(grads->dL_dsh)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dsh must be 16-byte aligned");
     if (grads->dL_drotations && !aligned16(grads->dL_drotations))
@@ -240,6 +288,7 @@ int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians*
     const int P = g->P, W = view->image_width, H = view->image_height;
     if (P == 0) {
         if (early_colors && hooks->after_masked_colors) hooks->after_masked_colors(hooks->ctx);
+        if (packed) CU(cudaMemsetAsync(packed_count, 0, sizeof(uint32_t), stream), "clear packed count");
         return B200SPLAT_OK;
     }
 
@@ -271,7 +320,7 @@ int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians*
         if (o.dL_dmeans2D) CU(cudaMemsetAsync(o.dL_dmeans2D, 0, 3 * n, ss->stream), "zero dL_dmeans2D");
         if (o.dL_dcolors) CU(cudaMemsetAsync(o.dL_dcolors, 0, 3 * n, ss->stream), "zero dL_dcolors");
         if (o.dL_dopacity) CU(cudaMemsetAsync(o.dL_dopacity, 0, n, ss->stream), "zero dL_dopacity");
-        CU(cudaMemsetAsync(o.dL_dmeans3D, 0, 3 * n, ss->stream), "zero dL_dmeans3D");
+        if (o.dL_dmeans3D) CU(cudaMemsetAsync(o.dL_dmeans3D, 0, 3 * n, ss->stream), "zero dL_dmeans3D");
         if (o.dL_dcov3D) CU(cudaMemsetAsync(o.dL_dcov3D, 0, 6 * n, ss->stream), "zero dL_dcov3D");
         if (o.dL_dsh) CU(cudaMemsetAsync(o.dL_dsh, 0, 3 * (size_t)g->M * n, ss->stream), "zero dL_dsh");
         if (o.dL_dscales) CU(cudaMemsetAsync(o.dL_dscales, 0, 3 * n, ss->stream), "zero dL_dscales");
@@ -291,7 +340,8 @@ int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians*
     }
     STAGE(launch_compact_active(P, touched, active_idx, active_count, stream), "compact touched Gaussians");
     CU(cudaStreamWaitEvent(stream, ss->join, 0), "join wait");
-    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, *grads, active_idx, active_count, stream), "preprocess backward");
+    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, *grads, active_idx, active_count, packed_rows, packed_count, stream),
+          "preprocess backward");
     tm.mark();
     if (times) {
         CU(cudaStreamSynchronize(stream), "timing sync");

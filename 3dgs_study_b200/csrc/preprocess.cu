@@ -286,6 +286,8 @@ struct BwdParams {
     b200splat_grads out;
     const uint32_t* active_idx;     // Gaussians the render backward touched (compact_active_kernel)
     const unsigned* active_count;
+    float4* packed_rows;            // packed mode (view-parallel exchange): one 64-byte row per touched Gaussian ...
+    unsigned* packed_count;         // ... and their number, instead of the dense outputs
 };
 
 __device__ __forceinline__ void store3(float* base, size_t i, float a, float b, float c) {
@@ -303,7 +305,7 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
     extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
     const PreParams& p = bp.p;
-    if (blockIdx.x * PRE_THREADS >= (int)__ldg(bp.active_count)) return;   // the grid is sized for the worst case
+    if (blockIdx.x > 0 && blockIdx.x * PRE_THREADS >= (int)__ldg(bp.active_count)) return;   // grid sized for the worst case
     load_view_consts(vc, p.view, p.proj, p.campos);
     // One thread per TOUCHED Gaussian.  A Gaussian that is on screen but never blended (hidden behind opaque splats,
     // or below 1/255 everywhere) has an all-zero accumulator row and every gradient is linear in that row: the
@@ -578,6 +580,20 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
             if (q < nq && ((vmask >> row) & 1u)) dst[(size_t)ri * nq + q] = wrows[row * RS4 + q];
         }
     }
+    if (bp.packed_rows) {
+        // row t of the packed buffer (b200splat.h "packed gradient rows"): everything the other ranks need from
+        // this view for Gaussian i, 64 bytes, written by one lane as four 16-byte stores
+        if (t == 0) *bp.packed_count = __ldg(bp.active_count);
+        if (in_range) {
+            float4* row = bp.packed_rows + 4 * (size_t)t;
+            row[0] = make_float4(__uint_as_float((unsigned)i), dcol[0], dcol[1], dcol[2]);
+            row[1] = make_float4(drot[0], drot[1], drot[2], drot[3]);
+            row[2] = make_float4(dmean[0], dmean[1], dmean[2], dsc[0]);
+            row[3] = make_float4(dsc[1], dsc[2], dop, 0.f);
+            if (o.dL_dmeans2D) store3(o.dL_dmeans2D, i, dndc[0], dndc[1], 0.f);
+        }
+        return;
+    }
     if (!in_range) return;
     store3(o.dL_dmeans3D, i, dmean[0], dmean[1], dmean[2]);
     if (o.dL_dmeans2D) store3(o.dL_dmeans2D, i, dndc[0], dndc[1], 0.f);
@@ -721,6 +737,119 @@ __global__ void __launch_bounds__(PRE_THREADS) sh_grad_from_views_kernel(int P, 
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Sparse view-parallel exchange.  A view touches a small fraction of the Gaussians (bench scene: 7 %), so each
+// rank publishes ONE 64-byte row per Gaussian its view touched (preprocess_bwd_kernel, packed mode) in memory
+// its peers can read, and every rank adds all rows of all views into its dense gradients: the row carries the
+// clamp-masked colour gradient, from which dL/dsh = Y(dir(mean_i - campos_v)) (x) dcol is rebuilt on the spot.
+// One warp per row; the 16 words of the row are one 64-byte load (over NVLink when the row is a peer's), the
+// 48 + 11 sums go out as red.global.add.f32, consecutive lanes to consecutive addresses.
+//   row: [0] index  [1..3] dcol  [4..7] d rotation  [8..10] d mean  [11..13] d scale  [14] d opacity  [15] -
+// ------------------------------------------------------------------------------------------------
+struct PackedSources {
+    int n;
+    const float* rows[B200SPLAT_MAX_VIEWS];
+    const unsigned* count[B200SPLAT_MAX_VIEWS];
+};
+
+// The row counts live next to the rows, possibly in a peer's memory: one warp fetches them once (n_src remote
+// loads) instead of every warp of the accumulate kernel hammering the same few remote words.
+__global__ void gather_counts_kernel(PackedSources src, unsigned* __restrict__ local_counts) {
+    if ((int)threadIdx.x < src.n) local_counts[threadIdx.x] = *reinterpret_cast<const volatile unsigned*>(src.count[threadIdx.x]);
+}
+
+constexpr int ACC_WARPS = 4;              // warps per block of accumulate_packed_kernel
+constexpr int ACC_RS4 = 13;               // 16-byte words per staged dL/dsh row (odd: conflict-free)
+
+__global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P, int M, int D, const float* __restrict__ means3D,
+                                                                           PackedSources src, const unsigned* __restrict__ local_counts,
+                                                                           const float* __restrict__ campos,
+                                                                           float* __restrict__ dL_dsh, float* __restrict__ dL_dgeom) {
+    // A warp takes 32 consecutive rows at a time.  Phase A, one row per lane: the 64-byte row (2 KB contiguous per
+    // warp, all loads in flight together -- one NVLink round trip per 32 rows when the rows are a peer's), the mean,
+    // the basis and the 3 M products of ITS row, staged in shared memory.  Phase B, one row per iteration, ONE
+    // instruction: lanes 0..11 add the dL/dsh row, lanes 12..14 the 48-byte geometry row, as 16-byte reductions
+    // (red.global.add.v4.f32).  The L2 retires a bounded number of atomic sectors per second (measured ~60 G/s), so
+    // the targets are laid out to touch as few sectors as possible: 6 + 2 per row.
+    __shared__ float4 s_row4[ACC_WARPS][32 * ACC_RS4];
+    __shared__ float4 s_g4[ACC_WARPS][32 * 3];
+    __shared__ unsigned s_idx[ACC_WARPS][32];            // bit 31: the row has a colour gradient
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    const int M3 = 3 * M, nb = (D + 1) * (D + 1), nq = M3 >> 2;
+    const bool vec = (M3 & 3) == 0 && nq <= 12 && (reinterpret_cast<size_t>(dL_dsh) & 15) == 0;
+    unsigned my_cnt = 0;                  // every source's row count (a local copy: gather_counts_kernel)
+    if (lane < src.n) my_cnt = __ldg(local_counts + lane);
+    // Batch-major, source-minor: the touched Gaussians of every view come in (roughly) increasing index order, so
+    // batch k of all sources lands in the same neighbourhood of the dense arrays -- a line filled for one view's
+    // row is still in L2 when the other views' rows for the same Gaussian arrive.
+    unsigned max_cnt = min(my_cnt, (unsigned)P);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) max_cnt = max(max_cnt, __shfl_xor_sync(0xffffffffu, max_cnt, d));
+    for (unsigned e0 = (unsigned)warp * 32u; e0 < max_cnt; e0 += (unsigned)n_warps * 32u) {
+        for (int v = 0; v < src.n; v++) {
+            const unsigned cnt = min(__shfl_sync(0xffffffffu, my_cnt, v), (unsigned)P);
+            if (e0 >= cnt) continue;
+            const float cx = __ldg(campos + 3 * v), cy = __ldg(campos + 3 * v + 1), cz = __ldg(campos + 3 * v + 2);
+            const float4* rows = reinterpret_cast<const float4*>(src.rows[v]);
+            const unsigned e = e0 + lane;
+            const int nrow = (int)min(32u, cnt - e0);
+            __syncwarp();
+            if (e < cnt) {
+                const float4 q0 = rows[4 * (size_t)e], q1 = rows[4 * (size_t)e + 1], q2 = rows[4 * (size_t)e + 2],
+                             q3 = rows[4 * (size_t)e + 3];
+                unsigned idx = __float_as_uint(q0.x);
+                const bool ok = idx < (unsigned)P;       // always true for a well-formed row
+                if (!ok) idx = 0;
+                const bool has_col = !(q0.y == 0.f && q0.z == 0.f && q0.w == 0.f);   // false: all channels clamped
+                s_idx[wib][lane] = ok ? (idx | (has_col ? 0x80000000u : 0u)) : 0xffffffffu;
+                s_g4[wib][lane * 3] = q1; s_g4[wib][lane * 3 + 1] = q2; s_g4[wib][lane * 3 + 2] = q3;
+                if (has_col) {
+                    const float x = __ldg(means3D + 3 * (size_t)idx), y = __ldg(means3D + 3 * (size_t)idx + 1),
+                                z = __ldg(means3D + 3 * (size_t)idx + 2);
+                    const float ddx = csub(x, cx), ddy = csub(y, cy), ddz = csub(z, cz);
+                    const float len = csqrt(cfma(ddz, ddz, cfma(ddy, ddy, cmul(ddx, ddx))));
+                    float b[16];
+                    sh_basis(D, cdiv(ddx, len), cdiv(ddy, len), cdiv(ddz, len), b);
+                    float pr[48];
+#pragma unroll
+                    for (int k = 0; k < 16; k++) {
+                        const float bk = k < nb ? b[k] : 0.f;
+                        pr[3 * k] = bk * q0.y; pr[3 * k + 1] = bk * q0.z; pr[3 * k + 2] = bk * q0.w;
+                    }
+                    float4* dstrow = s_row4[wib] + lane * ACC_RS4;
+#pragma unroll
+                    for (int q = 0; q < 12; q++)
+                        if (4 * q < M3) dstrow[q] = make_float4(pr[4 * q], pr[4 * q + 1], pr[4 * q + 2], pr[4 * q + 3]);
+                }
+            }
+            __syncwarp();
+            for (int r = 0; r < nrow; r++) {
+                const unsigned tag = s_idx[wib][r];
+                if (tag == 0xffffffffu) continue;
+                const unsigned idx = tag & 0x7fffffffu;
+                const bool has_col = (tag >> 31) != 0u;
+                if (vec) {
+                    const bool sh_lane = lane < nq;
+                    if ((sh_lane && has_col) || (lane >= 12 && lane < 15)) {
+                        float4* dst = sh_lane ? reinterpret_cast<float4*>(dL_dsh + (size_t)idx * M3) + lane
+                                              : reinterpret_cast<float4*>(dL_dgeom) + 3 * (size_t)idx + (lane - 12);
+                        const float4 val = sh_lane ? s_row4[wib][r * ACC_RS4 + lane] : s_g4[wib][r * 3 + (lane - 12)];
+                        atomicAdd(dst, val);
+                    }
+                } else {
+                    if (lane >= 12 && lane < 15)
+                        atomicAdd(reinterpret_cast<float4*>(dL_dgeom) + 3 * (size_t)idx + (lane - 12), s_g4[wib][r * 3 + (lane - 12)]);
+                    if (!has_col) continue;
+                    float* drow = dL_dsh + (size_t)idx * M3;
+                    const float* srow = reinterpret_cast<const float*>(s_row4[wib] + r * ACC_RS4);
+                    for (int el = lane; el < M3 && el < 48; el += 32) atomicAdd(drow + el, srow[el]);
+                }
+            }
+        }
+    }
+}
+
 // Densification statistics of one view in ONE pass (the reference does this with five torch ops,
 // /root/reference/scene/gaussian_model.py:576-581 and /root/reference/train.py:127):
 //   accum[i] += ||dL_dmeans2D[i, :2]||  and  denom[i] += 1   for visible Gaussians,  max_radii[i] = max(., radii[i])
@@ -809,12 +938,13 @@ cudaError_t launch_compact_active(int P, const uint8_t* touched, uint32_t* activ
 
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
                                   GeomView gv, const float* acc, const b200splat_grads& out, const uint32_t* active_idx,
-                                  const unsigned* active_count, cudaStream_t s) {
+                                  const unsigned* active_count, float* packed_rows, unsigned* packed_count, cudaStream_t s) {
     (void)gv;
     if (g.P == 0) return cudaSuccess;
     BwdParams bp;
     bp.p = make_params(v, g);
     bp.radii = radii; bp.acc = acc; bp.out = out; bp.active_idx = active_idx; bp.active_count = active_count;
+    bp.packed_rows = reinterpret_cast<float4*>(packed_rows); bp.packed_count = packed_count;
     const int M3 = 3 * g.M;
     const int coop = (g.shs && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
     const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
@@ -824,6 +954,25 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
     }
     cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop, coop_shift(M3 >> 2), out.dL_dsh ? 1 : 0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, int n_src, const float* const* rows,
+                                     const unsigned* const* counts, const float* campos, float* dL_dsh, float* dL_dgeom,
+                                     cudaStream_t s) {
+    if (P == 0 || n_src == 0) return cudaSuccess;
+    PackedSources src;
+    src.n = n_src;
+    for (int v = 0; v < n_src; v++) { src.rows[v] = rows[v]; src.count[v] = counts[v]; }
+    int dev = 0, sms = 148;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    static thread_local unsigned* counts_buf[64] = {nullptr};     // per device, 64 words, lives as long as the process
+    if (!counts_buf[dev & 63] && (e = cudaMalloc(&counts_buf[dev & 63], 64 * sizeof(unsigned))) != cudaSuccess) return e;
+    unsigned* lc = counts_buf[dev & 63];
+    gather_counts_kernel<<<1, 32, 0, s>>>(src, lc);
+    accumulate_packed_kernel<<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom);
     return cudaGetLastError();
 }
 

@@ -88,7 +88,13 @@ cudaError_t launch_compact_active(int P, const uint8_t* touched, uint32_t* activ
 // the caller has zero-filled `out` (every gradient of an untouched Gaussian is exactly zero).
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
                                   GeomView gv, const float* acc, const b200splat_grads& out, const uint32_t* active_idx,
-                                  const unsigned* active_count, cudaStream_t s);
+                                  const unsigned* active_count, float* packed_rows, unsigned* packed_count, cudaStream_t s);
+// packed_rows != NULL: instead of the dense outputs (only out.dL_dmeans2D is still written), one 64-byte row per
+// touched Gaussian and their number; launch_accumulate_packed adds the rows of any number of views (local or in
+// a peer GPU's memory) into dense gradients.
+cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, int n_src, const float* const* rows,
+                                     const unsigned* const* counts, const float* campos, float* dL_dsh, float* dL_dgeom,
+                                     cudaStream_t s);
 cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
                                 unsigned long long* out14, cudaStream_t s);
 cudaError_t launch_masked_colour_grad(int P, const int32_t* radii, GeomView gv, const float* acc, float* dcol, cudaStream_t s);

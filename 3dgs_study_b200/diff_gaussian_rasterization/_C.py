@@ -119,6 +119,13 @@ def lib():
                                                    ctypes.c_void_p]
         L.b200splat_densify_stats.restype = ctypes.c_int
         L.b200splat_densify_stats.argtypes = [ctypes.c_int32] + [ctypes.c_void_p] * 6
+        L.b200splat_backward_packed.restype = ctypes.c_int
+        L.b200splat_backward_packed.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int32] + [ctypes.c_void_p] * 5 + [
+            _alloc_fn_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_accumulate_packed.restype = ctypes.c_int
+        L.b200splat_accumulate_packed.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int32,
+                                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                                  ctypes.c_void_p]
         L.b200splat_render_stats.restype = ctypes.c_int
         L.b200splat_render_stats.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -388,6 +395,83 @@ def sh_grad_from_views(means3D, dcols, campos, M: int, degree: int, out: Optiona
                                                 _stream_ptr(dev))
     _check(rc, "sh_grad_from_views")
     return dL_dsh
+
+
+PACKED_ROW_WORDS = 16     # f32 words per packed gradient row (include/b200splat.h "packed gradient rows")
+
+
+def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rotations, scale_modifier, viewmatrix, projmatrix,
+                                        tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
+                                        imageBuffer, opacities, packed_rows, packed_count, image_height, image_width,
+                                        antialiasing=False, dL_dmeans2D=None, dL_dout_invdepth=None,
+                                        stage_times: StageTimes = None):
+    """The backward pass of one view, producing packed gradient rows (one 64-byte row per Gaussian the view touched)
+    for the sparse view-parallel exchange instead of dense gradients (b200splat_backward_packed).
+    packed_rows: fp32 CUDA tensor with room for P rows of 16 words, or the raw device address (int) of such a
+    buffer; packed_count: int32/uint32 CUDA tensor of one element, or its address.  dL_dmeans2D ([P,3], optional)
+    is still written densely (densification statistics are rank-local)."""
+    dev = means3D.device
+    P = means3D.shape[0]
+    H, W = int(image_height), int(image_width)
+    dL_dout_color = _f32c(dL_dout_color, "dL_dout_color", dev)
+    dL_dout_invdepth = _f32c(dL_dout_invdepth, "dL_dout_invdepth", dev)
+    means3D = _f32c(means3D, "means3D", dev); scales = _f32c(scales, "scales", dev)
+    rotations = _f32c(rotations, "rotations", dev); sh = _f32c(sh, "shs", dev)
+    opacities = _f32c(opacities, "opacities", dev); background = _f32c(background, "bg", dev)
+    viewmatrix = _f32c(viewmatrix, "viewmatrix", dev); projmatrix = _f32c(projmatrix, "projmatrix", dev)
+    campos = _f32c(campos, "campos", dev)
+    if sh is None or scales is None or rotations is None or opacities is None:
+        raise RuntimeError("packed rows need shs, scales, rotations and opacities")
+    M = int(sh.shape[1])
+    if isinstance(packed_rows, torch.Tensor):
+        if not (packed_rows.is_cuda and packed_rows.dtype == torch.float32 and packed_rows.is_contiguous()
+                and packed_rows.numel() >= PACKED_ROW_WORDS * P):
+            raise RuntimeError("packed_rows must be a contiguous fp32 CUDA tensor with room for P rows of 16 words")
+    if dL_dmeans2D is not None and not (dL_dmeans2D.is_cuda and dL_dmeans2D.dtype == torch.float32
+                                        and dL_dmeans2D.is_contiguous() and dL_dmeans2D.numel() == 3 * P):
+        raise RuntimeError("dL_dmeans2D must be a contiguous fp32 CUDA tensor [P,3]")
+    rows_ptr = packed_rows.data_ptr() if isinstance(packed_rows, torch.Tensor) else int(packed_rows)
+    cnt_ptr = packed_count.data_ptr() if isinstance(packed_count, torch.Tensor) else int(packed_count)
+    view = _View(H, W, float(tan_fovx), float(tan_fovy), float(scale_modifier), int(degree), 0, 0,
+                 int(bool(antialiasing)), _ptr(background), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos))
+    g = _Gaussians(P, M, _ptr(means3D), _ptr(sh), None, _ptr(opacities), _ptr(scales), _ptr(rotations), None)
+    ta = _TensorAllocator(dev)
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_backward_packed(ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer),
+                                             _ptr(binningBuffer), _ptr(imageBuffer), int(R), _ptr(dL_dout_color),
+                                             _ptr(dL_dout_invdepth), _ptr(dL_dmeans2D), rows_ptr, cnt_ptr, ta.cb, 1,
+                                             ctypes.addressof(stage_times) if stage_times is not None else None,
+                                             _stream_ptr(dev))
+    ta.release()
+    if ta.error is not None:
+        raise ta.error
+    _check(rc, "backward_packed")
+
+
+def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh, dL_dgeom):
+    """Adds the packed gradient rows of len(rows) views into dense gradients the caller has cleared: dL_dsh [P,M,3],
+    rebuilt from each row's colour gradient and its view's camera centre, and dL_dgeom [P,12] = per Gaussian
+    (d rotation[4], d mean[3], d scale[3], d opacity, 0) interleaved (b200splat_accumulate_packed).
+    rows[v] / counts[v]: tensors or raw device addresses (ints) -- e.g. a peer GPU's buffers mapped through symmetric
+    memory: the kernel then reads them over NVLink.  campos: [len(rows),3] fp32 CUDA tensor."""
+    dev = means3D.device
+    P = means3D.shape[0]
+    means3D = _f32c(means3D, "means3D", dev)
+    campos = _f32c(campos, "campos", dev)
+    n = len(rows)
+    if len(counts) != n or campos is None or campos.numel() != 3 * n:
+        raise RuntimeError("rows, counts and campos must describe the same number of views")
+    rp, cp = (ctypes.c_void_p * n)(), (ctypes.c_void_p * n)()
+    for v in range(n):
+        rp[v] = rows[v].data_ptr() if isinstance(rows[v], torch.Tensor) else int(rows[v])
+        cp[v] = counts[v].data_ptr() if isinstance(counts[v], torch.Tensor) else int(counts[v])
+    for name, t, numel in (("dL_dsh", dL_dsh, 3 * int(M) * P), ("dL_dgeom", dL_dgeom, 12 * P)):
+        if t is None or not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == numel):
+            raise RuntimeError(f"{name} must be a contiguous fp32 CUDA tensor with {numel} elements")
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_accumulate_packed(P, int(M), int(degree), _ptr(means3D), n, rp, cp, _ptr(campos),
+                                               _ptr(dL_dsh), _ptr(dL_dgeom), _stream_ptr(dev))
+    _check(rc, "accumulate_packed")
 
 
 def densify_stats(dL_dmeans2D, radii, xyz_gradient_accum, denom, max_radii2D):

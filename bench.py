@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sh-degree", type=int, default=3)
-    ap.add_argument("--exchange", default=None, choices=["allreduce", "factorized"],
+    ap.add_argument("--exchange", default=None, choices=["allreduce", "factorized", "packed"],
                     help="N>1 gradient exchange (default: factorized); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
     ap.add_argument("--peer-memory", action="store_true", help="factorized exchange through NVLink peer mappings (fused rebuild kernel + multimem all-reduce) instead of NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")

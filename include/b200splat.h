@@ -209,6 +209,33 @@ B200SPLAT_API int b200splat_sh_grad_from_views(int32_t P, int32_t M, int32_t sh_
                            int32_t n_views, const float* const* dcol, const float* campos,
                            float* dL_dsh, void* stream);
 
+/* Sparse view-parallel exchange (what the multi-GPU training step uses; the reference is single-GPU,
+ * /root/reference/train.py:86-98).  One view touches a small fraction of the Gaussians (bench scene: 7 %), and
+ * every gradient of an untouched Gaussian is exactly zero, so a rank publishes "packed gradient rows": one
+ * 64-byte row of 16 f32 words per Gaussian its view touched,
+ *   [0] index i (u32 bits)   [1..3] colour gradient x SH clamp mask   [4..7] dL/drotation
+ *   [8..10] dL/dmean3D       [11..13] dL/dscale                       [14] dL/dopacity      [15] 0
+ * b200splat_backward_packed is b200splat_backward producing these rows (packed_rows: room for P rows, 16-byte
+ * aligned; *packed_count: their number) instead of the dense gradients; SH + scale/rotation inputs only.
+ * dL_dmeans2D ([P,3], nullable) is still written densely: the densification statistics are rank-local.
+ * b200splat_accumulate_packed ADDS the rows of n_src views into dense gradients the caller has cleared:
+ * dL_dsh [P,M,3] (M <= 16), rebuilt on the spot as Y(normalize(mean_i - campos_v)) (x) colour gradient, and
+ * dL_dgeom [P,12] = words 4..15 of the rows, i.e. per Gaussian (dL/drotation[4], dL/dmean3D[3], dL/dscale[3],
+ * dL/dopacity, 0) interleaved -- one 48-byte run per Gaussian instead of four arrays, because the L2 retires
+ * a bounded number of atomic sectors per second and the exchange is bound by exactly that.  rows[v] / counts[v] are DEVICE
+ * pointers (host arrays of n_src entries) and may address a peer GPU's memory mapped into this process: the
+ * kernel then reads the peer's rows over NVLink, i.e. the exchange is this kernel -- there is no collective.
+ * campos: device array [n_src,3], the camera centre of each source view. */
+B200SPLAT_API int b200splat_backward_packed(const b200splat_view* view, const b200splat_gaussians* g,
+                       const int32_t* radii, const void* geom, const void* binning, const void* image,
+                       int32_t num_rendered, const float* dL_dout_color,
+                       const float* dL_dout_invdepth /* [1,H,W] or NULL */, float* dL_dmeans2D,
+                       float* packed_rows, uint32_t* packed_count, b200splat_alloc_fn scratch_alloc,
+                       void* scratch_ctx, b200splat_stage_times* times /* nullable */, void* stream);
+B200SPLAT_API int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D,
+                       int32_t n_src, const float* const* rows, const uint32_t* const* counts,
+                       const float* campos, float* dL_dsh, float* dL_dgeom, void* stream);
+
 /* Densification statistics of one rendered view, fused (consumers of the operator's outputs in the reference:
  * add_densification_stats, /root/reference/scene/gaussian_model.py:576-581, and the max_radii2D update,
  * /root/reference/train.py:127).  For every Gaussian with radii > 0:

@@ -160,13 +160,15 @@ def test_factorized_exchange_pieces_match_direct_path():
         params = vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations)
         bg = torch.tensor([0.2, 0.1, 0.3], device=dev)
         a = vp.ViewParallelStep(params, Dg, bg, exchange="allreduce")
-        b = vp.ViewParallelStep(params, Dg, bg, exchange="factorized")
         ca = a.step(cams, dLs)
-        cb = b.step(cams, dLs)
-        torch.cuda.synchronize()
-        assert torch.equal(ca, cb)
-        for name, x, y in zip(vp.GaussianParams._fields, a.grads(), b.grads()):
-            err = float((x - y).abs().max()) / max(float(x.abs().max()), 1e-20)
-            assert err <= 5e-4, f"P={P} D={Dg} {name}: {err}"   # float-atomic order differs run to run
-        assert torch.allclose(a.xyz_gradient_accum, b.xyz_gradient_accum, rtol=1e-5, atol=1e-12)
-        assert torch.equal(a.denom, b.denom) and torch.equal(a.max_radii2D, b.max_radii2D)
+        for mode in ("factorized", "packed"):      # packed: rows of touched Gaussians + b200splat_accumulate_packed
+            b = vp.ViewParallelStep(params, Dg, bg, exchange=mode)
+            for _ in range(2):                     # twice: the second step reuses buffers of the first
+                cb = b.step(cams, dLs)
+            torch.cuda.synchronize()
+            assert torch.equal(ca, cb)
+            for name, x, y in zip(vp.GaussianParams._fields, a.grads(), b.grads()):
+                err = float((x - y).abs().max()) / max(float(x.abs().max()), 1e-20)
+                assert err <= 5e-4, f"{mode} P={P} D={Dg} {name}: {err}"   # float-atomic order differs run to run
+            assert torch.allclose(a.xyz_gradient_accum, b.xyz_gradient_accum, rtol=1e-5, atol=1e-12)
+            assert torch.equal(a.denom, b.denom) and torch.equal(a.max_radii2D, b.max_radii2D)

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""torchrun, N >= 2 GPUs: the three exchange flavours of the view-parallel step give the same summed gradients
+"""torchrun, N >= 2 GPUs: the exchange flavours (incl. the sparse packed-row exchange over peer memory) of the view-parallel step give the same summed gradients
 (allreduce baseline == factorized over NCCL == factorized over NVLink peer memory), to float-summation noise."""
 import importlib, os, sys
 import numpy as np
@@ -21,7 +21,7 @@ for P, W, H, D in ((20000, 320, 200, 3), (4321, 200, 120, 1)):
     bg = torch.zeros(3, device=dev)
     res = {}
     for name, kw in (("allreduce", dict(exchange="allreduce")), ("nccl", dict(exchange="factorized", peer_memory=False)),
-                     ("peer", dict(exchange="factorized", peer_memory="try"))):
+                     ("peer", dict(exchange="factorized", peer_memory="try")), ("packed", dict(exchange="packed"))):
         st = vp.ViewParallelStep(params, D, bg, world_size=world, **kw)
         for _ in range(3):     # repeated steps exercise buffer reuse / the second barrier
             st.step([cam], [dL])
@@ -29,7 +29,7 @@ for P, W, H, D in ((20000, 320, 200, 3), (4321, 200, 120, 1)):
         st.reduce_densification_stats()
         res[name] = ([g.clone() for g in st.grads()], st.xyz_gradient_accum.clone(), st.denom.clone(), st.max_radii2D.clone(),
                      bool(st._symm and "flat" in st._symm))
-    for name in ("nccl", "peer"):
+    for name in ("nccl", "peer", "packed"):
         for f, a, b in zip(vp.GaussianParams._fields, res["allreduce"][0], res[name][0]):
             err = float((a - b).abs().max()) / max(float(a.abs().max()), 1e-20)
             if err > 5e-4:
