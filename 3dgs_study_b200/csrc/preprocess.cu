@@ -761,6 +761,9 @@ __global__ void gather_counts_kernel(PackedSources src, unsigned* __restrict__ l
 constexpr int ACC_WARPS = 4;              // warps per block of accumulate_packed_kernel
 constexpr int ACC_RS4 = 13;               // 16-byte words per staged dL/dsh row (odd: conflict-free)
 
+// STORE: the targets are known to hold zero and nobody else writes them while this launch runs (one source, whose
+// rows have distinct indices): plain 16-byte stores instead of reductions.
+template <bool STORE>
 __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P, int M, int D, const float* __restrict__ means3D,
                                                                            PackedSources src, const unsigned* __restrict__ local_counts,
                                                                            const float* __restrict__ campos,
@@ -835,7 +838,7 @@ __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P
                         float4* dst = sh_lane ? reinterpret_cast<float4*>(dL_dsh + (size_t)idx * M3) + lane
                                               : reinterpret_cast<float4*>(dL_dgeom) + 3 * (size_t)idx + (lane - 12);
                         const float4 val = sh_lane ? s_row4[wib][r * ACC_RS4 + lane] : s_g4[wib][r * 3 + (lane - 12)];
-                        atomicAdd(dst, val);
+                        if (STORE) *dst = val; else atomicAdd(dst, val);
                     }
                 } else {
                     if (lane >= 12 && lane < 15)
@@ -959,7 +962,7 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
 
 cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, int n_src, const float* const* rows,
                                      const unsigned* const* counts, const float* campos, float* dL_dsh, float* dL_dgeom,
-                                     cudaStream_t s) {
+                                     int store, cudaStream_t s) {
     if (P == 0 || n_src == 0) return cudaSuccess;
     PackedSources src;
     src.n = n_src;
@@ -968,11 +971,16 @@ cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, 
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    static thread_local unsigned* counts_buf[64] = {nullptr};     // per device, 64 words, lives as long as the process
+    // per device: two slots of 32 words (store / add launches may be queued back to back), lives as long as the process
+    static thread_local unsigned* counts_buf[64] = {nullptr};
     if (!counts_buf[dev & 63] && (e = cudaMalloc(&counts_buf[dev & 63], 64 * sizeof(unsigned))) != cudaSuccess) return e;
-    unsigned* lc = counts_buf[dev & 63];
+    unsigned* lc = counts_buf[dev & 63] + (store ? 32 : 0);
     gather_counts_kernel<<<1, 32, 0, s>>>(src, lc);
-    accumulate_packed_kernel<<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom);
+    const bool vec_ok = ((3 * M) & 3) == 0;     // the store flavour relies on the 16-byte path
+    if (store && vec_ok && n_src == 1)
+        accumulate_packed_kernel<true><<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom);
+    else
+        accumulate_packed_kernel<false><<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom);
     return cudaGetLastError();
 }
 

@@ -94,7 +94,7 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
 // a peer GPU's memory) into dense gradients.
 cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, int n_src, const float* const* rows,
                                      const unsigned* const* counts, const float* campos, float* dL_dsh, float* dL_dgeom,
-                                     cudaStream_t s);
+                                     int store, cudaStream_t s);
 cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
                                 unsigned long long* out14, cudaStream_t s);
 cudaError_t launch_masked_colour_grad(int P, const int32_t* radii, GeomView gv, const float* acc, float* dcol, cudaStream_t s);

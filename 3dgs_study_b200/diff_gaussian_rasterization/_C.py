@@ -125,7 +125,7 @@ def lib():
         L.b200splat_accumulate_packed.restype = ctypes.c_int
         L.b200splat_accumulate_packed.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int32,
                                                   ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
-                                                  ctypes.c_void_p]
+                                                  ctypes.c_int32, ctypes.c_void_p]
         L.b200splat_render_stats.restype = ctypes.c_int
         L.b200splat_render_stats.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -448,12 +448,13 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
     _check(rc, "backward_packed")
 
 
-def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh, dL_dgeom):
+def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh, dL_dgeom, store: bool = False):
     """Adds the packed gradient rows of len(rows) views into dense gradients the caller has cleared: dL_dsh [P,M,3],
     rebuilt from each row's colour gradient and its view's camera centre, and dL_dgeom [P,12] = per Gaussian
     (d rotation[4], d mean[3], d scale[3], d opacity, 0) interleaved (b200splat_accumulate_packed).
     rows[v] / counts[v]: tensors or raw device addresses (ints) -- e.g. a peer GPU's buffers mapped through symmetric
-    memory: the kernel then reads them over NVLink.  campos: [len(rows),3] fp32 CUDA tensor."""
+    memory: the kernel then reads them over NVLink.  campos: [len(rows),3] fp32 CUDA tensor.
+    store=True (one source): written instead of added, for the first source into freshly cleared gradients."""
     dev = means3D.device
     P = means3D.shape[0]
     means3D = _f32c(means3D, "means3D", dev)
@@ -470,7 +471,7 @@ def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh
             raise RuntimeError(f"{name} must be a contiguous fp32 CUDA tensor with {numel} elements")
     with torch.cuda.device(dev):
         rc = lib().b200splat_accumulate_packed(P, int(M), int(degree), _ptr(means3D), n, rp, cp, _ptr(campos),
-                                               _ptr(dL_dsh), _ptr(dL_dgeom), _stream_ptr(dev))
+                                               _ptr(dL_dsh), _ptr(dL_dgeom), int(bool(store)), _stream_ptr(dev))
     _check(rc, "accumulate_packed")
 
 

@@ -113,7 +113,12 @@ class ViewParallelStep:
         # default = the CUDA library through _C, CPU tests inject a torch stand-in
         self._backend = backend
         if exchange is None:
-            exchange = "factorized" if (world_size > 1 and rasterize is None) else "allreduce"
+            # N > 1 on CUDA: the sparse packed-row exchange over peer memory; with an injected backend (CPU tests):
+            # the factorized exchange over the process group; with an injected rasterizer: plain all-reduce
+            if world_size > 1 and rasterize is None:
+                exchange = "packed" if (backend is None and dev.type == "cuda") else "factorized"
+            else:
+                exchange = "allreduce"
         if exchange not in ("allreduce", "factorized", "packed"):
             raise ValueError("exchange must be 'allreduce', 'factorized' or 'packed'")
         self.exchange = exchange
@@ -165,6 +170,14 @@ class ViewParallelStep:
         if self.exchange == "factorized":
             return self._step_factorized(cams, dL_images, reduce, on_forward)
         if self.exchange == "packed":
+            if self.world_size > 1 and reduce and self._packed is None:
+                try:
+                    self._setup_packed(self.leaves.means3D.shape[0], len(cams), self.leaves.means3D.device)
+                except Exception as e:      # no peer mappings on this system: the NCCL flavour of the exchange
+                    import warnings
+                    warnings.warn(f"packed exchange unavailable ({e!r}); using the factorized NCCL exchange")
+                    self.exchange = "factorized"
+                    return self._step_factorized(cams, dL_images, reduce, on_forward)
             return self._step_packed(cams, dL_images, reduce, on_forward)
         for t in self.leaves:
             t.grad = None
@@ -212,8 +225,6 @@ class ViewParallelStep:
         dev = lv.means3D.device
         G = self.world_size if reduce else 1
         nv = len(cams)
-        if G * nv > 16:
-            raise ValueError("packed exchange: at most 16 views per step (B200SPLAT_MAX_VIEWS)")
         self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         main = torch.cuda.current_stream(dev)
         if self._side is None:
@@ -251,20 +262,25 @@ class ViewParallelStep:
             self.last_radii = radii
         self.stats_reduced = self.world_size == 1
         main.wait_event(cleared)
+        # this rank's own rows go in first, before the barrier (i.e. while the slower peers are still rendering):
+        # the first view is WRITTEN into the freshly cleared gradients (plain stores), further local views are added
+        C.accumulate_packed(lv.means3D, [base[0] + 64], [base[0]], campos[0:1], M, self.sh_degree, dsh, geom, store=True)
+        if nv > 1:
+            C.accumulate_packed(lv.means3D, [b + 64 for b in base[1:]], base[1:], campos[1:], M, self.sh_degree, dsh, geom)
         if G > 1:
             main.wait_event(gathered)
             all_campos.record_stream(main)
             pk["hd"].barrier(channel=0)                 # every rank's rows are in place
-            # every rank starts with its own rows and walks the peers in a different rotation, so that at any moment
-            # the eight ranks read from eight different peers
+            # the peers' rows, read over NVLink; each rank walks its peers in a different rotation, so that at any
+            # moment the ranks read from different peers
             me = dist.get_rank(self.group)
-            order = [(me + j) % G for j in range(G)]
+            order = [(me + j) % G for j in range(1, G)]
             bases = [pk["ptrs"][r] + 4 * k * pk["stride"] for r in order for k in range(nv)]
-            all_campos = all_campos.view(G, nv, 3)[order].reshape(G * nv, 3).contiguous()
-        else:
-            bases = base
-        C.accumulate_packed(lv.means3D, [b + 64 for b in bases], bases, all_campos, M, self.sh_degree, dsh, geom)
-        if G > 1:
+            peers_campos = torch.roll(all_campos.view(G, nv, 3), shifts=-me, dims=0)[1:].reshape((G - 1) * nv, 3)
+            for lo in range(0, len(bases), 16):         # B200SPLAT_MAX_VIEWS sources per launch
+                hi = min(lo + 16, len(bases))
+                C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], peers_campos[lo:hi].contiguous(),
+                                    M, self.sh_degree, dsh, geom)
             pk["hd"].barrier(channel=1)                 # every rank has read them: the next step may overwrite
         # the geometry gradients are strided views of the interleaved [P,12] rows
         self.leaves.rotations.grad = geom[:, 0:4]
@@ -470,12 +486,15 @@ class ViewParallelStep:
         return self.leaves.means3D.grad.sum() + self.leaves.opacities.grad.sum()
 
     # -- measurement helpers (CUDA path only) ------------------------------------------------------------
-    @staticmethod
-    def launches_per_view() -> int:
-        """Kernels of THIS library launched per view fwd+bwd (single GPU step): preprocess, duplicateWithKeys (emit),
-        identifyTileRanges, tile order, render fwd, render bwd, per-Gaussian bwd, densification statistics (CUB
-        scan / sort passes and memsets are library / driver work and are not counted)."""
-        return 8
+    def launches_per_view(self=None) -> int:
+        """Kernels of THIS library launched per view fwd+bwd: preprocess, duplicateWithKeys (emit), identifyTileRanges,
+        tile order, render fwd, render bwd, compaction of the touched Gaussians, per-Gaussian bwd, densification
+        statistics -- plus, in the packed exchange, the count gather + accumulate kernels for the rank's own rows and
+        for its peers' (CUB scan / sort passes and memsets are library / driver work and are not counted)."""
+        n = 9
+        if self is not None and getattr(self, "exchange", None) == "packed":
+            n += 2 + (2 if self.world_size > 1 else 0)
+        return n
 
     def stage_profile(self, cam, dL, iters: int = 5):
         """Per-stage device milliseconds (CUDA events on the launch stream, inside the library) averaged

@@ -327,8 +327,9 @@ def run_ours(a):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a), "gaussians": P, "sh_degree": D, "width": W, "height": H,
                    "visible": stats.get("visible"), "tile_pairs_R": stats.get("R"), "views_per_rank_per_step": 1,
-                   "parallelism": f"view-parallel x{world}, Gaussians replicated" + ((", exchange=" + stepper.exchange + (": NCCL all-gather of [P,3] masked colour grads + all-reduce of 11 f32/Gaussian, dL/dsh rebuilt locally"
-                                                                          if stepper.exchange == "factorized" else ": NCCL sum-allreduce of 59 f32/Gaussian grads")) if world > 1 else ""),
+                   "parallelism": f"view-parallel x{world}, Gaussians replicated" + ((", exchange=" + stepper.exchange + ({"factorized": ": NCCL all-gather of [P,3] masked colour grads + all-reduce of 11 f32/Gaussian, dL/dsh rebuilt locally",
+                                                                           "packed": ": one 64-byte gradient row per Gaussian a view touched, read from every peer over NVLink by the kernel that adds them into the dense gradients (no collective on the data path)"}
+                                                                          .get(stepper.exchange, ": NCCL sum-allreduce of 59 f32/Gaussian grads"))) if world > 1 else ""),
                    "l2_note": "inputs (0.7 GB of Gaussians + 0.2 GB of keys per view) exceed the 126 MB L2; a different view every step"},
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": round(ms_e2e / a.steps, 4),

@@ -225,7 +225,10 @@ B200SPLAT_API int b200splat_sh_grad_from_views(int32_t P, int32_t M, int32_t sh_
  * a bounded number of atomic sectors per second and the exchange is bound by exactly that.  rows[v] / counts[v] are DEVICE
  * pointers (host arrays of n_src entries) and may address a peer GPU's memory mapped into this process: the
  * kernel then reads the peer's rows over NVLink, i.e. the exchange is this kernel -- there is no collective.
- * campos: device array [n_src,3], the camera centre of each source view. */
+ * campos: device array [n_src,3], the camera centre of each source view.
+ * store != 0 (n_src must be 1): the rows are WRITTEN instead of added -- for the first source into freshly
+ * cleared gradients, e.g. a rank's own rows while it waits for its peers; nothing else may write the
+ * gradients while that launch runs. */
 B200SPLAT_API int b200splat_backward_packed(const b200splat_view* view, const b200splat_gaussians* g,
                        const int32_t* radii, const void* geom, const void* binning, const void* image,
                        int32_t num_rendered, const float* dL_dout_color,
@@ -234,7 +237,7 @@ B200SPLAT_API int b200splat_backward_packed(const b200splat_view* view, const b2
                        void* scratch_ctx, b200splat_stage_times* times /* nullable */, void* stream);
 B200SPLAT_API int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D,
                        int32_t n_src, const float* const* rows, const uint32_t* const* counts,
-                       const float* campos, float* dL_dsh, float* dL_dgeom, void* stream);
+                       const float* campos, float* dL_dsh, float* dL_dgeom, int32_t store, void* stream);
 
 /* Densification statistics of one rendered view, fused (consumers of the operator's outputs in the reference:
  * add_densification_stats, /root/reference/scene/gaussian_model.py:576-581, and the max_radii2D update,
