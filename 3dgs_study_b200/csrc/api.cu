@@ -116,6 +116,11 @@ int validate(const b200splat_view* v, const b200splat_gaussians* g) {
 
 }  // namespace
 
+// error string shared with the other translation units (next_steps.cu, ply_io.cu)
+namespace b200splat {
+int report_error(int code, const char* msg) { return fail(code, msg); }
+}
+
 extern "C" {
 
 const char* b200splat_last_error(void) { return g_last_error.c_str(); }

@@ -1,0 +1,590 @@
+// next_steps.cu -- the steps either side of the rasterizer (include/b200splat_next.h): fused L1 + SSIM loss
+// forward / backward, one-launch Adam over all parameter groups, exact 3-nearest-neighbour mean squared
+// distance.  sm_100a; all of it HBM / shared-memory bound elementwise and stencil work.
+//
+// L1 + SSIM.  A block owns a 32x32 output tile of one plane: the two input tiles with a 5-pixel halo are staged
+// in shared memory once (zero outside the image = the zero padding of F.conv2d), the five products are filtered
+// along x into shared memory, then along y in registers (each thread produces a 4-row column strip from 14
+// staged values per quantity), and the SSIM map, its three partial derivatives and the block's sums leave the
+// SM once.  Algorithmic HBM bytes per pixel and plane: forward 8 in + 12 out, backward 20 in + 4 out.
+// The sums are reduced deterministically: per-block partials, then one block per plane in double.
+#include <cfloat>
+#include <cmath>
+#include <cub/cub.cuh>
+#include <string>
+
+#include "../../include/b200splat_next.h"
+#include "splat_internal.cuh"
+
+using namespace b200splat;
+
+namespace {
+
+constexpr int LT = 32;              // output tile edge
+constexpr int LR = 5;               // window radius (11 taps)
+constexpr int LIN = LT + 2 * LR;    // staged tile edge (42)
+constexpr int LPITCH = LIN + 2;     // shared-memory row pitch
+constexpr int LTHREADS = 256;
+constexpr int LROWS = LT / (LTHREADS / 32);   // rows per thread in the y pass (4)
+
+struct Taps { float w[2 * LR + 1]; };
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// y pass of one quantity for this thread's column: LROWS outputs from LROWS + 10 staged rows
+__device__ __forceinline__ void ypass(const float (*col)[LT], int r0, int tx, const Taps& tw, float* out) {
+    float v[LROWS + 2 * LR];
+#pragma unroll
+    for (int i = 0; i < LROWS + 2 * LR; ++i) v[i] = col[r0 + i][tx];
+#pragma unroll
+    for (int j = 0; j < LROWS; ++j) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 2 * LR + 1; ++k) acc = fmaf(tw.w[k], v[j + k], acc);
+        out[j] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(LTHREADS)
+l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, Taps tw,
+                   float* __restrict__ maps, size_t map_stride, float2* __restrict__ partials) {
+    __shared__ float sa[LIN][LPITCH];
+    __shared__ float sb[LIN][LPITCH];
+    __shared__ float sh[5][LIN][LT];
+    __shared__ float red[2][LTHREADS / 32];
+
+    const int plane = blockIdx.z;
+    const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
+    const size_t pbase = (size_t)plane * H * W;
+    const float* A = img + pbase;
+    const float* B = gt + pbase;
+
+    for (int i = threadIdx.x; i < LIN * LIN; i += LTHREADS) {
+        int r = i / LIN, c = i - r * LIN;
+        int y = y0 + r - LR, x = x0 + c - LR;
+        bool in = (y >= 0) && (y < H) && (x >= 0) && (x < W);
+        size_t o = in ? ((size_t)y * W + x) : 0;
+        sa[r][c] = in ? __ldg(A + o) : 0.0f;
+        sb[r][c] = in ? __ldg(B + o) : 0.0f;
+    }
+    __syncthreads();
+
+    // x pass: 42 rows x 32 columns, five quantities
+    for (int i = threadIdx.x; i < LIN * LT; i += LTHREADS) {
+        int r = i >> 5, c = i & 31;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f, s4 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 2 * LR + 1; ++k) {
+            float a = sa[r][c + k], b = sb[r][c + k], w = tw.w[k];
+            s0 = fmaf(w, a, s0);
+            s1 = fmaf(w, b, s1);
+            s2 = fmaf(w, __fmul_rn(a, a), s2);
+            s3 = fmaf(w, __fmul_rn(b, b), s3);
+            s4 = fmaf(w, __fmul_rn(a, b), s4);
+        }
+        sh[0][r][c] = s0; sh[1][r][c] = s1; sh[2][r][c] = s2; sh[3][r][c] = s3; sh[4][r][c] = s4;
+    }
+    __syncthreads();
+
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int r0 = ty * LROWS;
+    float mu1[LROWS], mu2[LROWS], e11[LROWS], e22[LROWS], e12[LROWS];
+    ypass(sh[0], r0, tx, tw, mu1);
+    ypass(sh[1], r0, tx, tw, mu2);
+    ypass(sh[2], r0, tx, tw, e11);
+    ypass(sh[3], r0, tx, tw, e22);
+    ypass(sh[4], r0, tx, tw, e12);
+
+    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+    float l1 = 0.0f, ss = 0.0f;
+    const int x = x0 + tx;
+#pragma unroll
+    for (int j = 0; j < LROWS; ++j) {
+        int y = y0 + r0 + j;
+        if (x < W && y < H) {
+            float m1 = mu1[j], m2 = mu2[j];
+            float m11 = m1 * m1, m22 = m2 * m2, m12 = m1 * m2;
+            float s1 = e11[j] - m11, s2 = e22[j] - m22, s12 = e12[j] - m12;
+            float An = 2.0f * m12 + C1, Bn = 2.0f * s12 + C2;
+            float Cd = m11 + m22 + C1, Dd = s1 + s2 + C2;
+            float inv = 1.0f / (Cd * Dd);
+            float m = An * Bn * inv;
+            ss += m;
+            l1 += fabsf(sa[r0 + j + LR][tx + LR] - sb[r0 + j + LR][tx + LR]);
+            if (maps) {
+                size_t o = pbase + (size_t)y * W + x;
+                maps[o] = 2.0f * inv * (m2 * (Bn - An) - m1 * m * (Dd - Cd));
+                maps[map_stride + o] = -m / Dd;
+                maps[2 * map_stride + o] = 2.0f * An * inv;
+            }
+        }
+    }
+    l1 = warp_sum(l1);
+    ss = warp_sum(ss);
+    if (tx == 0) { red[0][ty] = l1; red[1][ty] = ss; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a = 0.f, b = 0.f;
+#pragma unroll
+        for (int i = 0; i < LTHREADS / 32; ++i) { a += red[0][i]; b += red[1][i]; }
+        size_t blk = ((size_t)plane * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        partials[blk] = make_float2(a, b);
+    }
+}
+
+// one block per plane: fixed-order sum of that plane's block partials in double -> per-plane means
+__global__ void __launch_bounds__(256)
+l1_ssim_finalize_kernel(int blocks_per_plane, double inv_count, const float2* __restrict__ partials, float* __restrict__ out) {
+    __shared__ double sl[256], ssm[256];
+    const float2* p = partials + (size_t)blockIdx.x * blocks_per_plane;
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < blocks_per_plane; i += 256) { float2 v = p[i]; a += (double)v.x; b += (double)v.y; }
+    sl[threadIdx.x] = a; ssm[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { sl[threadIdx.x] += sl[threadIdx.x + o]; ssm[threadIdx.x] += ssm[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        out[2 * blockIdx.x] = (float)(sl[0] * inv_count);
+        out[2 * blockIdx.x + 1] = (float)(ssm[0] * inv_count);
+    }
+}
+
+__global__ void __launch_bounds__(LTHREADS)
+l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, Taps tw,
+                   const float* __restrict__ maps, size_t map_stride, const float* __restrict__ scale,
+                   float* __restrict__ dimg) {
+    __shared__ float sm[3][LIN][LPITCH];
+    __shared__ float sh[3][LIN][LT];
+
+    const int plane = blockIdx.z;
+    const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
+    const size_t pbase = (size_t)plane * H * W;
+
+    for (int i = threadIdx.x; i < LIN * LIN; i += LTHREADS) {
+        int r = i / LIN, c = i - r * LIN;
+        int y = y0 + r - LR, x = x0 + c - LR;
+        bool in = (y >= 0) && (y < H) && (x >= 0) && (x < W);
+        size_t o = in ? (pbase + (size_t)y * W + x) : 0;
+        sm[0][r][c] = in ? __ldg(maps + o) : 0.0f;
+        sm[1][r][c] = in ? __ldg(maps + map_stride + o) : 0.0f;
+        sm[2][r][c] = in ? __ldg(maps + 2 * map_stride + o) : 0.0f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < LIN * LT; i += LTHREADS) {
+        int r = i >> 5, c = i & 31;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 2 * LR + 1; ++k) {
+            float w = tw.w[k];
+            s0 = fmaf(w, sm[0][r][c + k], s0);
+            s1 = fmaf(w, sm[1][r][c + k], s1);
+            s2 = fmaf(w, sm[2][r][c + k], s2);
+        }
+        sh[0][r][c] = s0; sh[1][r][c] = s1; sh[2][r][c] = s2;
+    }
+    __syncthreads();
+
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int r0 = ty * LROWS;
+    float f0[LROWS], f1[LROWS], f2[LROWS];
+    ypass(sh[0], r0, tx, tw, f0);
+    ypass(sh[1], r0, tx, tw, f1);
+    ypass(sh[2], r0, tx, tw, f2);
+    const float sl = __ldg(scale + 2 * plane), ssc = __ldg(scale + 2 * plane + 1);
+    const int x = x0 + tx;
+#pragma unroll
+    for (int j = 0; j < LROWS; ++j) {
+        int y = y0 + r0 + j;
+        if (x < W && y < H) {
+            size_t o = pbase + (size_t)y * W + x;
+            float a = __ldg(img + o), b = __ldg(gt + o);
+            float d = a - b;
+            float sg = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);
+            float g = f0[j] + 2.0f * a * f1[j] + b * f2[j];
+            dimg[o] = sl * sg + ssc * g;
+        }
+    }
+}
+
+// ---- Adam ------------------------------------------------------------------------------------------------
+constexpr int ADAM_THREADS = 256;
+constexpr int ADAM_PER_BLOCK = ADAM_THREADS * 16;   // 4 x float4 per thread
+
+struct AdamLaunch {
+    float* p[B200SPLAT_ADAM_MAX_GROUPS];
+    const float* g[B200SPLAT_ADAM_MAX_GROUPS];
+    float* m[B200SPLAT_ADAM_MAX_GROUPS];
+    float* v[B200SPLAT_ADAM_MAX_GROUPS];
+    long long n[B200SPLAT_ADAM_MAX_GROUPS];
+    float step_size[B200SPLAT_ADAM_MAX_GROUPS];
+    float bc2_sqrt[B200SPLAT_ADAM_MAX_GROUPS];
+    unsigned block_start[B200SPLAT_ADAM_MAX_GROUPS + 1];
+    int vec[B200SPLAT_ADAM_MAX_GROUPS];
+    int ng;
+    float beta2, w1, w2, eps;
+};
+
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float step_size, float bc2_sqrt,
+                                         float beta2, float w1, float w2, float eps) {
+    float mi = __fmaf_rn(__fsub_rn(g, m), w1, m);                    // m + (g - m) * (1 - beta1)
+    float vi = __fmaf_rn(__fmul_rn(w2, g), g, __fmul_rn(v, beta2));  // v * beta2 + ((1 - beta2) * g) * g
+    float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), bc2_sqrt), eps);
+    p = __fmaf_rn(-step_size, __fdiv_rn(mi, denom), p);
+    m = mi;
+    v = vi;
+}
+
+__global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const AdamLaunch L) {
+    int gi = 0;
+#pragma unroll
+    for (int i = 1; i < B200SPLAT_ADAM_MAX_GROUPS; ++i)
+        if (i < L.ng && blockIdx.x >= L.block_start[i]) gi = i;
+    float* __restrict__ P = L.p[gi];
+    const float* __restrict__ G = L.g[gi];
+    float* __restrict__ M = L.m[gi];
+    float* __restrict__ V = L.v[gi];
+    const long long n = L.n[gi];
+    const float step_size = L.step_size[gi], bc2_sqrt = L.bc2_sqrt[gi];
+    const long long base = (long long)(blockIdx.x - L.block_start[gi]) * ADAM_PER_BLOCK;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+        long long e = base + ((long long)it * ADAM_THREADS + threadIdx.x) * 4;
+        if (e >= n) continue;
+        if (L.vec[gi] && e + 4 <= n) {
+            float4 p = *reinterpret_cast<const float4*>(P + e);
+            float4 g = __ldg(reinterpret_cast<const float4*>(G + e));
+            float4 m = *reinterpret_cast<const float4*>(M + e);
+            float4 v = *reinterpret_cast<const float4*>(V + e);
+            adam_one(p.x, g.x, m.x, v.x, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            adam_one(p.y, g.y, m.y, v.y, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            adam_one(p.z, g.z, m.z, v.z, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            adam_one(p.w, g.w, m.w, v.w, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            *reinterpret_cast<float4*>(P + e) = p;
+            *reinterpret_cast<float4*>(M + e) = m;
+            *reinterpret_cast<float4*>(V + e) = v;
+        } else {
+            for (int j = 0; j < 4 && e + j < n; ++j) {
+                float p = P[e + j], m = M[e + j], v = V[e + j];
+                adam_one(p, G[e + j], m, v, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+                P[e + j] = p; M[e + j] = m; V[e + j] = v;
+            }
+        }
+    }
+}
+
+// ---- 3 nearest neighbours ----------------------------------------------------------------------------------
+constexpr int KBOX = 64;          // points per leaf box (sorted by Morton code)
+constexpr int KSUPER = 64;        // leaf boxes per super box
+
+struct Box { float lo[3]; float hi[3]; };
+
+__device__ __forceinline__ unsigned expand10(unsigned x) {   // 10 bits -> every third bit
+    x = (x | (x << 16)) & 0x030000FFu;
+    x = (x | (x << 8)) & 0x0300F00Fu;
+    x = (x | (x << 4)) & 0x030C30C3u;
+    x = (x | (x << 2)) & 0x09249249u;
+    return x;
+}
+
+// ordered-int encoding of a float so that integer min/max are float min/max
+__device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7FFFFFFF; }
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
+
+__global__ void knn_bounds_init_kernel(int* b6) {
+    if (threadIdx.x < 3) b6[threadIdx.x] = 0x7FFFFFFF;             // min
+    else if (threadIdx.x < 6) b6[threadIdx.x] = (int)0x80000000;   // max
+}
+
+__global__ void __launch_bounds__(256) knn_bounds_kernel(int P, const float* __restrict__ xyz, int* __restrict__ b6) {
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (long long)gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { float c = xyz[3 * i + k]; lo[k] = fminf(lo[k], c); hi[k] = fmaxf(hi[k], c); }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { atomicMin(b6 + k, f2ord(lo[k])); atomicMax(b6 + 3 + k, f2ord(hi[k])); }
+    }
+}
+
+__global__ void __launch_bounds__(256) knn_morton_kernel(int P, const float* __restrict__ xyz, const int* __restrict__ b6,
+                                                         unsigned* __restrict__ codes, unsigned* __restrict__ ids) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    unsigned code = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float lo = ord2f(b6[k]), hi = ord2f(b6[3 + k]);
+        float ext = hi - lo;
+        float t = ext > 0.0f ? (xyz[3 * i + k] - lo) / ext : 0.0f;
+        t = fminf(fmaxf(t, 0.0f), 1.0f);          // NaN -> 0
+        unsigned q = (unsigned)(t * 1023.0f);
+        code |= expand10(q > 1023u ? 1023u : q) << k;
+    }
+    codes[i] = code;
+    ids[i] = (unsigned)i;
+}
+
+// points gathered into Morton order (float4: x, y, z, unused) + leaf boxes of KBOX consecutive points
+__global__ void __launch_bounds__(KBOX) knn_gather_boxes_kernel(int P, const float* __restrict__ xyz,
+                                                                const unsigned* __restrict__ ids_sorted,
+                                                                float4* __restrict__ pts, Box* __restrict__ boxes) {
+    int i = blockIdx.x * KBOX + threadIdx.x;
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (i < P) {
+        unsigned id = ids_sorted[i];
+        float x = xyz[3 * (size_t)id], y = xyz[3 * (size_t)id + 1], z = xyz[3 * (size_t)id + 2];
+        pts[i] = make_float4(x, y, z, 0.0f);
+        lo[0] = hi[0] = x; lo[1] = hi[1] = y; lo[2] = hi[2] = z;
+    }
+    __shared__ float slo[KBOX / 32][3], shi[KBOX / 32][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+        if ((threadIdx.x & 31) == 0) { slo[threadIdx.x >> 5][k] = lo[k]; shi[threadIdx.x >> 5][k] = hi[k]; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        Box b;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            b.lo[k] = fminf(slo[0][k], slo[1][k]);
+            b.hi[k] = fmaxf(shi[0][k], shi[1][k]);
+        }
+        boxes[blockIdx.x] = b;
+    }
+}
+
+__global__ void __launch_bounds__(KSUPER) knn_super_boxes_kernel(int n_boxes, const Box* __restrict__ boxes, Box* __restrict__ supers) {
+    int i = blockIdx.x * KSUPER + threadIdx.x;
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (i < n_boxes) {
+        Box b = boxes[i];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { lo[k] = b.lo[k]; hi[k] = b.hi[k]; }
+    }
+    __shared__ float slo[KSUPER / 32][3], shi[KSUPER / 32][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+        if ((threadIdx.x & 31) == 0) { slo[threadIdx.x >> 5][k] = lo[k]; shi[threadIdx.x >> 5][k] = hi[k]; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        Box b;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            b.lo[k] = fminf(slo[0][k], slo[1][k]);
+            b.hi[k] = fmaxf(shi[0][k], shi[1][k]);
+        }
+        supers[blockIdx.x] = b;
+    }
+}
+
+// squared distance in the one canonical form every comparison uses; per-axis monotone, so a box's value never
+// exceeds that of any point inside it and pruning on it is exact
+__device__ __forceinline__ float dist2(float dx, float dy, float dz) {
+    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+}
+__device__ __forceinline__ float box_dist2(const Box& b, float x, float y, float z) {
+    float dx = fmaxf(0.0f, fmaxf(__fsub_rn(b.lo[0], x), __fsub_rn(x, b.hi[0])));
+    float dy = fmaxf(0.0f, fmaxf(__fsub_rn(b.lo[1], y), __fsub_rn(y, b.hi[1])));
+    float dz = fmaxf(0.0f, fmaxf(__fsub_rn(b.lo[2], z), __fsub_rn(z, b.hi[2])));
+    return dist2(dx, dy, dz);
+}
+__device__ __forceinline__ void push3(float* best, float d) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+        if (best[k] > d) { float t = best[k]; best[k] = d; d = t; }
+}
+__device__ __forceinline__ void scan_leaf(int P, const float4* __restrict__ pts, int box, int self, float x, float y,
+                                          float z, float* best) {
+    int lo = box * KBOX, hi = min(P, lo + KBOX);
+    for (int j = lo; j < hi; ++j) {
+        if (j == self) continue;
+        float4 q = __ldg(pts + j);
+        push3(best, dist2(__fsub_rn(q.x, x), __fsub_rn(q.y, y), __fsub_rn(q.z, z)));
+    }
+}
+
+__global__ void __launch_bounds__(128) knn_search_kernel(int P, const float4* __restrict__ pts,
+                                                         const unsigned* __restrict__ ids_sorted, int n_boxes,
+                                                         const Box* __restrict__ boxes, int n_supers,
+                                                         const Box* __restrict__ supers, float* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    float4 me = pts[i];
+    float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+    const int own = i / KBOX;
+    scan_leaf(P, pts, own, i, me.x, me.y, me.z, best);
+    for (int s = 0; s < n_supers; ++s) {
+        Box sb = supers[s];
+        if (box_dist2(sb, me.x, me.y, me.z) > best[2]) continue;
+        int b1 = min(n_boxes, (s + 1) * KSUPER);
+        for (int b = s * KSUPER; b < b1; ++b) {
+            if (b == own) continue;
+            Box lb = boxes[b];
+            if (box_dist2(lb, me.x, me.y, me.z) > best[2]) continue;
+            scan_leaf(P, pts, b, i, me.x, me.y, me.z, best);
+        }
+    }
+    out[ids_sorted[i]] = __fdiv_rn(__fadd_rn(__fadd_rn(best[0], best[1]), best[2]), 3.0f);
+}
+
+inline bool aligned16p(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+#define CUN(call, where)                                                                   \
+    do {                                                                                   \
+        cudaError_t _e = (call);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            std::string _m = std::string(where) + ": " + cudaGetErrorString(_e);           \
+            return report_error(B200SPLAT_ERR_CUDA, _m.c_str());                           \
+        }                                                                                  \
+    } while (0)
+
+inline int tiles_1d(int n) { return (n + LT - 1) / LT; }
+
+}  // namespace
+
+extern "C" {
+
+size_t b200splat_l1_ssim_partials(int32_t planes, int32_t height, int32_t width) {
+    if (planes <= 0 || height <= 0 || width <= 0) return 0;
+    return (size_t)planes * tiles_1d(height) * tiles_1d(width);
+}
+
+int b200splat_l1_ssim_forward(int32_t planes, int32_t height, int32_t width, const float* img, const float* gt,
+                              const float* window11, float* maps, float* partials, float* out, void* stream_) {
+    if (planes <= 0 || height <= 0 || width <= 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: bad sizes");
+    if (planes > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: more than 65535 planes");
+    if (!img || !gt || !window11 || !partials || !out) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: null argument");
+    cudaStream_t s = (cudaStream_t)stream_;
+    Taps tw;
+    for (int k = 0; k < 2 * LR + 1; ++k) tw.w[k] = window11[k];
+    dim3 grid(tiles_1d(width), tiles_1d(height), planes);
+    if (grid.y > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: image too tall");
+    l1_ssim_fwd_kernel<<<grid, LTHREADS, 0, s>>>(height, width, img, gt, tw, maps, (size_t)planes * height * width,
+                                                 reinterpret_cast<float2*>(partials));
+    CUN(cudaGetLastError(), "l1_ssim forward");
+    l1_ssim_finalize_kernel<<<planes, 256, 0, s>>>((int)(grid.x * grid.y), 1.0 / ((double)height * (double)width),
+                                                   reinterpret_cast<const float2*>(partials), out);
+    CUN(cudaGetLastError(), "l1_ssim finalize");
+    return B200SPLAT_OK;
+}
+
+int b200splat_l1_ssim_backward(int32_t planes, int32_t height, int32_t width, const float* img, const float* gt,
+                               const float* window11, const float* maps, const float* scale, float* dL_dimg,
+                               void* stream_) {
+    if (planes <= 0 || height <= 0 || width <= 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: bad sizes");
+    if (planes > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: more than 65535 planes");
+    if (!img || !gt || !window11 || !maps || !scale || !dL_dimg) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: null argument");
+    Taps tw;
+    for (int k = 0; k < 2 * LR + 1; ++k) tw.w[k] = window11[k];
+    dim3 grid(tiles_1d(width), tiles_1d(height), planes);
+    if (grid.y > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: image too tall");
+    l1_ssim_bwd_kernel<<<grid, LTHREADS, 0, (cudaStream_t)stream_>>>(height, width, img, gt, tw, maps,
+                                                                     (size_t)planes * height * width, scale, dL_dimg);
+    CUN(cudaGetLastError(), "l1_ssim backward");
+    return B200SPLAT_OK;
+}
+
+int b200splat_adam_step(int32_t n_groups, const b200splat_adam_group* groups, double beta1, double beta2, double eps,
+                        void* stream_) {
+    if (n_groups < 0 || n_groups > B200SPLAT_ADAM_MAX_GROUPS) return report_error(B200SPLAT_ERR_INVALID_ARG, "adam: bad group count");
+    if (n_groups > 0 && !groups) return report_error(B200SPLAT_ERR_INVALID_ARG, "adam: null groups");
+    AdamLaunch L;
+    memset(&L, 0, sizeof(L));
+    unsigned blocks = 0;
+    int ng = 0;
+    for (int i = 0; i < n_groups; ++i) {
+        const b200splat_adam_group& g = groups[i];
+        if (g.n < 0 || g.step < 1) return report_error(B200SPLAT_ERR_INVALID_ARG, "adam: bad n or step");
+        if (!g.grad || g.n == 0) continue;
+        if (!g.param || !g.exp_avg || !g.exp_avg_sq) return report_error(B200SPLAT_ERR_INVALID_ARG, "adam: null state");
+        long long nb = (g.n + ADAM_PER_BLOCK - 1) / ADAM_PER_BLOCK;
+        if (nb + blocks > 0x7FFFFFFFll) return report_error(B200SPLAT_ERR_INVALID_ARG, "adam: too many elements");
+        L.p[ng] = g.param; L.g[ng] = g.grad; L.m[ng] = g.exp_avg; L.v[ng] = g.exp_avg_sq; L.n[ng] = g.n;
+        double bc1 = 1.0 - pow(beta1, (double)g.step), bc2 = 1.0 - pow(beta2, (double)g.step);
+        L.step_size[ng] = (float)(g.lr / bc1);
+        L.bc2_sqrt[ng] = (float)sqrt(bc2);
+        L.vec[ng] = aligned16p(g.param) && aligned16p(g.grad) && aligned16p(g.exp_avg) && aligned16p(g.exp_avg_sq);
+        L.block_start[ng] = blocks;
+        blocks += (unsigned)nb;
+        ++ng;
+    }
+    if (ng == 0) return B200SPLAT_OK;
+    for (int i = ng; i <= B200SPLAT_ADAM_MAX_GROUPS; ++i) L.block_start[i] = blocks;
+    L.ng = ng;
+    L.beta2 = (float)beta2;
+    L.w1 = (float)(1.0 - beta1);
+    L.w2 = (float)(1.0 - beta2);
+    L.eps = (float)eps;
+    adam_kernel<<<blocks, ADAM_THREADS, 0, (cudaStream_t)stream_>>>(L);
+    CUN(cudaGetLastError(), "adam");
+    return B200SPLAT_OK;
+}
+
+int b200splat_dist2_knn3(int32_t P, const float* xyz, float* out, void* stream_) {
+    if (P < 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "knn: bad P");
+    if (P == 0) return B200SPLAT_OK;
+    if (!xyz || !out) return report_error(B200SPLAT_ERR_INVALID_ARG, "knn: null argument");
+    cudaStream_t s = (cudaStream_t)stream_;
+    const int n_boxes = (P + KBOX - 1) / KBOX, n_supers = (n_boxes + KSUPER - 1) / KSUPER;
+    size_t sort_bytes = 0;
+    CUN(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const unsigned*)nullptr, (unsigned*)nullptr,
+                                        (const unsigned*)nullptr, (unsigned*)nullptr, P, 0, 30, s), "knn sort size");
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+    size_t o_b6 = take(6 * sizeof(int)), o_codes = take(sizeof(unsigned) * P), o_codes2 = take(sizeof(unsigned) * P),
+           o_ids = take(sizeof(unsigned) * P), o_ids2 = take(sizeof(unsigned) * P), o_pts = take(sizeof(float4) * (size_t)P),
+           o_boxes = take(sizeof(Box) * (size_t)n_boxes), o_supers = take(sizeof(Box) * (size_t)n_supers),
+           o_sort = take(sort_bytes);
+    char* base = nullptr;
+    CUN(cudaMallocAsync((void**)&base, off, s), "knn scratch");
+    int* b6 = (int*)(base + o_b6);
+    unsigned *codes = (unsigned*)(base + o_codes), *codes2 = (unsigned*)(base + o_codes2), *ids = (unsigned*)(base + o_ids),
+             *ids2 = (unsigned*)(base + o_ids2);
+    float4* pts = (float4*)(base + o_pts);
+    Box *boxes = (Box*)(base + o_boxes), *supers = (Box*)(base + o_supers);
+    cudaError_t e = cudaSuccess;
+    do {
+        knn_bounds_init_kernel<<<1, 32, 0, s>>>(b6);
+        int nb = (P + 255) / 256;
+        knn_bounds_kernel<<<nb < 1184 ? nb : 1184, 256, 0, s>>>(P, xyz, b6);
+        knn_morton_kernel<<<nb, 256, 0, s>>>(P, xyz, b6, codes, ids);
+        if ((e = cudaGetLastError()) != cudaSuccess) break;
+        if ((e = cub::DeviceRadixSort::SortPairs(base + o_sort, sort_bytes, codes, codes2, ids, ids2, P, 0, 30, s)) != cudaSuccess) break;
+        knn_gather_boxes_kernel<<<n_boxes, KBOX, 0, s>>>(P, xyz, ids2, pts, boxes);
+        knn_super_boxes_kernel<<<n_supers, KSUPER, 0, s>>>(n_boxes, boxes, supers);
+        knn_search_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, pts, ids2, n_boxes, boxes, n_supers, supers, out);
+        e = cudaGetLastError();
+    } while (0);
+    cudaError_t e2 = cudaFreeAsync(base, s);
+    CUN(e, "knn kernels");
+    CUN(e2, "knn scratch free");
+    return B200SPLAT_OK;
+}
+
+}  // extern "C"

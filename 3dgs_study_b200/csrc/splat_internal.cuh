@@ -46,6 +46,9 @@ constexpr float THR_MARGIN = 1.0e-3f;
 
 inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 
+// sets the thread-local string b200splat_last_error() returns; returns `code` (api.cu)
+int report_error(int code, const char* msg);
+
 struct GeomView {
     float* depths; float4* rec; uint2* rect; uint32_t* iota; uint32_t* depth_sorted; uint32_t* order;
     uint32_t* offsets; void* scan_tmp; void* dsort_tmp;

@@ -1,0 +1,85 @@
+"""Adam over the Gaussian parameter groups in ONE kernel launch (b200splat_adam_step).
+
+`FusedAdam` subclasses torch.optim.Adam so that everything the reference does to its optimizer keeps working
+unchanged -- construction with named param groups (scene/gaussian_model.py:185-203), per-iteration
+`param_group['lr'] = ...` (:210-216), the state surgery of densification (`optimizer.state[...]['exp_avg']`,
+deleting / re-inserting state entries: replace_tensor_to_optimizer, _prune_optimizer, cat_tensors_to_optimizer),
+state_dict()/load_state_dict() -- and only `step()` is replaced.  Same state layout as torch (state[p] =
+{'step': tensor, 'exp_avg', 'exp_avg_sq'}), same formulas; CUDA fp32 parameters only, no fallback."""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def expon_lr(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):
+    """The position learning-rate schedule (get_expon_lr_func, /root/reference/utils/general_utils.py:30-69):
+    log-linear interpolation from lr_init to lr_final over max_steps, optional sine-eased warm-up."""
+    def helper(step):
+        if step < 0 or (lr_init == 0.0 and lr_final == 0.0):
+            return 0.0
+        if lr_delay_steps > 0:
+            delay_rate = lr_delay_mult + (1 - lr_delay_mult) * np.sin(0.5 * np.pi * np.clip(step / lr_delay_steps, 0, 1))
+        else:
+            delay_rate = 1.0
+        t = np.clip(step / max_steps, 0, 1)
+        return delay_rate * np.exp(np.log(lr_init) * (1 - t) + np.log(lr_final) * t)
+    return helper
+
+
+class FusedAdam(torch.optim.Adam):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        super().__init__(params, lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        todo = []          # (beta1, beta2, eps) -> list of AdamGroup, launched per distinct hyper-parameter set
+        for group in self.param_groups:
+            if group.get("weight_decay", 0) != 0 or group.get("amsgrad", False) or group.get("maximize", False):
+                raise RuntimeError("FusedAdam implements plain Adam only (the reference's settings)")
+            key = (float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]))
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                if not p.is_cuda:
+                    raise RuntimeError("FusedAdam needs CUDA parameters (there is no CPU path)")
+                if p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError("FusedAdam needs contiguous fp32 parameters")
+                if p.grad.is_sparse:
+                    raise RuntimeError("FusedAdam does not support sparse gradients")
+                g = p.grad if (p.grad.dtype == torch.float32 and p.grad.is_contiguous()) else p.grad.float().contiguous()
+                st = self.state[p]
+                if len(st) == 0:
+                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
+                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                if not torch.is_tensor(st["step"]):
+                    st["step"] = torch.tensor(float(st["step"]), dtype=torch.float32)
+                st["step"] += 1
+                for k in ("exp_avg", "exp_avg_sq"):
+                    if not (st[k].is_contiguous() and st[k].dtype == torch.float32 and st[k].device == p.device):
+                        st[k] = st[k].to(device=p.device, dtype=torch.float32).contiguous()
+                step = int(st["step"].item()) if st["step"].device.type == "cpu" else int(st["step"].cpu().item())
+                todo.append((key, p.device, _lib.AdamGroup(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(),
+                                                           st["exp_avg_sq"].data_ptr(), p.numel(), float(group["lr"]), step, 0), g))
+        L = _lib.lib()
+        i = 0
+        while i < len(todo):
+            key, dev = todo[i][0], todo[i][1]
+            batch = []
+            while i < len(todo) and len(batch) < _lib.ADAM_MAX_GROUPS and todo[i][0] == key and todo[i][1] == dev:
+                batch.append(todo[i][2])
+                i += 1
+            arr = (_lib.AdamGroup * len(batch))(*batch)
+            with torch.cuda.device(dev):
+                _lib.check(L.b200splat_adam_step(len(batch), ctypes.addressof(arr), key[0], key[1], key[2],
+                                                 _lib.stream_ptr(dev)), "adam step")
+        return loss
