@@ -136,9 +136,9 @@ l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
     }
 }
 
-// one block per plane: fixed-order sum of that plane's block partials in double -> per-plane means
+// one block per plane: fixed-order sum of that plane's block partials in double -> per-plane sums
 __global__ void __launch_bounds__(256)
-l1_ssim_finalize_kernel(int blocks_per_plane, double inv_count, const float2* __restrict__ partials, float* __restrict__ out) {
+l1_ssim_finalize_kernel(int blocks_per_plane, const float2* __restrict__ partials, float* __restrict__ out) {
     __shared__ double sl[256], ssm[256];
     const float2* p = partials + (size_t)blockIdx.x * blocks_per_plane;
     double a = 0.0, b = 0.0;
@@ -150,8 +150,8 @@ l1_ssim_finalize_kernel(int blocks_per_plane, double inv_count, const float2* __
         __syncthreads();
     }
     if (threadIdx.x == 0) {
-        out[2 * blockIdx.x] = (float)(sl[0] * inv_count);
-        out[2 * blockIdx.x + 1] = (float)(ssm[0] * inv_count);
+        out[2 * blockIdx.x] = (float)sl[0];
+        out[2 * blockIdx.x + 1] = (float)ssm[0];
     }
 }
 
@@ -488,8 +488,7 @@ int b200splat_l1_ssim_forward(int32_t planes, int32_t height, int32_t width, con
     l1_ssim_fwd_kernel<<<grid, LTHREADS, 0, s>>>(height, width, img, gt, tw, maps, (size_t)planes * height * width,
                                                  reinterpret_cast<float2*>(partials));
     CUN(cudaGetLastError(), "l1_ssim forward");
-    l1_ssim_finalize_kernel<<<planes, 256, 0, s>>>((int)(grid.x * grid.y), 1.0 / ((double)height * (double)width),
-                                                   reinterpret_cast<const float2*>(partials), out);
+    l1_ssim_finalize_kernel<<<planes, 256, 0, s>>>((int)(grid.x * grid.y), reinterpret_cast<const float2*>(partials), out);
     CUN(cudaGetLastError(), "l1_ssim finalize");
     return B200SPLAT_OK;
 }

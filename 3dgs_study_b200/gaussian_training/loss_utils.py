@@ -50,7 +50,7 @@ def _prep(img1: torch.Tensor, img2: torch.Tensor):
 
 
 class _L1SSIM(torch.autograd.Function):
-    """(img, gt) -> per-plane means [planes, 2] = (mean |img-gt|, mean SSIM map).  Differentiable in img."""
+    """(img, gt) -> per-plane sums [planes, 2] = (sum |img-gt|, sum of the SSIM map).  Differentiable in img."""
 
     @staticmethod
     def forward(ctx, img, gt, window_size):
@@ -81,8 +81,7 @@ class _L1SSIM(torch.autograd.Function):
         H, W = a.shape[-2:]
         planes = a.numel() // (H * W)
         dev = a.device
-        # out[p] are means over H*W pixels: fold 1/(H*W) and the upstream gradients into the per-plane scales
-        scale = (g_out.to(torch.float32) * (1.0 / (H * W))).contiguous()
+        scale = g_out.to(torch.float32).contiguous()      # upstream gradients of the per-plane sums
         da = torch.empty_like(a)
         taps = window_taps(ctx.window_size)
         with torch.cuda.device(dev):
@@ -95,13 +94,14 @@ class _L1SSIM(torch.autograd.Function):
 def l1_and_ssim(img: torch.Tensor, gt: torch.Tensor, window_size: int = 11, size_average: bool = True):
     """(l1_loss(img, gt), ssim(img, gt, window_size, size_average)) from one pass over the images."""
     out = _L1SSIM.apply(img, gt, int(window_size))
-    l1 = out[:, 0].mean()                     # equal-sized planes: the mean of plane means is the global mean
+    n = img.numel()
+    l1 = out[:, 0].sum() / n                  # .mean() of the reference: one division by the element count
     if size_average:
-        return l1, out[:, 1].mean()
+        return l1, out[:, 1].sum() / n
     if img.dim() != 4:
         # the reference's ssim_map.mean(1).mean(1).mean(1) needs a batch dimension too (loss_utils.py:108)
         raise RuntimeError("size_average=False needs a [B,C,H,W] input")
-    return l1, out[:, 1].view(img.shape[0], img.shape[1]).mean(1)
+    return l1, out[:, 1].view(img.shape[0], img.shape[1]).sum(1) / (n // img.shape[0])
 
 
 def l1_loss(network_output: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:

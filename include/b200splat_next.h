@@ -39,14 +39,14 @@ extern "C" {
  * window is passed centred and zero padded.  The reference's 2-D window is the outer product of these taps
  * (:54) and its convolutions are zero padded (:83-93): the kernels apply the taps separably, x then y.
  *
- * forward:  out[2p] = mean |img-gt| over plane p, out[2p+1] = mean of the SSIM map over plane p (device,
- *           2*planes floats; equal-sized planes, so the reference's global / per-batch means are means of
- *           these).  maps (device, 3*planes*H*W floats, or NULL when no gradient is wanted) receives
+ * forward:  out[2p] = sum of |img-gt| over plane p, out[2p+1] = sum of the SSIM map over plane p (device,
+ *           2*planes floats, accumulated in double in a fixed order; the reference's global / per-batch means
+ *           are sums of these divided by the element count).  maps (device, 3*planes*H*W floats, or NULL when no gradient is wanted) receives
  *           d m/d mu1, d m/d conv(img^2), d m/d conv(img*gt) of the SSIM map m.  partials: device scratch of
  *           b200splat_l1_ssim_partials(planes, H, W) float pairs.
  * backward: dL_dimg[p] = scale[2p] * sign(img-gt) + scale[2p+1] * d(sum of the SSIM map of plane p)/d img,
- *           scale = device array of 2*planes floats in which the caller has folded the upstream gradients and
- *           the 1/count of the means (so no host synchronisation is needed to read them).
+ *           scale = device array of 2*planes floats = the upstream gradients of out (1/count for a plain mean);
+ *           a device array so that no host synchronisation is needed to read them.
  */
 B200SPLAT_API size_t b200splat_l1_ssim_partials(int32_t planes, int32_t height, int32_t width);
 B200SPLAT_API int b200splat_l1_ssim_forward(int32_t planes, int32_t height, int32_t width, const float* img,
