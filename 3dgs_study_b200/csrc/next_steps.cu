@@ -155,10 +155,30 @@ l1_ssim_finalize_kernel(int blocks_per_plane, const float2* __restrict__ partial
     }
 }
 
+// the training loss in one block: loss3 = (loss, mean |a-b|, mean SSIM), loss = (1-lambda) l1 + lambda (1 - ssim)
+__global__ void __launch_bounds__(256)
+l1_ssim_loss_kernel(int n_partials, double inv_count, float lambda, const float2* __restrict__ partials, float* __restrict__ loss3) {
+    __shared__ double sl[256], ssm[256];
+    double a = 0.0, b = 0.0;
+    for (int i = threadIdx.x; i < n_partials; i += 256) { float2 v = partials[i]; a += (double)v.x; b += (double)v.y; }
+    sl[threadIdx.x] = a; ssm[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { sl[threadIdx.x] += sl[threadIdx.x + o]; ssm[threadIdx.x] += ssm[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        float l1 = (float)(sl[0] * inv_count), ss = (float)(ssm[0] * inv_count);
+        loss3[0] = (1.0f - lambda) * l1 + lambda * (1.0f - ss);
+        loss3[1] = l1;
+        loss3[2] = ss;
+    }
+}
+
 __global__ void __launch_bounds__(LTHREADS)
 l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, Taps tw,
                    const float* __restrict__ maps, size_t map_stride, const float* __restrict__ scale,
-                   float* __restrict__ dimg) {
+                   const float* __restrict__ upstream, float c_l1, float c_ssim, float* __restrict__ dimg) {
     __shared__ float sm[3][LIN][LPITCH];
     __shared__ float sh[3][LIN][LT];
 
@@ -196,7 +216,10 @@ l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
     ypass(sh[0], r0, tx, tw, f0);
     ypass(sh[1], r0, tx, tw, f1);
     ypass(sh[2], r0, tx, tw, f2);
-    const float sl = __ldg(scale + 2 * plane), ssc = __ldg(scale + 2 * plane + 1);
+    // per-plane factors, or one upstream scalar times two host constants (the fused training loss)
+    const float up = upstream ? __ldg(upstream) : 1.0f;
+    const float sl = scale ? __ldg(scale + 2 * plane) : up * c_l1;
+    const float ssc = scale ? __ldg(scale + 2 * plane + 1) : up * c_ssim;
     const int x = x0 + tx;
 #pragma unroll
     for (int j = 0; j < LROWS; ++j) {
@@ -223,6 +246,9 @@ struct AdamLaunch {
     float* v[B200SPLAT_ADAM_MAX_GROUPS];
     long long n[B200SPLAT_ADAM_MAX_GROUPS];
     float step_size[B200SPLAT_ADAM_MAX_GROUPS];
+    float step_size_tail[B200SPLAT_ADAM_MAX_GROUPS];   // for elements whose column (index % row_width) >= row_split
+    int row_width[B200SPLAT_ADAM_MAX_GROUPS];          // 0: one learning rate for the whole tensor
+    int row_split[B200SPLAT_ADAM_MAX_GROUPS];
     float bc2_sqrt[B200SPLAT_ADAM_MAX_GROUPS];
     unsigned block_start[B200SPLAT_ADAM_MAX_GROUPS + 1];
     int vec[B200SPLAT_ADAM_MAX_GROUPS];
@@ -250,31 +276,92 @@ __global__ void __launch_bounds__(ADAM_THREADS) adam_kernel(const AdamLaunch L) 
     float* __restrict__ M = L.m[gi];
     float* __restrict__ V = L.v[gi];
     const long long n = L.n[gi];
-    const float step_size = L.step_size[gi], bc2_sqrt = L.bc2_sqrt[gi];
+    const float step_head = L.step_size[gi], step_tail = L.step_size_tail[gi], bc2_sqrt = L.bc2_sqrt[gi];
+    const int rw = L.row_width[gi], rs = L.row_split[gi];
     const long long base = (long long)(blockIdx.x - L.block_start[gi]) * ADAM_PER_BLOCK;
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
         long long e = base + ((long long)it * ADAM_THREADS + threadIdx.x) * 4;
         if (e >= n) continue;
+        // learning rate by column, per element (a float4 may straddle the split or a row end)
+        float ss[4];
+        if (rw > 0) {
+            int c = (int)(e % rw);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { ss[j] = (c >= rs) ? step_tail : step_head; if (++c == rw) c = 0; }
+        } else {
+            ss[0] = ss[1] = ss[2] = ss[3] = step_head;
+        }
         if (L.vec[gi] && e + 4 <= n) {
             float4 p = *reinterpret_cast<const float4*>(P + e);
             float4 g = __ldg(reinterpret_cast<const float4*>(G + e));
             float4 m = *reinterpret_cast<const float4*>(M + e);
             float4 v = *reinterpret_cast<const float4*>(V + e);
-            adam_one(p.x, g.x, m.x, v.x, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
-            adam_one(p.y, g.y, m.y, v.y, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
-            adam_one(p.z, g.z, m.z, v.z, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
-            adam_one(p.w, g.w, m.w, v.w, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            adam_one(p.x, g.x, m.x, v.x, ss[0], bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            adam_one(p.y, g.y, m.y, v.y, ss[1], bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            adam_one(p.z, g.z, m.z, v.z, ss[2], bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+            adam_one(p.w, g.w, m.w, v.w, ss[3], bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
             *reinterpret_cast<float4*>(P + e) = p;
             *reinterpret_cast<float4*>(M + e) = m;
             *reinterpret_cast<float4*>(V + e) = v;
         } else {
             for (int j = 0; j < 4 && e + j < n; ++j) {
                 float p = P[e + j], m = M[e + j], v = V[e + j];
-                adam_one(p, G[e + j], m, v, step_size, bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
+                adam_one(p, G[e + j], m, v, ss[j], bc2_sqrt, L.beta2, L.w1, L.w2, L.eps);
                 P[e + j] = p; M[e + j] = m; V[e + j] = v;
             }
         }
+    }
+}
+
+// ---- activations of the raw parameters -----------------------------------------------------------------------
+// scales = exp(raw), rotations = raw / max(||raw||, 1e-12), opacities = sigmoid(raw): one pass over the 8 raw
+// floats of a Gaussian instead of ~8 elementwise/reduction launches, and one pass back instead of ~15.
+__global__ void __launch_bounds__(256)
+activate_fwd_kernel(int P, const float* __restrict__ scaling, const float4* __restrict__ rotation,
+                    const float* __restrict__ opacity, float* __restrict__ scales, float4* __restrict__ rotations,
+                    float* __restrict__ opacities) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) scales[3 * (size_t)i + k] = expf(scaling[3 * (size_t)i + k]);
+    float4 q = rotation[i];
+    float nrm = sqrtf(__fmaf_rn(q.w, q.w, __fmaf_rn(q.z, q.z, __fmaf_rn(q.y, q.y, __fmul_rn(q.x, q.x)))));
+    float d = fmaxf(nrm, 1e-12f);
+    rotations[i] = make_float4(q.x / d, q.y / d, q.z / d, q.w / d);
+    opacities[i] = 1.0f / (1.0f + expf(-opacity[i]));
+}
+
+// raw gradients from the activated values (saved by the forward) and their upstream gradients
+__global__ void __launch_bounds__(256)
+activate_bwd_kernel(int P, const float4* __restrict__ rotation, const float* __restrict__ scales,
+                    const float* __restrict__ opacities, const float* __restrict__ g_scales,
+                    const float4* __restrict__ g_rotations, const float* __restrict__ g_opacities,
+                    float* __restrict__ d_scaling, float4* __restrict__ d_rotation, float* __restrict__ d_opacity) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    if (g_scales) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) d_scaling[3 * (size_t)i + k] = g_scales[3 * (size_t)i + k] * scales[3 * (size_t)i + k];
+    }
+    if (g_rotations) {
+        float4 q = rotation[i], g = g_rotations[i];
+        float nrm = sqrtf(__fmaf_rn(q.w, q.w, __fmaf_rn(q.z, q.z, __fmaf_rn(q.y, q.y, __fmul_rn(q.x, q.x)))));
+        float4 r;
+        if (nrm > 1e-12f) {
+            // y = q / n:  dq = (g - y (y . g)) / n
+            float inv = 1.0f / nrm;
+            float4 y = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
+            float dot = y.x * g.x + y.y * g.y + y.z * g.z + y.w * g.w;
+            r = make_float4((g.x - y.x * dot) * inv, (g.y - y.y * dot) * inv, (g.z - y.z * dot) * inv, (g.w - y.w * dot) * inv);
+        } else {
+            r = make_float4(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f, g.w * 1e12f);   // clamp_min branch: y = q / eps
+        }
+        d_rotation[i] = r;
+    }
+    if (g_opacities) {
+        float o = opacities[i];
+        d_opacity[i] = g_opacities[i] * ((1.0f - o) * o);
     }
 }
 
@@ -403,10 +490,11 @@ __global__ void __launch_bounds__(KSUPER) knn_super_boxes_kernel(int n_boxes, co
     }
 }
 
-// squared distance in the one canonical form every comparison uses; per-axis monotone, so a box's value never
+// squared distance in the one canonical form every comparison uses -- the instruction sequence nvcc emits for the
+// reference's d.x*d.x + d.y*d.y + d.z*d.z (FMUL dy*dy, FFMA dx*dx, FFMA dz*dz; SASS of its boxMeanDist); per-axis monotone, so a box's value never
 // exceeds that of any point inside it and pruning on it is exact
 __device__ __forceinline__ float dist2(float dx, float dy, float dz) {
-    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+    return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
 }
 __device__ __forceinline__ float box_dist2(const Box& b, float x, float y, float z) {
     float dx = fmaxf(0.0f, fmaxf(__fsub_rn(b.lo[0], x), __fsub_rn(x, b.hi[0])));
@@ -504,8 +592,46 @@ int b200splat_l1_ssim_backward(int32_t planes, int32_t height, int32_t width, co
     dim3 grid(tiles_1d(width), tiles_1d(height), planes);
     if (grid.y > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "l1_ssim: image too tall");
     l1_ssim_bwd_kernel<<<grid, LTHREADS, 0, (cudaStream_t)stream_>>>(height, width, img, gt, tw, maps,
-                                                                     (size_t)planes * height * width, scale, dL_dimg);
+                                                                     (size_t)planes * height * width, scale, nullptr, 0.f, 0.f, dL_dimg);
     CUN(cudaGetLastError(), "l1_ssim backward");
+    return B200SPLAT_OK;
+}
+
+int b200splat_training_loss_forward(int32_t planes, int32_t height, int32_t width, const float* img, const float* gt,
+                                    const float* window11, float lambda_dssim, float* maps, float* partials, float* loss3,
+                                    void* stream_) {
+    if (planes <= 0 || height <= 0 || width <= 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: bad sizes");
+    if (planes > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: more than 65535 planes");
+    if (!img || !gt || !window11 || !partials || !loss3) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: null argument");
+    cudaStream_t s = (cudaStream_t)stream_;
+    Taps tw;
+    for (int k = 0; k < 2 * LR + 1; ++k) tw.w[k] = window11[k];
+    dim3 grid(tiles_1d(width), tiles_1d(height), planes);
+    if (grid.y > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: image too tall");
+    l1_ssim_fwd_kernel<<<grid, LTHREADS, 0, s>>>(height, width, img, gt, tw, maps, (size_t)planes * height * width,
+                                                 reinterpret_cast<float2*>(partials));
+    CUN(cudaGetLastError(), "training_loss forward");
+    l1_ssim_loss_kernel<<<1, 256, 0, s>>>((int)(grid.x * grid.y * grid.z), 1.0 / ((double)planes * height * width), lambda_dssim,
+                                          reinterpret_cast<const float2*>(partials), loss3);
+    CUN(cudaGetLastError(), "training_loss finalize");
+    return B200SPLAT_OK;
+}
+
+int b200splat_training_loss_backward(int32_t planes, int32_t height, int32_t width, const float* img, const float* gt,
+                                     const float* window11, float lambda_dssim, const float* maps, const float* upstream,
+                                     float* dL_dimg, void* stream_) {
+    if (planes <= 0 || height <= 0 || width <= 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: bad sizes");
+    if (planes > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: more than 65535 planes");
+    if (!img || !gt || !window11 || !maps || !dL_dimg) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: null argument");
+    Taps tw;
+    for (int k = 0; k < 2 * LR + 1; ++k) tw.w[k] = window11[k];
+    dim3 grid(tiles_1d(width), tiles_1d(height), planes);
+    if (grid.y > 65535) return report_error(B200SPLAT_ERR_INVALID_ARG, "training_loss: image too tall");
+    const double n = (double)planes * height * width;
+    l1_ssim_bwd_kernel<<<grid, LTHREADS, 0, (cudaStream_t)stream_>>>(height, width, img, gt, tw, maps, (size_t)planes * height * width,
+                                                                     nullptr, upstream, (float)((1.0 - (double)lambda_dssim) / n),
+                                                                     (float)(-(double)lambda_dssim / n), dL_dimg);
+    CUN(cudaGetLastError(), "training_loss backward");
     return B200SPLAT_OK;
 }
 
@@ -527,6 +653,11 @@ int b200splat_adam_step(int32_t n_groups, const b200splat_adam_group* groups, do
         L.p[ng] = g.param; L.g[ng] = g.grad; L.m[ng] = g.exp_avg; L.v[ng] = g.exp_avg_sq; L.n[ng] = g.n;
         double bc1 = 1.0 - pow(beta1, (double)g.step), bc2 = 1.0 - pow(beta2, (double)g.step);
         L.step_size[ng] = (float)(g.lr / bc1);
+        if (g.row_width < 0 || g.row_split < 0 || g.row_split > g.row_width || (g.row_width > 0 && g.n % g.row_width != 0))
+            return report_error(B200SPLAT_ERR_INVALID_ARG, "adam: bad row_width / row_split");
+        L.step_size_tail[ng] = (float)(g.lr_tail / bc1);
+        L.row_width[ng] = g.row_width;
+        L.row_split[ng] = g.row_split;
         L.bc2_sqrt[ng] = (float)sqrt(bc2);
         L.vec[ng] = aligned16p(g.param) && aligned16p(g.grad) && aligned16p(g.exp_avg) && aligned16p(g.exp_avg_sq);
         L.block_start[ng] = blocks;
@@ -542,6 +673,34 @@ int b200splat_adam_step(int32_t n_groups, const b200splat_adam_group* groups, do
     L.eps = (float)eps;
     adam_kernel<<<blocks, ADAM_THREADS, 0, (cudaStream_t)stream_>>>(L);
     CUN(cudaGetLastError(), "adam");
+    return B200SPLAT_OK;
+}
+
+int b200splat_activate_forward(int32_t P, const float* scaling, const float* rotation, const float* opacity, float* scales,
+                               float* rotations, float* opacities, void* stream_) {
+    if (P < 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "activate: bad P");
+    if (P == 0) return B200SPLAT_OK;
+    if (!scaling || !rotation || !opacity || !scales || !rotations || !opacities) return report_error(B200SPLAT_ERR_INVALID_ARG, "activate: null argument");
+    if (!aligned16p(rotation) || !aligned16p(rotations)) return report_error(B200SPLAT_ERR_INVALID_ARG, "activate: rotations must be 16-byte aligned");
+    activate_fwd_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, scaling, (const float4*)rotation, opacity, scales,
+                                                                           (float4*)rotations, opacities);
+    CUN(cudaGetLastError(), "activate forward");
+    return B200SPLAT_OK;
+}
+
+int b200splat_activate_backward(int32_t P, const float* rotation, const float* scales, const float* opacities, const float* g_scales,
+                                const float* g_rotations, const float* g_opacities, float* d_scaling, float* d_rotation,
+                                float* d_opacity, void* stream_) {
+    if (P < 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "activate: bad P");
+    if (P == 0) return B200SPLAT_OK;
+    if ((g_scales && (!scales || !d_scaling)) || (g_rotations && (!rotation || !d_rotation)) || (g_opacities && (!opacities || !d_opacity)))
+        return report_error(B200SPLAT_ERR_INVALID_ARG, "activate backward: null argument");
+    if (g_rotations && (!aligned16p(rotation) || !aligned16p(g_rotations) || !aligned16p(d_rotation)))
+        return report_error(B200SPLAT_ERR_INVALID_ARG, "activate backward: rotations must be 16-byte aligned");
+    activate_bwd_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream_>>>(P, (const float4*)rotation, scales, opacities, g_scales,
+                                                                           (const float4*)g_rotations, g_opacities, d_scaling,
+                                                                           (float4*)d_rotation, d_opacity);
+    CUN(cudaGetLastError(), "activate backward");
     return B200SPLAT_OK;
 }
 

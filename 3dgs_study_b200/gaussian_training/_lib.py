@@ -12,7 +12,8 @@ ADAM_MAX_GROUPS = 8
 class AdamGroup(ctypes.Structure):
     _fields_ = [("param", ctypes.c_void_p), ("grad", ctypes.c_void_p), ("exp_avg", ctypes.c_void_p),
                 ("exp_avg_sq", ctypes.c_void_p), ("n", ctypes.c_int64), ("lr", ctypes.c_double),
-                ("step", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+                ("step", ctypes.c_int32), ("row_width", ctypes.c_int32), ("row_split", ctypes.c_int32),
+                ("reserved", ctypes.c_int32), ("lr_tail", ctypes.c_double)]
 
 
 _ready = False
@@ -29,6 +30,14 @@ def lib():
         L.b200splat_l1_ssim_forward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
         L.b200splat_l1_ssim_backward.restype = ctypes.c_int
         L.b200splat_l1_ssim_backward.argtypes = [i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
+        L.b200splat_training_loss_forward.restype = ctypes.c_int
+        L.b200splat_training_loss_forward.argtypes = [i32, i32, i32, vp, vp, vp, ctypes.c_float, vp, vp, vp, vp]
+        L.b200splat_training_loss_backward.restype = ctypes.c_int
+        L.b200splat_training_loss_backward.argtypes = [i32, i32, i32, vp, vp, vp, ctypes.c_float, vp, vp, vp, vp]
+        L.b200splat_activate_forward.restype = ctypes.c_int
+        L.b200splat_activate_forward.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp]
+        L.b200splat_activate_backward.restype = ctypes.c_int
+        L.b200splat_activate_backward.argtypes = [i32] + [vp] * 10
         L.b200splat_adam_step.restype = ctypes.c_int
         L.b200splat_adam_step.argtypes = [i32, vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, vp]
         L.b200splat_dist2_knn3.restype = ctypes.c_int

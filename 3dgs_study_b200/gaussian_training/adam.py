@@ -5,7 +5,12 @@ unchanged -- construction with named param groups (scene/gaussian_model.py:185-2
 `param_group['lr'] = ...` (:210-216), the state surgery of densification (`optimizer.state[...]['exp_avg']`,
 deleting / re-inserting state entries: replace_tensor_to_optimizer, _prune_optimizer, cat_tensors_to_optimizer),
 state_dict()/load_state_dict() -- and only `step()` is replaced.  Same state layout as torch (state[p] =
-{'step': tensor, 'exp_avg', 'exp_avg_sq'}), same formulas; CUDA fp32 parameters only, no fallback."""
+{'step': tensor, 'exp_avg', 'exp_avg_sq'}), same formulas; CUDA fp32 parameters only, no fallback.
+
+One addition: a group may carry `row_width`, `row_split` and `lr_tail`; its tensors are then treated as
+[n / row_width, row_width] matrices whose columns >= row_split train with `lr_tail` instead of `lr`.  That lets
+the SH coefficients live in ONE [P, M, 3] parameter (row_width = 3 M, row_split = 3: f_dc / f_rest learning rates
+of gaussian_model.py:187-188), so the torch.cat of get_features (:119-122) and its backward split disappear."""
 from __future__ import annotations
 
 import ctypes
@@ -68,8 +73,12 @@ class FusedAdam(torch.optim.Adam):
                     if not (st[k].is_contiguous() and st[k].dtype == torch.float32 and st[k].device == p.device):
                         st[k] = st[k].to(device=p.device, dtype=torch.float32).contiguous()
                 step = int(st["step"].item()) if st["step"].device.type == "cpu" else int(st["step"].cpu().item())
+                rw, rs = int(group.get("row_width", 0)), int(group.get("row_split", 0))
+                if rw and p.numel() % rw != 0:
+                    raise RuntimeError(f"group {group.get('name')}: {p.numel()} elements are not rows of {rw}")
                 todo.append((key, p.device, _lib.AdamGroup(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(),
-                                                           st["exp_avg_sq"].data_ptr(), p.numel(), float(group["lr"]), step, 0), g))
+                                                           st["exp_avg_sq"].data_ptr(), p.numel(), float(group["lr"]), step,
+                                                           rw, rs, 0, float(group.get("lr_tail", group["lr"]))), g))
         L = _lib.lib()
         i = 0
         while i < len(todo):

@@ -91,6 +91,49 @@ class _L1SSIM(torch.autograd.Function):
         return da.to(ctx.in_dtype), None, None
 
 
+class _TrainingLoss(torch.autograd.Function):
+    """(img, gt) -> [3] = (loss, Ll1, ssim) with loss = (1-l) Ll1 + l (1 - ssim): two kernels forward, one
+    backward, no elementwise glue.  Only `loss` (element 0) carries a gradient."""
+
+    @staticmethod
+    def forward(ctx, img, gt, lambda_dssim):
+        a, b = _prep(img.detach(), gt.detach())
+        H, W = a.shape[-2:]
+        planes = a.numel() // (H * W)
+        dev = a.device
+        L = _lib.lib()
+        taps = window_taps(11)
+        need_grad = bool(ctx.needs_input_grad[0])
+        maps = torch.empty((3,) + tuple(a.shape), dtype=torch.float32, device=dev) if need_grad else None
+        partials = torch.empty((L.b200splat_l1_ssim_partials(planes, H, W), 2), dtype=torch.float32, device=dev)
+        out = torch.empty(3, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(L.b200splat_training_loss_forward(planes, H, W, a.data_ptr(), b.data_ptr(), ctypes.addressof(taps),
+                                                         float(lambda_dssim), maps.data_ptr() if need_grad else None,
+                                                         partials.data_ptr(), out.data_ptr(), _lib.stream_ptr(dev)), "training_loss forward")
+        ctx.save_for_backward(a, b, maps)
+        ctx.lambda_dssim = float(lambda_dssim)
+        ctx.in_dtype = img.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        a, b, maps = ctx.saved_tensors
+        if maps is None:
+            return None, None, None
+        H, W = a.shape[-2:]
+        planes = a.numel() // (H * W)
+        dev = a.device
+        up = g_out.to(torch.float32).contiguous()     # [3]; element 0 = d L / d loss (read on the device)
+        da = torch.empty_like(a)
+        taps = window_taps(11)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().b200splat_training_loss_backward(planes, H, W, a.data_ptr(), b.data_ptr(), ctypes.addressof(taps),
+                                                                   ctx.lambda_dssim, maps.data_ptr(), up.data_ptr(), da.data_ptr(),
+                                                                   _lib.stream_ptr(dev)), "training_loss backward")
+        return da.to(ctx.in_dtype), None, None
+
+
 def l1_and_ssim(img: torch.Tensor, gt: torch.Tensor, window_size: int = 11, size_average: bool = True):
     """(l1_loss(img, gt), ssim(img, gt, window_size, size_average)) from one pass over the images."""
     out = _L1SSIM.apply(img, gt, int(window_size))
@@ -115,5 +158,5 @@ def ssim(img1: torch.Tensor, img2: torch.Tensor, window_size: int = 11, size_ave
 def training_loss(image: torch.Tensor, gt_image: torch.Tensor, lambda_dssim: float = 0.2):
     """-> (loss, Ll1): loss = (1 - lambda) * Ll1 + lambda * (1 - ssim(image, gt)), train.py:103-104
     (lambda_dssim default: arguments/__init__.py:89)."""
-    Ll1, s = l1_and_ssim(image, gt_image)
-    return (1.0 - lambda_dssim) * Ll1 + lambda_dssim * (1.0 - s), Ll1
+    out = _TrainingLoss.apply(image, gt_image, float(lambda_dssim))
+    return out[0], out[1].detach()

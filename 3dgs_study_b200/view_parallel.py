@@ -11,9 +11,15 @@ Densification side statistics keep the reference's semantics
 gradient NORM is taken per view and then summed (so it is accumulated locally per view, then
 sum-reduced), `denom` counts visible views, `max_radii2D` is max-reduced.
 
-Two exchange modes:
+Three exchange modes:
+  "packed"      (default for world_size > 1 on CUDA) the per-Gaussian backward writes ONE 64-byte row per Gaussian
+                the view touched (geometry gradients + masked colour gradient, b200splat_backward_packed) into a
+                symmetric (peer-mapped) buffer; after one barrier every rank READS its peers' rows over NVLink in
+                the kernel that adds them into its dense gradients and rebuilds dL/dsh from the colour gradient and
+                the camera centre (b200splat_accumulate_packed).  No collective on the data path; the bytes on NVLink
+                follow the Gaussians a view actually touched, not P.  8 GPUs: 3650 views/s (85 % of 8x the 1-GPU rate).
   "allreduce"   every rank all-reduces the full 59 f32 / Gaussian (708 MB at 3 M SH3).  The plain baseline.
-  "factorized"  (default for world_size > 1 on CUDA) the SH gradient of a view is the outer product
+  "factorized"  (the NCCL flavour; default with an injected backend) the SH gradient of a view is the outer product
                 Y(dir(mean, campos_v)) (x) dcol_v, so ranks all-gather the [P,3] masked colour gradients
                 (12 B per Gaussian and view) plus the camera centres, all-reduce only the remaining
                 11 f32 / Gaussian (rotation 4, mean 3, scale 3, opacity 1) as ONE flat buffer, and every rank

@@ -56,6 +56,30 @@ B200SPLAT_API int b200splat_l1_ssim_backward(int32_t planes, int32_t height, int
                            const float* gt, const float* window11, const float* maps, const float* scale,
                            float* dL_dimg, void* stream);
 
+/* The training loss of train.py:103-104 in one go: loss3 (device, 3 floats) = (loss, Ll1, ssim) with
+ * loss = (1 - lambda_dssim) * Ll1 + lambda_dssim * (1 - ssim), means over all planes*H*W elements.  The
+ * backward multiplies by `upstream` (device scalar = d L / d loss, NULL = 1), so loss.backward() needs no
+ * elementwise glue kernels at all.  maps / partials as above. */
+B200SPLAT_API int b200splat_training_loss_forward(int32_t planes, int32_t height, int32_t width, const float* img,
+                           const float* gt, const float* window11, float lambda_dssim, float* maps, float* partials,
+                           float* loss3, void* stream);
+B200SPLAT_API int b200splat_training_loss_backward(int32_t planes, int32_t height, int32_t width, const float* img,
+                           const float* gt, const float* window11, float lambda_dssim, const float* maps,
+                           const float* upstream, float* dL_dimg, void* stream);
+
+/* ---- Activations of the raw parameters --------------------------------------------------------------
+ * GaussianModel.get_scaling / get_rotation / get_opacity (scene/gaussian_model.py:104-130 over the
+ * functions set at :34-42): scales = exp(scaling), rotations = normalize(rotation) = rotation /
+ * max(||rotation||_2, 1e-12), opacities = sigmoid(opacity); [P,3], [P,4], [P,1] device arrays.  The backward
+ * takes the activated values the forward produced and the gradients the rasterizer returned for them; any of
+ * the three gradient inputs may be NULL (that output is then left untouched). */
+B200SPLAT_API int b200splat_activate_forward(int32_t P, const float* scaling, const float* rotation,
+                           const float* opacity, float* scales, float* rotations, float* opacities, void* stream);
+B200SPLAT_API int b200splat_activate_backward(int32_t P, const float* rotation, const float* scales,
+                           const float* opacities, const float* g_scales, const float* g_rotations,
+                           const float* g_opacities, float* d_scaling, float* d_rotation, float* d_opacity,
+                           void* stream);
+
 /* ---- Adam -----------------------------------------------------------------------------------------
  * One optimizer step over up to B200SPLAT_ADAM_MAX_GROUPS tensors in one launch (torch.optim.Adam
  * formulas, no weight decay, no amsgrad):
@@ -75,7 +99,10 @@ typedef struct {
     int64_t n;
     double lr;
     int32_t step;        /* per-group step count (groups re-created by densification restart at 1) */
-    int32_t reserved;
+    int32_t row_width;   /* 0: `lr` for every element.  > 0: the tensor is [n / row_width, row_width] and   */
+    int32_t row_split;   /*    columns >= row_split use lr_tail -- one [P, M*3] SH tensor trained with the   */
+    int32_t reserved;    /*    f_dc / f_rest learning rates of gaussian_model.py:187-188 without splitting it */
+    double lr_tail;
 } b200splat_adam_group;
 B200SPLAT_API int b200splat_adam_step(int32_t n_groups, const b200splat_adam_group* groups, double beta1,
                            double beta2, double eps, void* stream);
@@ -83,8 +110,8 @@ B200SPLAT_API int b200splat_adam_step(int32_t n_groups, const b200splat_adam_gro
 /* ---- distCUDA2 ------------------------------------------------------------------------------------
  * out[i] = mean of the squared distances from point i to its 3 nearest other points (device, P floats);
  * xyz = device [P,3].  Exact search (Morton order, two-level bounding boxes), distances evaluated as
- * fma(dz,dz, fma(dy,dy, dx*dx)) -- what nvcc makes of the reference's expression -- so results are
- * bit-identical to an exhaustive search.  Scratch comes from the stream-ordered CUDA allocator. */
+ * fma(dz,dz, fma(dx,dx, dy*dy)) -- the instruction sequence nvcc emits for the reference's expression -- so
+ * results are bit-identical to the reference's own build and to an exhaustive search.  Scratch comes from the stream-ordered CUDA allocator. */
 B200SPLAT_API int b200splat_dist2_knn3(int32_t P, const float* xyz, float* out, void* stream);
 
 /* ---- Gaussian PLY file (host memory) --------------------------------------------------------------

@@ -96,6 +96,35 @@ def adam_step(p, g, m, v, lr, step, beta1=0.9, beta2=0.999, eps=1e-15):
     lib().orc_adam_step(ctypes.c_int64(p.size), _p(p), _p(g), _p(m), _p(v), f(lr), f(beta1), f(beta2), f(eps), ctypes.c_int(step))
 
 
+def activate_forward(scaling, rotation, opacity):
+    s, r, o = (np.ascontiguousarray(x, np.float32) for x in (scaling, rotation, opacity))
+    P = s.shape[0]
+    out = (np.zeros_like(s), np.zeros_like(r), np.zeros_like(o))
+    lib().orc_activate_forward(ctypes.c_int(P), _p(s), _p(r), _p(o), _p(out[0]), _p(out[1]), _p(out[2]))
+    return out
+
+
+def activate_backward(rotation, scales, opacities, g_scales, g_rotations, g_opacities):
+    a = [np.ascontiguousarray(x, np.float32) for x in (rotation, scales, opacities, g_scales, g_rotations, g_opacities)]
+    P = a[0].shape[0]
+    out = (np.zeros_like(a[1]), np.zeros_like(a[0]), np.zeros_like(a[2]))
+    lib().orc_activate_backward(ctypes.c_int(P), *(_p(x) for x in a), _p(out[0]), _p(out[1]), _p(out[2]))
+    return out
+
+
+def adam_step_rows(p, g, m, v, lr, lr_tail, row_width, row_split, step, beta1=0.9, beta2=0.999, eps=1e-15):
+    """Adam on a [rows, row_width] tensor whose columns >= row_split use lr_tail (FusedAdam's row_width / row_split /
+    lr_tail group keys): restated as two plain Adam steps on the two column blocks."""
+    P = p.size // row_width
+    views = [x.reshape(P, row_width) for x in (p, g, m, v)]
+    for lo, hi, rate in ((0, row_split, lr), (row_split, row_width, lr_tail)):
+        if hi > lo:
+            blk = [np.ascontiguousarray(x[:, lo:hi]) for x in views]
+            adam_step(blk[0], blk[1], blk[2], blk[3], rate, step, beta1, beta2, eps)
+            for x, b in zip((views[0], views[2], views[3]), (blk[0], blk[2], blk[3])):
+                x[:, lo:hi] = b
+
+
 def dist2_knn3(xyz: np.ndarray) -> np.ndarray:
     xyz = np.ascontiguousarray(xyz, np.float32)
     out = np.zeros(xyz.shape[0], np.float32)

@@ -112,6 +112,25 @@ def adam_case(out):
             gm.optimizer.zero_grad(set_to_none=True)
             for n, p in params.items():
                 out[f"adam_param_{n}_{k}"] = p.detach().numpy().copy()
+        # activations: GaussianModel.get_scaling / get_rotation / get_opacity (gaussian_model.py:104-130) + autograd
+        ga = torch.Generator().manual_seed(7)
+        Pa = 37
+        gm2 = GaussianModel(3)
+        raw = {"scaling": torch.randn(Pa, 3, generator=ga) - 2.0, "rotation": torch.randn(Pa, 4, generator=ga) * 3.0,
+               "opacity": torch.randn(Pa, 1, generator=ga) * 3.0}
+        raw["rotation"][5] = 0.0                       # the clamp_min(1e-12) branch of normalize
+        raw["rotation"][6] = torch.tensor([1e-3, 0.0, 0.0, 0.0])
+        gm2._scaling = torch.nn.Parameter(raw["scaling"].clone())
+        gm2._rotation = torch.nn.Parameter(raw["rotation"].clone())
+        gm2._opacity = torch.nn.Parameter(raw["opacity"].clone())
+        outs = {"scaling": gm2.get_scaling, "rotation": gm2.get_rotation, "opacity": gm2.get_opacity}
+        ups = {k: torch.randn(v.shape, generator=ga) for k, v in outs.items()}
+        sum((outs[k] * ups[k]).sum() for k in outs).backward()
+        for k, prm in (("scaling", gm2._scaling), ("rotation", gm2._rotation), ("opacity", gm2._opacity)):
+            out[f"act_raw_{k}"] = raw[k].numpy()
+            out[f"act_out_{k}"] = outs[k].detach().numpy()
+            out[f"act_up_{k}"] = ups[k].numpy()
+            out[f"act_grad_{k}"] = prm.grad.numpy().copy()
         out["adam_iters"] = np.array(iters, np.int32)
         out["adam_lrs"] = np.array(lrs, np.float64)
         out["adam_group_names"] = np.array([grp["name"] for grp in gm.optimizer.param_groups])

@@ -215,6 +215,57 @@ def test_adam_large_unaligned_and_missing_grad():
     assert new_p[-1].item() < 0.0                                                  # moved against its gradient
 
 
+def test_adam_row_split_learning_rates():
+    """One [P, M, 3] SH parameter trained with the f_dc / f_rest learning rates (row_width 48, row_split 3) equals two
+    separate Adam groups on the column blocks (the reference's layout, gaussian_model.py:187-188)."""
+    import gaussian_training as gtr
+    g = torch.Generator().manual_seed(21)
+    P, M = 1001, 16
+    feats = torch.randn(P, M, 3, generator=g)
+    p = torch.nn.Parameter(feats.clone().to(DEV))
+    opt = gtr.FusedAdam([{"params": [p], "lr": 0.0025, "lr_tail": 0.0025 / 20.0, "row_width": 3 * M, "row_split": 3,
+                          "name": "features"}], lr=0.0, eps=1e-15)
+    rp, rm, rv = feats.numpy().copy(), np.zeros((P, M, 3), np.float32), np.zeros((P, M, 3), np.float32)
+    for step in (1, 2, 3):
+        gr = torch.randn(P, M, 3, generator=g) * 1e-2
+        p.grad = gr.to(DEV)
+        opt.step()
+        no.adam_step_rows(rp, gr.numpy(), rm, rv, 0.0025, 0.0025 / 20.0, 3 * M, 3, step)
+    got = p.detach().cpu().numpy()
+    assert np.all(np.abs(got - rp) <= 1e-7 + 1e-6 * np.abs(rp))
+    _note("adam_row_split", {"elements_differing_from_oracle": int((got != rp).sum())})
+    # the two column blocks really moved at different rates
+    d = np.abs(got - feats.numpy())
+    assert d[:, 0, :].mean() > 5 * d[:, 1:, :].mean()
+
+
+def test_activations_match_reference_and_oracle():
+    import gaussian_training as gtr
+    raw = {k: torch.from_numpy(G[f"act_raw_{k}"]).to(DEV).requires_grad_() for k in ("scaling", "rotation", "opacity")}
+    s, r, o = gtr.activate(raw["scaling"], raw["rotation"], raw["opacity"])
+    ups = {k: torch.from_numpy(G[f"act_up_{k}"]).to(DEV) for k in raw}
+    ((s * ups["scaling"]).sum() + (r * ups["rotation"]).sum() + (o * ups["opacity"]).sum()).backward()
+    os_, or_, oo = no.activate_forward(*(G[f"act_raw_{k}"] for k in ("scaling", "rotation", "opacity")))
+    ods, odr, odo = no.activate_backward(G["act_raw_rotation"], os_, oo, G["act_up_scaling"], G["act_up_rotation"], G["act_up_opacity"])
+    for got, k, orc in ((s, "scaling", os_), (r, "rotation", or_), (o, "opacity", oo)):
+        got = got.detach().cpu().numpy()
+        ref = G[f"act_out_{k}"]
+        assert np.all(np.abs(got - ref) <= 1e-7 + 2e-6 * np.abs(ref)), k              # vs the reference's model: a few ulp
+        assert np.all(np.abs(got - orc) <= 1e-7 + 2e-6 * np.abs(orc)), k              # vs the C oracle
+    for k, orc in (("scaling", ods), ("rotation", odr), ("opacity", odo)):
+        got = raw[k].grad.cpu().numpy()
+        ref = G[f"act_grad_{k}"]
+        assert np.all(np.abs(got - ref) <= 1e-6 * np.abs(ref).max() + 2e-5 * np.abs(ref)), (k, float(np.abs(got - ref).max()))
+        assert np.all(np.abs(got - orc) <= 1e-6 * np.abs(orc).max() + 2e-5 * np.abs(orc)), k
+    # only some outputs used: the others get no gradient kernel input (NULL) and come back as zeros from autograd
+    raw2 = {k: torch.from_numpy(G[f"act_raw_{k}"]).to(DEV).requires_grad_() for k in raw}
+    s2, _, _ = gtr.activate(raw2["scaling"], raw2["rotation"], raw2["opacity"])
+    s2.sum().backward()
+    assert torch.allclose(raw2["scaling"].grad, s2.detach())
+    with pytest.raises(RuntimeError, match="CUDA"):
+        gtr.activate(torch.zeros(2, 3), torch.zeros(2, 4), torch.zeros(2, 1))
+
+
 def test_knn_bit_exact_against_exhaustive_search():
     from simple_knn._C import distCUDA2
     g = torch.Generator().manual_seed(11)

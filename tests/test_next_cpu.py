@@ -83,18 +83,20 @@ def test_ply_errors(tmp_path):
 def test_next_header_symbols_exported_and_plain_c(tmp_path):
     hdr = open(os.path.join(ROOT, "include", "b200splat_next.h")).read()
     names = sorted(set(re.findall(r"B200SPLAT_API\s+[\w\s\*]+?\b(b200splat_\w+)\s*\(", hdr)))
-    assert names == ["b200splat_adam_step", "b200splat_dist2_knn3", "b200splat_l1_ssim_backward", "b200splat_l1_ssim_forward",
-                     "b200splat_l1_ssim_partials", "b200splat_ply_read", "b200splat_ply_read_header", "b200splat_ply_write"]
+    assert names == ["b200splat_activate_backward", "b200splat_activate_forward", "b200splat_adam_step", "b200splat_dist2_knn3",
+                     "b200splat_l1_ssim_backward", "b200splat_l1_ssim_forward", "b200splat_l1_ssim_partials", "b200splat_ply_read",
+                     "b200splat_ply_read_header", "b200splat_ply_write", "b200splat_training_loss_backward",
+                     "b200splat_training_loss_forward"]
     lib = ctypes.CDLL(os.path.join(ROOT, "3dgs_study_b200", "libb200splat.so"))
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/b200splat_next.h but not exported"
     lib.b200splat_l1_ssim_partials.restype = ctypes.c_size_t
     assert lib.b200splat_l1_ssim_partials(3, 1080, 1920) == 3 * 34 * 60
     c = tmp_path / "t.c"
-    c.write_text('#include "b200splat_next.h"\nint main(void){ b200splat_adam_group g; (void)g; return sizeof(g) == 56 ? 0 : 1; }\n')
+    c.write_text('#include "b200splat_next.h"\nint main(void){ b200splat_adam_group g; (void)g; return sizeof(g) == 72 ? 0 : 1; }\n')
     assert os.system(f"/usr/bin/gcc -std=c99 -Wall -Werror -I{ROOT}/include {c} -o {tmp_path}/t && {tmp_path}/t") == 0
     from gaussian_training import _lib
-    assert ctypes.sizeof(_lib.AdamGroup) == 56
+    assert ctypes.sizeof(_lib.AdamGroup) == 72
 
 
 def test_gpu_entry_points_fail_loudly_on_cpu_tensors():

@@ -3,7 +3,8 @@
 (activations of gaussian_model.py:104-130, render() of gaussian_renderer/__init__.py:20-112, loss,
 backward, densification statistics, optimizer step), at BASELINE configs[1] size on one GPU, in two arms:
 
-  fused : gaussian_training.training_loss + b200splat_densify_stats + FusedAdam (this repo's 8f pieces)
+  fused : gaussian_training.activate + training_loss + b200splat_densify_stats + FusedAdam, SH coefficients
+          in one [P,M,3] parameter (this repo's 8f pieces)
   torch : the reference's own Python around the same operator -- loss_utils restated with stock torch ops,
           boolean-mask densification statistics, stock torch.optim.Adam(eps=1e-15)
 
@@ -49,8 +50,13 @@ class Model:
     def __init__(self, sc, dev, fused):
         P = sc.means3D.shape[0]
         self._xyz = torch.nn.Parameter(sc.means3D.to(dev))
-        self._features_dc = torch.nn.Parameter(sc.shs[:, :1, :].contiguous().to(dev))
-        self._features_rest = torch.nn.Parameter(sc.shs[:, 1:, :].contiguous().to(dev))
+        self.fused = fused
+        if fused:
+            # ONE [P, M, 3] SH parameter (FusedAdam trains its f_dc / f_rest columns at their own rates): no torch.cat
+            self._features = torch.nn.Parameter(sc.shs.contiguous().to(dev))
+        else:
+            self._features_dc = torch.nn.Parameter(sc.shs[:, :1, :].contiguous().to(dev))
+            self._features_rest = torch.nn.Parameter(sc.shs[:, 1:, :].contiguous().to(dev))
         self._scaling = torch.nn.Parameter(torch.log(sc.scales).to(dev))
         self._rotation = torch.nn.Parameter(sc.rotations.to(dev))
         op = sc.opacities.clamp(1e-6, 1 - 1e-6)
@@ -58,9 +64,12 @@ class Model:
         self.xyz_gradient_accum = torch.zeros(P, 1, device=dev)
         self.denom = torch.zeros(P, 1, device=dev)
         self.max_radii2D = torch.zeros(P, device=dev)
-        groups = [{"params": [self._xyz], "lr": 0.00016, "name": "xyz"},
-                  {"params": [self._features_dc], "lr": 0.0025, "name": "f_dc"},
-                  {"params": [self._features_rest], "lr": 0.0025 / 20.0, "name": "f_rest"},
+        M = sc.shs.shape[1]
+        feats = ([{"params": [self._features], "lr": 0.0025, "lr_tail": 0.0025 / 20.0, "row_width": 3 * M, "row_split": 3,
+                   "name": "features"}] if fused else
+                 [{"params": [self._features_dc], "lr": 0.0025, "name": "f_dc"},
+                  {"params": [self._features_rest], "lr": 0.0025 / 20.0, "name": "f_rest"}])
+        groups = [{"params": [self._xyz], "lr": 0.00016, "name": "xyz"}] + feats + [
                   {"params": [self._opacity], "lr": 0.05, "name": "opacity"},
                   {"params": [self._scaling], "lr": 0.005, "name": "scaling"},
                   {"params": [self._rotation], "lr": 0.001, "name": "rotation"}]
@@ -77,9 +86,14 @@ def iteration(m, cam, gt, bg, it, fused, w2):
                                        tanfovy=cam.tanfovy, bg=bg, scale_modifier=1.0, viewmatrix=cam.world_view_transform,
                                        projmatrix=cam.full_proj_transform, sh_degree=3, campos=cam.camera_center,
                                        prefiltered=False, debug=False)
-    image, radii = GaussianRasterizer(rs)(means3D=m._xyz, means2D=screen, shs=torch.cat((m._features_dc, m._features_rest), dim=1),
-                                          colors_precomp=None, opacities=torch.sigmoid(m._opacity), scales=torch.exp(m._scaling),
-                                          rotations=F.normalize(m._rotation), cov3D_precomp=None)
+    if fused:
+        shs = m._features
+        scales, rotations, opacities = gtr.activate(m._scaling, m._rotation, m._opacity)
+    else:
+        shs = torch.cat((m._features_dc, m._features_rest), dim=1)
+        scales, rotations, opacities = torch.exp(m._scaling), F.normalize(m._rotation), torch.sigmoid(m._opacity)
+    image, radii = GaussianRasterizer(rs)(means3D=m._xyz, means2D=screen, shs=shs, colors_precomp=None, opacities=opacities,
+                                          scales=scales, rotations=rotations, cov3D_precomp=None)
     if fused:
         loss, _ = gtr.training_loss(image, gt, 0.2)
     else:
@@ -105,6 +119,7 @@ def main():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--iters", type=int, default=24)
     ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--arms", default="fused,torch")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     sc = synth.make_scene(a.gaussians, 3, seed=0)
@@ -117,6 +132,8 @@ def main():
     res = {"workload": f"{a.gaussians} Gaussians SH3, {a.width}x{a.height}, one view per iteration, 8-camera orbit",
            "iters": a.iters, "warmup": a.warmup}
     for name, fused in (("fused", True), ("torch", False)):
+        if name not in a.arms.split(","):
+            continue
         try:
             m = Model(sc, dev, fused)
             for i in range(a.warmup):
