@@ -22,17 +22,22 @@ KEYS = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
 
 
 def launches(path):
-    lines = [l for l in open(path) if not l.startswith('==')]
+    lines = [l for l in open(path) if l.startswith('"')]
     agg, tot = collections.OrderedDict(), 0.0
+    scale = {'byte': 1e-6, 'Kbyte': 1e-3, 'Mbyte': 1.0, 'Gbyte': 1e3}
     for row in csv.DictReader(lines):
         v = float(row['Metric Value'].replace(',', ''))
         u = row['Metric Unit']
-        v = v / 1e3 if u == 'ns' else (v * 1e3 if u == 'ms' else v)
         k = re.sub(r'\(.*', '', row['Kernel Name'])[:100]
-        a = agg.setdefault(k, [0, 0.0]); a[0] += 1; a[1] += v; tot += v
-    print(f"# per-kernel device time over the captured launches (cold-cache, serialised: compare shares)\n# total {tot:.1f} us")
-    for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
-        print(f"{t / n:10.1f} us avg  x{n:4d}  {100 * t / tot:5.1f}%  {k}")
+        a = agg.setdefault(k, [0, 0.0, 0.0])
+        if row['Metric Name'] == 'gpu__time_duration.sum':
+            v = v / 1e3 if u in ('ns', 'nsecond') else (v * 1e3 if u in ('ms', 'msecond') else v)
+            a[0] += 1; a[1] += v; tot += v
+        elif row['Metric Name'].startswith('dram__bytes'):
+            a[2] += v * scale.get(u, 1e-6)
+    print(f"# per-kernel device time over the captured launches (cold-cache, serialised: compare shares); DRAM MB = read + write per launch\n# total {tot:.1f} us")
+    for k, (n, t, mb) in sorted(agg.items(), key=lambda x: -x[1][1]):
+        print(f"{t / n:10.1f} us avg  x{n:4d}  {100 * t / tot:5.1f}%  {mb / max(n, 1):9.1f} MB  {k}")
 
 
 def raw(path):

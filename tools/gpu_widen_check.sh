@@ -1,7 +1,6 @@
 #!/bin/bash
 # One short GPU session for the 8f pieces: parity tests, kernel timings next to the reference's own code on
-# the same box, the full training iteration, then the rasterizer parity suite (nothing there changed, the
-# library was relinked).  Every step has its own timeout; outputs land in gpurun_out/.
+# the same box, the full training iteration.  Every step has its own timeout; outputs land in gpurun_out/.
 mkdir -p gpurun_out
 rm -f gpurun_out/widen_observed.jsonl
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm,power.limit --format=csv > gpurun_out/widen_gpu.txt 2>&1
@@ -14,6 +13,3 @@ tail -6 gpurun_out/bench_next.log
 timeout 150 python tools/train_iter_bench.py > gpurun_out/train_iter.log 2>&1
 echo "exit $?" >> gpurun_out/train_iter.log
 tail -4 gpurun_out/train_iter.log
-timeout 120 python -m pytest tests/test_gpu_parity.py -q -x -m gpu -p no:cacheprovider > gpurun_out/parity_tests.log 2>&1
-echo "exit $?" >> gpurun_out/parity_tests.log
-tail -4 gpurun_out/parity_tests.log
