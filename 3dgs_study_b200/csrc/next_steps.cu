@@ -35,26 +35,49 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-// y pass of one quantity for this thread's column: LROWS outputs from LROWS + 10 staged rows
-__device__ __forceinline__ void ypass(const float (*col)[LT], int r0, int tx, const Taps& tw, float* out) {
-    float v[LROWS + 2 * LR];
+// ---- packed fp32 pairs (one FFMA2 / FMUL2 per two lanes' worth of work; each half is the IEEE result) ----------
+struct f2 { unsigned long long v; };
+__device__ __forceinline__ f2 mk2(float lo, float hi) {
+    f2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void un2(f2 a, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a.v)); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    f2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+    return r;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    f2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v));
+    return r;
+}
+__device__ __forceinline__ f2 ld2(const float2* p) { float2 t = *p; return mk2(t.x, t.y); }
+
+struct Taps2 { f2 w[2 * LR + 1]; };   // (w, w) pairs
+__device__ __forceinline__ Taps2 pair_taps(const Taps& tw) {
+    Taps2 t;
 #pragma unroll
-    for (int i = 0; i < LROWS + 2 * LR; ++i) v[i] = col[r0 + i][tx];
-#pragma unroll
-    for (int j = 0; j < LROWS; ++j) {
-        float acc = 0.0f;
-#pragma unroll
-        for (int k = 0; k < 2 * LR + 1; ++k) acc = fmaf(tw.w[k], v[j + k], acc);
-        out[j] = acc;
-    }
+    for (int k = 0; k < 2 * LR + 1; ++k) t.w[k] = mk2(tw.w[k], tw.w[k]);
+    return t;
 }
 
+constexpr int XTASKS = LIN * (LT / 2);   // x pass: one task = one staged row x two adjacent output columns
+
+// Forward.  Shared memory: the (img, gt) pair of every staged pixel interleaved (float2), and the x-filtered
+// quantities as (mu1', mu2') pairs, (E11', E22') pairs and E12' scalars.  x pass: a task owns two adjacent output
+// columns of one row, loads its 12 staged pairs with six 16-byte loads (conflict-free: consecutive tasks are 16 bytes
+// apart), forms the products once per staged pixel and runs the 11 taps on packed pairs.  y pass: a thread owns one
+// column x four rows and walks 14 staged rows.  Same tap order as the oracle (x then y, ascending), and each half of
+// a packed FMA is the IEEE fma, so results are those of the scalar formulation.
 __global__ void __launch_bounds__(LTHREADS)
 l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, Taps tw,
                    float* __restrict__ maps, size_t map_stride, float2* __restrict__ partials) {
-    __shared__ float sa[LIN][LPITCH];
-    __shared__ float sb[LIN][LPITCH];
-    __shared__ float sh[5][LIN][LT];
+    __shared__ __align__(16) float2 sab[LIN][LPITCH];
+    __shared__ __align__(16) float2 sh01[LIN][LT];
+    __shared__ __align__(16) float2 sh23[LIN][LT];
+    __shared__ __align__(16) float sh4[LIN][LT];
     __shared__ float red[2][LTHREADS / 32];
 
     const int plane = blockIdx.z;
@@ -63,41 +86,87 @@ l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
     const float* A = img + pbase;
     const float* B = gt + pbase;
 
-    for (int i = threadIdx.x; i < LIN * LIN; i += LTHREADS) {
-        int r = i / LIN, c = i - r * LIN;
-        int y = y0 + r - LR, x = x0 + c - LR;
-        bool in = (y >= 0) && (y < H) && (x >= 0) && (x < W);
-        size_t o = in ? ((size_t)y * W + x) : 0;
-        sa[r][c] = in ? __ldg(A + o) : 0.0f;
-        sb[r][c] = in ? __ldg(B + o) : 0.0f;
+    // staging: all of a thread's global loads are issued before the first shared-memory store (7 x 2 in flight)
+    {
+        constexpr int NST = (LIN * LIN + LTHREADS - 1) / LTHREADS;
+        float va[NST], vb[NST];
+#pragma unroll
+        for (int u = 0; u < NST; ++u) {
+            int i = threadIdx.x + u * LTHREADS;
+            int r = i / LIN, c = i - r * LIN;
+            int y = y0 + r - LR, x = x0 + c - LR;
+            bool in = (i < LIN * LIN) && (y >= 0) && (y < H) && (x >= 0) && (x < W);
+            size_t o = in ? ((size_t)y * W + x) : 0;
+            va[u] = in ? __ldg(A + o) : 0.0f;
+            vb[u] = in ? __ldg(B + o) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < NST; ++u) {
+            int i = threadIdx.x + u * LTHREADS;
+            int r = i / LIN, c = i - r * LIN;
+            if (i < LIN * LIN) sab[r][c] = make_float2(va[u], vb[u]);
+        }
     }
     __syncthreads();
 
-    // x pass: 42 rows x 32 columns, five quantities
-    for (int i = threadIdx.x; i < LIN * LT; i += LTHREADS) {
-        int r = i >> 5, c = i & 31;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f, s4 = 0.f;
+    const Taps2 t2 = pair_taps(tw);
+    for (int t = threadIdx.x; t < XTASKS; t += LTHREADS) {
+        const int r = t >> 4, c = (t & 15) * 2;
+        f2 ab[12], qq[12];
+        float pq[12];
+        const float4* src = reinterpret_cast<const float4*>(&sab[r][c]);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            float4 v = src[j];
+            ab[2 * j] = mk2(v.x, v.y);
+            ab[2 * j + 1] = mk2(v.z, v.w);
+            pq[2 * j] = __fmul_rn(v.x, v.y);
+            pq[2 * j + 1] = __fmul_rn(v.z, v.w);
+        }
+#pragma unroll
+        for (int j = 0; j < 12; ++j) qq[j] = mul2(ab[j], ab[j]);
+        f2 m0 = mk2(0.f, 0.f), m1 = m0, e0 = m0, e1 = m0;
+        float x0s = 0.f, x1s = 0.f;
 #pragma unroll
         for (int k = 0; k < 2 * LR + 1; ++k) {
-            float a = sa[r][c + k], b = sb[r][c + k], w = tw.w[k];
-            s0 = fmaf(w, a, s0);
-            s1 = fmaf(w, b, s1);
-            s2 = fmaf(w, __fmul_rn(a, a), s2);
-            s3 = fmaf(w, __fmul_rn(b, b), s3);
-            s4 = fmaf(w, __fmul_rn(a, b), s4);
+            m0 = fma2(t2.w[k], ab[k], m0);
+            m1 = fma2(t2.w[k], ab[k + 1], m1);
+            e0 = fma2(t2.w[k], qq[k], e0);
+            e1 = fma2(t2.w[k], qq[k + 1], e1);
+            x0s = fmaf(tw.w[k], pq[k], x0s);
+            x1s = fmaf(tw.w[k], pq[k + 1], x1s);
         }
-        sh[0][r][c] = s0; sh[1][r][c] = s1; sh[2][r][c] = s2; sh[3][r][c] = s3; sh[4][r][c] = s4;
+        float a0, a1, a2, a3;
+        un2(m0, a0, a1); un2(m1, a2, a3);
+        *reinterpret_cast<float4*>(&sh01[r][c]) = make_float4(a0, a1, a2, a3);
+        un2(e0, a0, a1); un2(e1, a2, a3);
+        *reinterpret_cast<float4*>(&sh23[r][c]) = make_float4(a0, a1, a2, a3);
+        *reinterpret_cast<float2*>(&sh4[r][c]) = make_float2(x0s, x1s);
     }
     __syncthreads();
 
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int r0 = ty * LROWS;
-    float mu1[LROWS], mu2[LROWS], e11[LROWS], e22[LROWS], e12[LROWS];
-    ypass(sh[0], r0, tx, tw, mu1);
-    ypass(sh[1], r0, tx, tw, mu2);
-    ypass(sh[2], r0, tx, tw, e11);
-    ypass(sh[3], r0, tx, tw, e22);
-    ypass(sh[4], r0, tx, tw, e12);
+    f2 mu[LROWS], ee[LROWS];
+    float e12[LROWS];
+#pragma unroll
+    for (int j = 0; j < LROWS; ++j) { mu[j] = mk2(0.f, 0.f); ee[j] = mu[j]; e12[j] = 0.f; }
+    // 14 staged rows feed 4 output rows: row i contributes to output j with tap k = i - j
+#pragma unroll
+    for (int i = 0; i < LROWS + 2 * LR; ++i) {
+        f2 v01 = ld2(&sh01[r0 + i][tx]);
+        f2 v23 = ld2(&sh23[r0 + i][tx]);
+        float v4 = sh4[r0 + i][tx];
+#pragma unroll
+        for (int j = 0; j < LROWS; ++j) {
+            const int k = i - j;
+            if (k >= 0 && k < 2 * LR + 1) {
+                mu[j] = fma2(t2.w[k], v01, mu[j]);
+                ee[j] = fma2(t2.w[k], v23, ee[j]);
+                e12[j] = fmaf(tw.w[k], v4, e12[j]);
+            }
+        }
+    }
 
     const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
     float l1 = 0.0f, ss = 0.0f;
@@ -106,15 +175,18 @@ l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
     for (int j = 0; j < LROWS; ++j) {
         int y = y0 + r0 + j;
         if (x < W && y < H) {
-            float m1 = mu1[j], m2 = mu2[j];
+            float m1, m2, e11, e22;
+            un2(mu[j], m1, m2);
+            un2(ee[j], e11, e22);
             float m11 = m1 * m1, m22 = m2 * m2, m12 = m1 * m2;
-            float s1 = e11[j] - m11, s2 = e22[j] - m22, s12 = e12[j] - m12;
+            float s1 = e11 - m11, s2 = e22 - m22, s12 = e12[j] - m12;
             float An = 2.0f * m12 + C1, Bn = 2.0f * s12 + C2;
             float Cd = m11 + m22 + C1, Dd = s1 + s2 + C2;
             float inv = 1.0f / (Cd * Dd);
             float m = An * Bn * inv;
             ss += m;
-            l1 += fabsf(sa[r0 + j + LR][tx + LR] - sb[r0 + j + LR][tx + LR]);
+            float2 px = sab[r0 + j + LR][tx + LR];
+            l1 += fabsf(px.x - px.y);
             if (maps) {
                 size_t o = pbase + (size_t)y * W + x;
                 maps[o] = 2.0f * inv * (m2 * (Bn - An) - m1 * m * (Dd - Cd));
@@ -175,47 +247,107 @@ l1_ssim_loss_kernel(int n_partials, double inv_count, float lambda, const float2
     }
 }
 
+// Backward: the same stencil over the three derivative maps, (d m/d mu1, d m/d E11) as packed pairs and d m/d E12
+// as scalars.
 __global__ void __launch_bounds__(LTHREADS)
 l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, Taps tw,
                    const float* __restrict__ maps, size_t map_stride, const float* __restrict__ scale,
                    const float* __restrict__ upstream, float c_l1, float c_ssim, float* __restrict__ dimg) {
-    __shared__ float sm[3][LIN][LPITCH];
-    __shared__ float sh[3][LIN][LT];
+    __shared__ __align__(16) float2 s01[LIN][LPITCH];
+    __shared__ __align__(16) float s2[LIN][LPITCH];
+    __shared__ __align__(16) float2 h01[LIN][LT];
+    __shared__ __align__(16) float h2[LIN][LT];
 
     const int plane = blockIdx.z;
     const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
     const size_t pbase = (size_t)plane * H * W;
 
-    for (int i = threadIdx.x; i < LIN * LIN; i += LTHREADS) {
-        int r = i / LIN, c = i - r * LIN;
-        int y = y0 + r - LR, x = x0 + c - LR;
-        bool in = (y >= 0) && (y < H) && (x >= 0) && (x < W);
-        size_t o = in ? (pbase + (size_t)y * W + x) : 0;
-        sm[0][r][c] = in ? __ldg(maps + o) : 0.0f;
-        sm[1][r][c] = in ? __ldg(maps + map_stride + o) : 0.0f;
-        sm[2][r][c] = in ? __ldg(maps + 2 * map_stride + o) : 0.0f;
+    {
+        constexpr int NST = (LIN * LIN + LTHREADS - 1) / LTHREADS;
+        float v0[NST], v1[NST], v2[NST];
+#pragma unroll
+        for (int u = 0; u < NST; ++u) {
+            int i = threadIdx.x + u * LTHREADS;
+            int r = i / LIN, c = i - r * LIN;
+            int y = y0 + r - LR, x = x0 + c - LR;
+            bool in = (i < LIN * LIN) && (y >= 0) && (y < H) && (x >= 0) && (x < W);
+            size_t o = in ? (pbase + (size_t)y * W + x) : 0;
+            v0[u] = in ? __ldg(maps + o) : 0.0f;
+            v1[u] = in ? __ldg(maps + map_stride + o) : 0.0f;
+            v2[u] = in ? __ldg(maps + 2 * map_stride + o) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < NST; ++u) {
+            int i = threadIdx.x + u * LTHREADS;
+            int r = i / LIN, c = i - r * LIN;
+            if (i < LIN * LIN) { s01[r][c] = make_float2(v0[u], v1[u]); s2[r][c] = v2[u]; }
+        }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < LIN * LT; i += LTHREADS) {
-        int r = i >> 5, c = i & 31;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+
+    // this thread's four pixels of img / gt for the epilogue: requested now, consumed after the two passes
+    float pa[LROWS], pb[LROWS];
+    {
+        const int ex = x0 + (threadIdx.x & 31), ey = y0 + (threadIdx.x >> 5) * LROWS;
+#pragma unroll
+        for (int j = 0; j < LROWS; ++j) {
+            bool in = (ex < W) && (ey + j < H);
+            size_t o = in ? (pbase + (size_t)(ey + j) * W + ex) : 0;
+            pa[j] = in ? __ldg(img + o) : 0.0f;
+            pb[j] = in ? __ldg(gt + o) : 0.0f;
+        }
+    }
+    const Taps2 t2 = pair_taps(tw);
+    for (int t = threadIdx.x; t < XTASKS; t += LTHREADS) {
+        const int r = t >> 4, c = (t & 15) * 2;
+        f2 ab[12];
+        float q[12];
+        const float4* src = reinterpret_cast<const float4*>(&s01[r][c]);
+        const float2* src2 = reinterpret_cast<const float2*>(&s2[r][c]);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            float4 v = src[j];
+            ab[2 * j] = mk2(v.x, v.y);
+            ab[2 * j + 1] = mk2(v.z, v.w);
+            float2 u = src2[j];
+            q[2 * j] = u.x;
+            q[2 * j + 1] = u.y;
+        }
+        f2 m0 = mk2(0.f, 0.f), m1 = m0;
+        float x0s = 0.f, x1s = 0.f;
 #pragma unroll
         for (int k = 0; k < 2 * LR + 1; ++k) {
-            float w = tw.w[k];
-            s0 = fmaf(w, sm[0][r][c + k], s0);
-            s1 = fmaf(w, sm[1][r][c + k], s1);
-            s2 = fmaf(w, sm[2][r][c + k], s2);
+            m0 = fma2(t2.w[k], ab[k], m0);
+            m1 = fma2(t2.w[k], ab[k + 1], m1);
+            x0s = fmaf(tw.w[k], q[k], x0s);
+            x1s = fmaf(tw.w[k], q[k + 1], x1s);
         }
-        sh[0][r][c] = s0; sh[1][r][c] = s1; sh[2][r][c] = s2;
+        float a0, a1, a2, a3;
+        un2(m0, a0, a1); un2(m1, a2, a3);
+        *reinterpret_cast<float4*>(&h01[r][c]) = make_float4(a0, a1, a2, a3);
+        *reinterpret_cast<float2*>(&h2[r][c]) = make_float2(x0s, x1s);
     }
     __syncthreads();
 
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int r0 = ty * LROWS;
-    float f0[LROWS], f1[LROWS], f2[LROWS];
-    ypass(sh[0], r0, tx, tw, f0);
-    ypass(sh[1], r0, tx, tw, f1);
-    ypass(sh[2], r0, tx, tw, f2);
+    f2 f01[LROWS];
+    float f2s[LROWS];
+#pragma unroll
+    for (int j = 0; j < LROWS; ++j) { f01[j] = mk2(0.f, 0.f); f2s[j] = 0.f; }
+#pragma unroll
+    for (int i = 0; i < LROWS + 2 * LR; ++i) {
+        f2 v01 = ld2(&h01[r0 + i][tx]);
+        float v2 = h2[r0 + i][tx];
+#pragma unroll
+        for (int j = 0; j < LROWS; ++j) {
+            const int k = i - j;
+            if (k >= 0 && k < 2 * LR + 1) {
+                f01[j] = fma2(t2.w[k], v01, f01[j]);
+                f2s[j] = fmaf(tw.w[k], v2, f2s[j]);
+            }
+        }
+    }
     // per-plane factors, or one upstream scalar times two host constants (the fused training loss)
     const float up = upstream ? __ldg(upstream) : 1.0f;
     const float sl = scale ? __ldg(scale + 2 * plane) : up * c_l1;
@@ -226,10 +358,12 @@ l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
         int y = y0 + r0 + j;
         if (x < W && y < H) {
             size_t o = pbase + (size_t)y * W + x;
-            float a = __ldg(img + o), b = __ldg(gt + o);
+            float a = pa[j], b = pb[j];
             float d = a - b;
             float sg = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);
-            float g = f0[j] + 2.0f * a * f1[j] + b * f2[j];
+            float f0, f1;
+            un2(f01[j], f0, f1);
+            float g = f0 + 2.0f * a * f1 + b * f2s[j];
             dimg[o] = sl * sg + ssc * g;
         }
     }

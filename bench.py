@@ -52,6 +52,7 @@ def parse_args():
                     help="N>1 gradient exchange (default: factorized); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
     ap.add_argument("--peer-memory", action="store_true", help="factorized exchange through NVLink peer mappings (fused rebuild kernel + multimem all-reduce) instead of NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train-iter", action="store_true", help="skip the full-training-iteration measurement (N=1 only)")
     ap.add_argument("--cpu-tile-stride", type=int, default=16, help="CPU legs render 1/stride of the tiles")
     ap.add_argument("--stages", action="store_true", help="print the per-stage table to stderr")
     return ap.parse_args()
@@ -537,6 +538,18 @@ def main():
             line["cpu_baseline_torch_config1"] = torch_oracle_config1()
         except Exception as e:   # reported, never fatal
             line["cpu_baseline_torch_config1"] = {"error": str(e)}
+    if int(os.environ.get("WORLD_SIZE", "1")) == 1 and a.impl == "ours" and a.sh_degree == 3 and not a.no_train_iter:
+        # beside the headline metric: one full training iteration around the operator, fused
+        # pieces of this repo vs the reference's own torch code around the same operator; reported, never fatal
+        try:
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("train_iter_bench", os.path.join(ROOT, "tools", "train_iter_bench.py"))
+            tib = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(tib)
+            torch.cuda.empty_cache()
+            line["training_iteration"] = tib.measure(a.gaussians, a.width, a.height, iters=24, warmup=4)
+        except Exception as e:
+            line["training_iteration"] = {"error": repr(e)}
     if a.stages:
         for k, v in (line.get("roofline") or {}).get("per_stage", {}).items():
             print(f"{k:16s} {v['ms']:8.3f} ms  {v['gbs']:8.1f} GB/s  {100 * v['frac_hbm']:5.1f}% of HBM peak", file=sys.stderr)

@@ -166,9 +166,9 @@ def test_adam_matches_reference_optimizer_and_oracle():
             assert np.all(np.abs(got - ref) <= 2e-7 + 1e-6 * np.abs(ref)), (n, k, float(np.abs(got - ref).max()))
             p, m, v = orc[n]
             no.adam_step(p, np.ascontiguousarray(G[f"adam_grad_{n}_{k}"]), m, v, float(opt.param_groups[gi]["lr"]), k + 1)
-            # vs the C oracle (same rounding points): 1e-6 relative; the number of differing elements is recorded
-            assert np.all(np.abs(got - p) <= 1e-7 + 1e-6 * np.abs(p)), (n, k)
+            # vs the C oracle (same rounding points, IEEE division and square root on both sides): bit-exact
             mism += int((got != p).sum())
+            assert np.array_equal(got, p), (n, k, int((got != p).sum()), float(np.abs(got - p).max()))
     for n in ADAM_NAMES:
         st = opt.state[params[n]]
         assert int(st["step"].item()) == len(iters)
@@ -232,7 +232,7 @@ def test_adam_row_split_learning_rates():
         opt.step()
         no.adam_step_rows(rp, gr.numpy(), rm, rv, 0.0025, 0.0025 / 20.0, 3 * M, 3, step)
     got = p.detach().cpu().numpy()
-    assert np.all(np.abs(got - rp) <= 1e-7 + 1e-6 * np.abs(rp))
+    assert np.array_equal(got, rp), int((got != rp).sum())                      # bit-exact vs the C oracle
     _note("adam_row_split", {"elements_differing_from_oracle": int((got != rp).sum())})
     # the two column blocks really moved at different rates
     d = np.abs(got - feats.numpy())

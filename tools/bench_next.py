@@ -90,12 +90,28 @@ def main():
 
     t_ours, t_ref = timed(ours, a.iters), timed(ref, a.iters)
     n = img.numel()
+    # the two kernels alone, through the C ABI (no autograd bookkeeping): forward(+finalize) and backward
+    from gaussian_training import _lib as nl
+    L = nl.lib()
+    wt = gtr.loss_utils.window_taps(11)
+    ai, bi = img.detach().contiguous(), gt.contiguous()
+    maps = torch.empty(3, 3, 1080, 1920, device=dev)
+    parts = torch.empty(L.b200splat_l1_ssim_partials(3, 1080, 1920), 2, device=dev)
+    out3, up, da = torch.empty(3, device=dev), torch.ones(3, device=dev), torch.empty_like(ai)
+    sp = nl.stream_ptr(dev)
+    k_fwd = timed(lambda: L.b200splat_training_loss_forward(3, 1080, 1920, ai.data_ptr(), bi.data_ptr(), ctypes.addressof(wt), 0.2,
+                                                            maps.data_ptr(), parts.data_ptr(), out3.data_ptr(), sp), 50)
+    k_bwd = timed(lambda: L.b200splat_training_loss_backward(3, 1080, 1920, ai.data_ptr(), bi.data_ptr(), ctypes.addressof(wt), 0.2,
+                                                             maps.data_ptr(), up.data_ptr(), da.data_ptr(), sp), 50)
     algo = 44 * n     # fwd 8 in + 12 out, bwd 20 in + 4 out bytes per pixel and plane
     lines.append({"step": "l1_ssim_loss fwd+bwd", "workload": "3x1080x1920 fp32, lambda 0.2", "ms": t_ours,
                   "torch_reference_ms": t_ref, "speedup_vs_torch": t_ref / t_ours, "algo_bytes": algo,
                   "achieved_gbs": algo / t_ours / 1e6, "hbm_peak_gbs": hbm, "frac": (algo / t_ours / 1e6 / hbm) if hbm else None,
-                  "note": "includes the autograd bookkeeping and the tiny mean/scale ops around the two kernels"})
-    del img, gt
+                  "kernels_fwd_ms": k_fwd, "kernels_bwd_ms": k_bwd, "kernels_gbs": algo / (k_fwd + k_bwd) / 1e6,
+                  "kernels_frac": (algo / (k_fwd + k_bwd) / 1e6 / hbm) if hbm else None,
+                  "note": "ms = through autograd (includes its bookkeeping; host-launch bound when run back to back); "
+                          "kernels_* = the C-ABI calls alone, back to back (working set 0.3 GB > L2)"})
+    del img, gt, maps
 
     # ---- Adam -------------------------------------------------------------------------------------------
     P = a.gaussians

@@ -29,7 +29,6 @@ import diff_gaussian_rasterization as dgr  # noqa: E402
 import gaussian_training as gtr  # noqa: E402
 from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _C  # noqa: E402
 
-dgr.LEGACY_OUTPUTS = True     # the reference call site unpacks (color, radii)
 
 
 def torch_ssim(img1, img2, w2):
@@ -112,6 +111,56 @@ def iteration(m, cam, gt, bg, it, fused, w2):
     return loss
 
 
+def measure(gaussians=3_000_000, width=1920, height=1080, iters=24, warmup=4, arms=("fused", "torch")):
+    """Time the two arms; returns the result dict (errors of an arm are reported in place, never raised)."""
+    legacy = dgr.LEGACY_OUTPUTS
+    dgr.LEGACY_OUTPUTS = True     # the reference call site unpacks (color, radii)
+    try:
+        return _measure(gaussians, width, height, iters, warmup, arms)
+    finally:
+        dgr.LEGACY_OUTPUTS = legacy
+
+
+def _measure(gaussians, width, height, iters, warmup, arms):
+    dev = torch.device("cuda:0")
+    sc = synth.make_scene(gaussians, 3, seed=0)
+    cams = [synth.make_camera(width, height, yaw=2 * math.pi * k / 8).to(dev) for k in range(8)]
+    g = torch.Generator().manual_seed(5)
+    gt = torch.rand(3, height, width, generator=g).to(dev)
+    bg = torch.zeros(3, device=dev)
+    taps = torch.tensor(list(gtr.loss_utils.window_taps(11)), device=dev)
+    w2 = (taps[:, None] * taps[None, :]).expand(3, 1, 11, 11).contiguous()
+    res = {"workload": f"{gaussians} Gaussians SH3, {width}x{height}, one view per iteration, 8-camera orbit: activations, "
+                       "render, L1+SSIM loss, backward, densification statistics, Adam step",
+           "iters": iters, "warmup": warmup}
+    for name, fused in (("fused", True), ("torch", False)):
+        if name not in arms:
+            continue
+        try:
+            m = Model(sc, dev, fused)
+            for i in range(warmup):
+                iteration(m, cams[i % 8], gt, bg, i + 1, fused, w2)
+            torch.cuda.synchronize()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            for i in range(iters):
+                loss = iteration(m, cams[i % 8], gt, bg, warmup + i + 1, fused, w2)
+            e.record()
+            torch.cuda.synchronize()
+            ms = s.elapsed_time(e) / iters
+            res[name] = {"ms_per_iteration": round(ms, 4), "iterations_per_s": round(1000.0 / ms, 2), "last_loss": float(loss.item())}
+            del m
+            torch.cuda.empty_cache()
+        except Exception as ex:  # report and keep going: the other arm is still worth having
+            res[name] = {"error": repr(ex)}
+    if "ms_per_iteration" in res.get("fused", {}) and "ms_per_iteration" in res.get("torch", {}):
+        res["speedup_fused_vs_torch"] = round(res["torch"]["ms_per_iteration"] / res["fused"]["ms_per_iteration"], 3)
+    res["arms"] = {"fused": "gaussian_training.activate + training_loss + b200splat_densify_stats + FusedAdam, SH in one parameter",
+                   "torch": "the reference's own torch code around the same operator (cat/exp/sigmoid/normalize, conv2d SSIM, "
+                            "masked-index statistics, stock torch.optim.Adam)"}
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gaussians", type=int, default=3_000_000)
@@ -121,39 +170,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--arms", default="fused,torch")
     a = ap.parse_args()
-    dev = torch.device("cuda:0")
-    sc = synth.make_scene(a.gaussians, 3, seed=0)
-    cams = [synth.make_camera(a.width, a.height, yaw=2 * math.pi * k / 8).to(dev) for k in range(8)]
-    g = torch.Generator().manual_seed(5)
-    gt = torch.rand(3, a.height, a.width, generator=g).to(dev)
-    bg = torch.zeros(3, device=dev)
-    taps = torch.tensor(list(gtr.loss_utils.window_taps(11)), device=dev)
-    w2 = (taps[:, None] * taps[None, :]).expand(3, 1, 11, 11).contiguous()
-    res = {"workload": f"{a.gaussians} Gaussians SH3, {a.width}x{a.height}, one view per iteration, 8-camera orbit",
-           "iters": a.iters, "warmup": a.warmup}
-    for name, fused in (("fused", True), ("torch", False)):
-        if name not in a.arms.split(","):
-            continue
-        try:
-            m = Model(sc, dev, fused)
-            for i in range(a.warmup):
-                iteration(m, cams[i % 8], gt, bg, i + 1, fused, w2)
-            torch.cuda.synchronize()
-            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s.record()
-            for i in range(a.iters):
-                loss = iteration(m, cams[i % 8], gt, bg, a.warmup + i + 1, fused, w2)
-            e.record()
-            torch.cuda.synchronize()
-            ms = s.elapsed_time(e) / a.iters
-            res[name] = {"ms_per_iteration": ms, "iterations_per_s": 1000.0 / ms, "last_loss": float(loss.item()),
-                         "peak_mem_gb": torch.cuda.max_memory_allocated() / 2 ** 30}
-            del m
-            torch.cuda.empty_cache()
-        except Exception as ex:  # report and keep going: the other arm is still worth having
-            res[name] = {"error": repr(ex)}
-    if "ms_per_iteration" in res.get("fused", {}) and "ms_per_iteration" in res.get("torch", {}):
-        res["speedup_fused_vs_torch"] = res["torch"]["ms_per_iteration"] / res["fused"]["ms_per_iteration"]
+    res = measure(a.gaussians, a.width, a.height, a.iters, a.warmup, tuple(a.arms.split(",")))
     print(json.dumps(res))
     out = os.path.join(ROOT, "gpurun_out")
     if os.path.isdir(out):
