@@ -86,25 +86,33 @@ l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
     const float* A = img + pbase;
     const float* B = gt + pbase;
 
-    // staging: all of a thread's global loads are issued before the first shared-memory store (7 x 2 in flight)
+    // staging: a warp owns staged rows w, w+8, ...; a lane owns columns lane and lane+32 of a row (no divisions, one
+    // row pointer per row); all of a thread's global loads are issued before its first shared-memory store
     {
-        constexpr int NST = (LIN * LIN + LTHREADS - 1) / LTHREADS;
-        float va[NST], vb[NST];
+        constexpr int NR = (LIN + LTHREADS / 32 - 1) / (LTHREADS / 32);      // 6 rows per warp
+        const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+        const int xa = x0 + lane - LR, xb = xa + 32;
+        const bool xa_in = (xa >= 0) && (xa < W);
+        const bool xb_in = (lane < LIN - 32) && (xb >= 0) && (xb < W);
+        float va[NR][2], vb[NR][2];
 #pragma unroll
-        for (int u = 0; u < NST; ++u) {
-            int i = threadIdx.x + u * LTHREADS;
-            int r = i / LIN, c = i - r * LIN;
-            int y = y0 + r - LR, x = x0 + c - LR;
-            bool in = (i < LIN * LIN) && (y >= 0) && (y < H) && (x >= 0) && (x < W);
-            size_t o = in ? ((size_t)y * W + x) : 0;
-            va[u] = in ? __ldg(A + o) : 0.0f;
-            vb[u] = in ? __ldg(B + o) : 0.0f;
+        for (int u = 0; u < NR; ++u) {
+            const int r = wrp + (LTHREADS / 32) * u;
+            const int y = y0 + r - LR;
+            const bool yin = (r < LIN) && (y >= 0) && (y < H);
+            const size_t ro = (size_t)(yin ? y : 0) * W;
+            va[u][0] = (yin && xa_in) ? __ldg(A + ro + xa) : 0.0f;
+            vb[u][0] = (yin && xa_in) ? __ldg(B + ro + xa) : 0.0f;
+            va[u][1] = (yin && xb_in) ? __ldg(A + ro + xb) : 0.0f;
+            vb[u][1] = (yin && xb_in) ? __ldg(B + ro + xb) : 0.0f;
         }
 #pragma unroll
-        for (int u = 0; u < NST; ++u) {
-            int i = threadIdx.x + u * LTHREADS;
-            int r = i / LIN, c = i - r * LIN;
-            if (i < LIN * LIN) sab[r][c] = make_float2(va[u], vb[u]);
+        for (int u = 0; u < NR; ++u) {
+            const int r = wrp + (LTHREADS / 32) * u;
+            if (r < LIN) {
+                sab[r][lane] = make_float2(va[u][0], vb[u][0]);
+                if (lane < LIN - 32) sab[r][lane + 32] = make_float2(va[u][1], vb[u][1]);
+            }
         }
     }
     __syncthreads();
@@ -190,7 +198,7 @@ l1_ssim_fwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
             if (maps) {
                 size_t o = pbase + (size_t)y * W + x;
                 maps[o] = 2.0f * inv * (m2 * (Bn - An) - m1 * m * (Dd - Cd));
-                maps[map_stride + o] = -m / Dd;
+                maps[map_stride + o] = -(m * (inv * Cd));     // -m / Dd with 1/Dd = inv * Cd: one division per pixel
                 maps[2 * map_stride + o] = 2.0f * An * inv;
             }
         }
@@ -249,7 +257,7 @@ l1_ssim_loss_kernel(int n_partials, double inv_count, float lambda, const float2
 
 // Backward: the same stencil over the three derivative maps, (d m/d mu1, d m/d E11) as packed pairs and d m/d E12
 // as scalars.
-__global__ void __launch_bounds__(LTHREADS)
+__global__ void __launch_bounds__(LTHREADS, 5)
 l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, Taps tw,
                    const float* __restrict__ maps, size_t map_stride, const float* __restrict__ scale,
                    const float* __restrict__ upstream, float c_l1, float c_ssim, float* __restrict__ dimg) {
@@ -263,28 +271,43 @@ l1_ssim_bwd_kernel(int H, int W, const float* __restrict__ img, const float* __r
     const size_t pbase = (size_t)plane * H * W;
 
     {
-        constexpr int NST = (LIN * LIN + LTHREADS - 1) / LTHREADS;
-        float v0[NST], v1[NST], v2[NST];
+        constexpr int NR = (LIN + LTHREADS / 32 - 1) / (LTHREADS / 32);      // 6 rows per warp
+        const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+        const int xa = x0 + lane - LR, xb = xa + 32;
+        const bool xa_in = (xa >= 0) && (xa < W);
+        const bool xb_in = (lane < LIN - 32) && (xb >= 0) && (xb < W);
+        const float* m0 = maps + pbase;
+        const float* m1 = m0 + map_stride;
+        const float* m2 = m1 + map_stride;
+        float v0[NR][2], v1[NR][2], v2[NR][2];
 #pragma unroll
-        for (int u = 0; u < NST; ++u) {
-            int i = threadIdx.x + u * LTHREADS;
-            int r = i / LIN, c = i - r * LIN;
-            int y = y0 + r - LR, x = x0 + c - LR;
-            bool in = (i < LIN * LIN) && (y >= 0) && (y < H) && (x >= 0) && (x < W);
-            size_t o = in ? (pbase + (size_t)y * W + x) : 0;
-            v0[u] = in ? __ldg(maps + o) : 0.0f;
-            v1[u] = in ? __ldg(maps + map_stride + o) : 0.0f;
-            v2[u] = in ? __ldg(maps + 2 * map_stride + o) : 0.0f;
+        for (int u = 0; u < NR; ++u) {
+            const int r = wrp + (LTHREADS / 32) * u;
+            const int y = y0 + r - LR;
+            const bool yin = (r < LIN) && (y >= 0) && (y < H);
+            const size_t ro = (size_t)(yin ? y : 0) * W;
+            const bool ia = yin && xa_in, ib = yin && xb_in;
+            v0[u][0] = ia ? __ldg(m0 + ro + xa) : 0.0f;
+            v1[u][0] = ia ? __ldg(m1 + ro + xa) : 0.0f;
+            v2[u][0] = ia ? __ldg(m2 + ro + xa) : 0.0f;
+            v0[u][1] = ib ? __ldg(m0 + ro + xb) : 0.0f;
+            v1[u][1] = ib ? __ldg(m1 + ro + xb) : 0.0f;
+            v2[u][1] = ib ? __ldg(m2 + ro + xb) : 0.0f;
         }
 #pragma unroll
-        for (int u = 0; u < NST; ++u) {
-            int i = threadIdx.x + u * LTHREADS;
-            int r = i / LIN, c = i - r * LIN;
-            if (i < LIN * LIN) { s01[r][c] = make_float2(v0[u], v1[u]); s2[r][c] = v2[u]; }
+        for (int u = 0; u < NR; ++u) {
+            const int r = wrp + (LTHREADS / 32) * u;
+            if (r < LIN) {
+                s01[r][lane] = make_float2(v0[u][0], v1[u][0]);
+                s2[r][lane] = v2[u][0];
+                if (lane < LIN - 32) {
+                    s01[r][lane + 32] = make_float2(v0[u][1], v1[u][1]);
+                    s2[r][lane + 32] = v2[u][1];
+                }
+            }
         }
     }
     __syncthreads();
-
     // this thread's four pixels of img / gt for the epilogue: requested now, consumed after the two passes
     float pa[LROWS], pb[LROWS];
     {
