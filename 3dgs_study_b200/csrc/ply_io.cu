@@ -1,5 +1,5 @@
 // ply_io.cu -- host-side codec of the Gaussian PLY file (include/b200splat_next.h; the wire format of
-// GaussianModel.save_ply / load_ply, /root/reference/scene/gaussian_model.py:218-258,267-318).  Host memory
+// GaussianModel.save_ply / load_ply, /root/reference/scene/gaussian_model.py:218-259,267-320).  Host memory
 // only; compiled with the library so the format lives next to the kernels that consume it.
 //
 // File: "ply / format binary_little_endian 1.0 / element vertex P / property float <name> ... / end_header",

@@ -1,7 +1,7 @@
 """Activations of the raw Gaussian parameters in one kernel each way (b200splat_activate_forward / _backward):
 scales = exp(_scaling), rotations = normalize(_rotation), opacities = sigmoid(_opacity) -- what
 GaussianModel.get_scaling / get_rotation / get_opacity compute with separate torch ops
-(/root/reference/scene/gaussian_model.py:34-42, 104-130).  CUDA fp32 only, no fallback."""
+(/root/reference/scene/gaussian_model.py:34-42, 106-127).  CUDA fp32 only, no fallback."""
 from __future__ import annotations
 
 import torch

@@ -1,8 +1,8 @@
 """Adam over the Gaussian parameter groups in ONE kernel launch (b200splat_adam_step).
 
 `FusedAdam` subclasses torch.optim.Adam so that everything the reference does to its optimizer keeps working
-unchanged -- construction with named param groups (scene/gaussian_model.py:185-203), per-iteration
-`param_group['lr'] = ...` (:210-216), the state surgery of densification (`optimizer.state[...]['exp_avg']`,
+unchanged -- construction with named param groups (scene/gaussian_model.py:185-197), per-iteration
+`param_group['lr'] = ...` (:207-214), the state surgery of densification (`optimizer.state[...]['exp_avg']`,
 deleting / re-inserting state entries: replace_tensor_to_optimizer, _prune_optimizer, cat_tensors_to_optimizer),
 state_dict()/load_state_dict() -- and only `step()` is replaced.  Same state layout as torch (state[p] =
 {'step': tensor, 'exp_avg', 'exp_avg_sq'}), same formulas; CUDA fp32 parameters only, no fallback.

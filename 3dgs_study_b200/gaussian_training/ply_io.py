@@ -1,7 +1,7 @@
 """Gaussian PLY file: the wire format of GaussianModel.save_ply / load_ply
-(/root/reference/scene/gaussian_model.py:218-258, 267-318) without the `plyfile` package (absent from this image).
+(/root/reference/scene/gaussian_model.py:218-259, 267-320) without the `plyfile` package (absent from this image).
 The codec is native host code in libb200splat.so (csrc/ply_io.cu: b200splat_ply_write / _read); tensors may live
-on any device and come back on the CPU (the reference moves them to "cuda" itself, :309-316)."""
+on any device and come back on the CPU (the reference moves them to "cuda" itself, :309-317)."""
 from __future__ import annotations
 
 import ctypes
@@ -23,7 +23,7 @@ def _host(t, shape):
 def save_ply(path: str, xyz, features_dc, features_rest, opacity, scaling, rotation) -> None:
     """Raw (pre-activation) values, as the reference stores them: xyz [P,3], features_dc [P,1,3],
     features_rest [P,M-1,3], opacity [P,1], scaling [P,3], rotation [P,4].  Creates the directory like
-    save_ply's mkdir_p (:234)."""
+    save_ply's mkdir_p (:241)."""
     P = int(xyz.shape[0])
     K = int(features_rest.shape[1]) if features_rest is not None and features_rest.dim() == 3 else 0
     a = [_host(xyz, (P, 3)), _host(features_dc, (P, 3)),
@@ -37,7 +37,7 @@ def save_ply(path: str, xyz, features_dc, features_rest, opacity, scaling, rotat
 
 def load_ply(path: str):
     """-> dict(xyz [P,3], features_dc [P,1,3], features_rest [P,M-1,3], opacity [P,1], scaling [P,3],
-    rotation [P,4]) of CPU fp32 tensors, in the layouts load_ply builds (:291-316)."""
+    rotation [P,4]) of CPU fp32 tensors, in the layouts load_ply builds (:279-317)."""
     L = _lib.lib()
     P = ctypes.c_int64(0)
     n_rest = ctypes.c_int32(0)

@@ -11,13 +11,13 @@
  *           kernels each way.
  *   b200splat_adam_step
  *       <-> gaussians.optimizer.step() (train.py:137-141) on the optimizer built at
- *           scene/gaussian_model.py:185-203: torch.optim.Adam(lr=0, eps=1e-15) over six parameter groups
- *           with per-group learning rates (xyz rescheduled every iteration, :210-216).  All groups in ONE launch.
+ *           scene/gaussian_model.py:185-197: torch.optim.Adam(lr=0, eps=1e-15) over six parameter groups
+ *           with per-group learning rates (xyz rescheduled every iteration, :207-214).  All groups in ONE launch.
  *   b200splat_dist2_knn3
  *       <-> simple_knn._C.distCUDA2 (submodules/simple-knn/spatial.cu:15-26 -> simple_knn.cu:186-221), called
  *           at scene/gaussian_model.py:153 to initialise the scales.
  *   b200splat_ply_write / _read_header / _read   (HOST memory; no GPU involved)
- *       <-> GaussianModel.save_ply / load_ply (scene/gaussian_model.py:233-258, 267-318), which go through
+ *       <-> GaussianModel.save_ply / load_ply (scene/gaussian_model.py:240-259, 267-320), which go through
  *           the third-party `plyfile` package (absent from this image).
  *
  * Device pointers are owned by the caller and valid on `stream`'s device; all device work is enqueued on
@@ -68,7 +68,7 @@ B200SPLAT_API int b200splat_training_loss_backward(int32_t planes, int32_t heigh
                            const float* upstream, float* dL_dimg, void* stream);
 
 /* ---- Activations of the raw parameters --------------------------------------------------------------
- * GaussianModel.get_scaling / get_rotation / get_opacity (scene/gaussian_model.py:104-130 over the
+ * GaussianModel.get_scaling / get_rotation / get_opacity (scene/gaussian_model.py:106-127 over the
  * functions set at :34-42): scales = exp(scaling), rotations = normalize(rotation) = rotation /
  * max(||rotation||_2, 1e-12), opacities = sigmoid(opacity); [P,3], [P,4], [P,1] device arrays.  The backward
  * takes the activated values the forward produced and the gradients the rasterizer returned for them; any of
@@ -116,9 +116,9 @@ B200SPLAT_API int b200splat_dist2_knn3(int32_t P, const float* xyz, float* out, 
 
 /* ---- Gaussian PLY file (host memory) --------------------------------------------------------------
  * binary_little_endian 1.0, one `vertex` element, float properties x y z nx ny nz f_dc_0..2
- * f_rest_0..(n_rest-1) opacity scale_0..2 rot_0..3 (scene/gaussian_model.py:218-231), raw pre-activation
+ * f_rest_0..(n_rest-1) opacity scale_0..2 rot_0..3 (scene/gaussian_model.py:218-238), raw pre-activation
  * values.  f_dc is [P,1,3] and f_rest [P,n_rest/3,3] in memory; the file holds them channel-major
- * (transpose(1,2).flatten, :238-239), and the reader transposes back (:291-295).  Normals are written as
+ * (transpose(1,2).flatten, :245-246), and the reader transposes back (:291-293, 310-313).  Normals are written as
  * zeros and ignored on read.  The reader finds properties by NAME (any order, extra properties skipped).
  */
 B200SPLAT_API int b200splat_ply_write(const char* path, int64_t P, int32_t n_rest, const float* xyz,

@@ -2,9 +2,9 @@
 
 CPU restatements of the steps either side of the rasterizer: L1 + SSIM loss
 (/root/reference/utils/loss_utils.py:17-24,35-108), the Adam step over the Gaussian parameters
-(/root/reference/scene/gaussian_model.py:185-213, train.py:137-141), distCUDA2
+(/root/reference/scene/gaussian_model.py:185-214, train.py:137-141), distCUDA2
 (/root/reference/submodules/simple-knn/simple_knn.cu:46-222) and the Gaussian PLY file
-(/root/reference/scene/gaussian_model.py:218-258,267-318; numpy, below).  Only tests/,
+(/root/reference/scene/gaussian_model.py:218-259,267-320; numpy, below).  Only tests/,
 __graft_entry__.smoke() and bench.py's cpu_baseline leg may import this module.
 """
 from __future__ import annotations
@@ -89,7 +89,7 @@ def loss_and_grad(a, b, lambda_dssim: float = 0.2, window_size: int = 11):
 
 
 def adam_step(p, g, m, v, lr, step, beta1=0.9, beta2=0.999, eps=1e-15):
-    """In place on float32 arrays p, m, v (torch.optim.Adam, the reference's settings: gaussian_model.py:203)."""
+    """In place on float32 arrays p, m, v (torch.optim.Adam, the reference's settings: gaussian_model.py:197)."""
     for x in (p, g, m, v):
         assert x.dtype == np.float32 and x.flags["C_CONTIGUOUS"]
     f = ctypes.c_double
@@ -134,7 +134,7 @@ def dist2_knn3(xyz: np.ndarray) -> np.ndarray:
 
 # ---- Gaussian PLY file (numpy restatement) -----------------------------------------------------------
 def ply_attribute_names(n_rest: int):
-    """construct_list_of_attributes, /root/reference/scene/gaussian_model.py:218-231 (f_dc 3, f_rest
+    """construct_list_of_attributes, /root/reference/scene/gaussian_model.py:218-238 (f_dc 3, f_rest
     3*(M-1) channel-major, 3 scales, 4 rotations)."""
     l = ["x", "y", "z", "nx", "ny", "nz"]
     l += [f"f_dc_{i}" for i in range(3)]
@@ -146,7 +146,7 @@ def ply_attribute_names(n_rest: int):
 
 
 def ply_bytes(xyz, f_dc, f_rest, opacity, scale, rot) -> bytes:
-    """save_ply, /root/reference/scene/gaussian_model.py:233-258: f_dc [P,1,3] / f_rest [P,M-1,3] are written
+    """save_ply, /root/reference/scene/gaussian_model.py:240-259: f_dc [P,1,3] / f_rest [P,M-1,3] are written
     transposed(1,2) and flattened (channel-major), normals are zeros, all properties f4 little-endian, in
     the binary_little_endian 1.0 layout plyfile (the absent third-party writer) produces for one `vertex`
     element built from a structured array."""

@@ -5,8 +5,8 @@
 Covers the steps either side of the rasterizer:
   * utils/loss_utils.py l1_loss (:17-24), ssim (:59-108) and their autograd gradients, and the training
     loss of train.py:103-104;
-  * the reference's own optimizer: GaussianModel.training_setup (scene/gaussian_model.py:172-208) builds
-    torch.optim.Adam over the six parameter groups, update_learning_rate (:210-216) + optimizer.step()
+  * the reference's own optimizer: GaussianModel.training_setup (scene/gaussian_model.py:176-205) builds
+    torch.optim.Adam over the six parameter groups, update_learning_rate (:207-214) + optimizer.step()
     (train.py:137-141) are driven for a few iterations.  `plyfile` and `simple_knn` (absent from this image)
     are stubbed for the import only and "cuda" is mapped to "cpu" in torch.zeros; no arithmetic is touched.
 
@@ -32,7 +32,10 @@ def _zeros_cpu(*a, **k):
 
 
 def loss_cases(out):
-    from utils.loss_utils import l1_loss, ssim
+    from utils.loss_utils import l1_loss, ssim, gaussian, create_window
+    for ws in (1, 3, 5, 7, 9, 11):
+        out[f"window_taps_{ws}"] = gaussian(ws, 1.5).numpy()               # loss_utils.py:35-45
+    out["window_2d_11"] = create_window(11, 3).numpy()                      # :46-57, [3,1,11,11]
     g = torch.Generator().manual_seed(4321)
     cases = {"chw": ((3, 37, 53), 11), "tiny": ((3, 7, 9), 11), "batch": ((2, 3, 24, 40), 11), "win7": ((3, 20, 31), 7),
              "wide": ((1, 33, 150), 11)}
@@ -112,7 +115,7 @@ def adam_case(out):
             gm.optimizer.zero_grad(set_to_none=True)
             for n, p in params.items():
                 out[f"adam_param_{n}_{k}"] = p.detach().numpy().copy()
-        # activations: GaussianModel.get_scaling / get_rotation / get_opacity (gaussian_model.py:104-130) + autograd
+        # activations: GaussianModel.get_scaling / get_rotation / get_opacity (gaussian_model.py:106-127) + autograd
         ga = torch.Generator().manual_seed(7)
         Pa = 37
         gm2 = GaussianModel(3)

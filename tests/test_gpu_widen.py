@@ -146,14 +146,14 @@ def _adam_groups(dev):
 def test_adam_matches_reference_optimizer_and_oracle():
     import gaussian_training as gtr
     params, groups = _adam_groups(DEV)
-    opt = gtr.FusedAdam(groups, lr=0.0, eps=1e-15)                                # gaussian_model.py:203
+    opt = gtr.FusedAdam(groups, lr=0.0, eps=1e-15)                                # gaussian_model.py:197
     iters, lrs = G["adam_iters"], G["adam_lrs"]
     sched = gtr.expon_lr(0.00016 * 2.5, 0.0000016 * 2.5, lr_delay_mult=0.01, max_steps=30000)
     orc = {n: (G[f"adam_init_{n}"].copy(), np.zeros_like(G[f"adam_init_{n}"]), np.zeros_like(G[f"adam_init_{n}"])) for n in ADAM_NAMES}
     mism = 0
     for k, it in enumerate(iters):
         for gi, grp in enumerate(opt.param_groups):
-            grp["lr"] = sched(int(it)) if grp["name"] == "xyz" else float(lrs[k, gi])   # update_learning_rate, :210-216
+            grp["lr"] = sched(int(it)) if grp["name"] == "xyz" else float(lrs[k, gi])   # update_learning_rate, :207-214
         assert abs(opt.param_groups[0]["lr"] - lrs[k, 0]) <= 1e-12 * lrs[k, 0]
         for n in ADAM_NAMES:
             params[n].grad = torch.from_numpy(G[f"adam_grad_{n}_{k}"]).to(DEV)

@@ -36,7 +36,7 @@ def test_ply_round_trip_and_bytes(tmp_path, P, K):
 
 
 def test_ply_reader_finds_properties_by_name(tmp_path):
-    """load_ply reads by property name (scene/gaussian_model.py:270-306): shuffled columns, an extra uchar
+    """load_ply reads by property name (scene/gaussian_model.py:269-306): shuffled columns, an extra uchar
     property and a trailing empty element must not matter."""
     import gaussian_training as gtr
     P, K = 33, 15

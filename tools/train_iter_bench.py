@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """One full training iteration around the operator, the way /root/reference/train.py:86-141 runs it
-(activations of gaussian_model.py:104-130, render() of gaussian_renderer/__init__.py:20-112, loss,
+(activations of gaussian_model.py:106-127, render() of gaussian_renderer/__init__.py:20-112, loss,
 backward, densification statistics, optimizer step), at BASELINE configs[1] size on one GPU, in two arms:
 
   fused : gaussian_training.activate + training_loss + b200splat_densify_stats + FusedAdam, SH coefficients
@@ -44,7 +44,7 @@ def torch_ssim(img1, img2, w2):
 
 
 class Model:
-    """Raw parameters + activations as GaussianModel keeps them (scene/gaussian_model.py:36-50,104-130)."""
+    """Raw parameters + activations as GaussianModel keeps them (scene/gaussian_model.py:36-50,106-127)."""
 
     def __init__(self, sc, dev, fused):
         P = sc.means3D.shape[0]
