@@ -14,26 +14,32 @@ of gaussian_model.py:187-188), so the torch.cat of get_features (:119-122) and i
 from __future__ import annotations
 
 import ctypes
+import math
 
-import numpy as np
 import torch
 
 from . import _lib
 
 
 def expon_lr(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):
-    """The position learning-rate schedule (get_expon_lr_func, /root/reference/utils/general_utils.py:30-69):
-    log-linear interpolation from lr_init to lr_final over max_steps, optional sine-eased warm-up."""
-    def helper(step):
-        if step < 0 or (lr_init == 0.0 and lr_final == 0.0):
+    """The position learning-rate schedule the reference builds at scene/gaussian_model.py:200-205 with
+    get_expon_lr_func (utils/general_utils.py:30-69): geometric interpolation lr_init -> lr_final over max_steps
+    (lr_init^(1-t) * lr_final^t), times an optional sine-eased warm-up factor that rises from lr_delay_mult to 1
+    over lr_delay_steps.  Returns step -> learning rate (a Python float)."""
+    disabled = (lr_init == 0.0 and lr_final == 0.0)
+    log_a, log_b = (0.0, 0.0) if disabled else (math.log(lr_init), math.log(lr_final))
+
+    def schedule(step):
+        if disabled or step < 0:
             return 0.0
+        t = min(max(step / max_steps, 0.0), 1.0)
+        lr = math.exp(log_a * (1.0 - t) + log_b * t)
         if lr_delay_steps > 0:
-            delay_rate = lr_delay_mult + (1 - lr_delay_mult) * np.sin(0.5 * np.pi * np.clip(step / lr_delay_steps, 0, 1))
-        else:
-            delay_rate = 1.0
-        t = np.clip(step / max_steps, 0, 1)
-        return delay_rate * np.exp(np.log(lr_init) * (1 - t) + np.log(lr_final) * t)
-    return helper
+            ramp = min(max(step / lr_delay_steps, 0.0), 1.0)
+            lr *= lr_delay_mult + (1.0 - lr_delay_mult) * math.sin(0.5 * math.pi * ramp)
+        return lr
+
+    return schedule
 
 
 class FusedAdam(torch.optim.Adam):
