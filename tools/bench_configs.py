@@ -13,10 +13,12 @@ import diff_gaussian_rasterization as dgr
 C = dgr._C
 dev = torch.device("cuda:0")
 which = sys.argv[1] if len(sys.argv) > 1 else "all"
+SIZES = tuple(int(x) for x in sys.argv[2].split(",")) if len(sys.argv) > 2 else (
+    100_000, 200_000, 500_000, 1_000_000, 2_000_000, 3_000_000, 4_000_000, 6_000_000)
 
 def sweep():
     W, H, D = 1600, 1060, 3
-    for P in (100_000, 200_000, 500_000, 1_000_000, 2_000_000, 3_000_000, 4_000_000, 6_000_000):
+    for P in SIZES:
         sc = synth.make_scene(P, D, seed=0).to(dev)
         cam = synth.make_camera(W, H).to(dev)
         dL = synth.make_grad_image(W, H).to(dev)

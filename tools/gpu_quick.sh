@@ -1,5 +1,4 @@
 #!/bin/bash
-# short GPU session: widened-row parity tests and their benches
-mkdir -p gpurun_out; rm -f gpurun_out/widen_observed.jsonl
-timeout 240 python -m pytest tests/test_gpu_widen.py -q -m gpu -p no:cacheprovider > gpurun_out/widen_tests.log 2>&1; echo "exit $?" >> gpurun_out/widen_tests.log; tail -5 gpurun_out/widen_tests.log
-timeout 150 python tools/bench_next.py > gpurun_out/bench_next.log 2>&1; echo "exit $?" >> gpurun_out/bench_next.log; head -c 900 gpurun_out/bench_next.log
+# two more points of BASELINE configs[2] (densification sweep) with the final build
+mkdir -p gpurun_out
+timeout 24 python tools/bench_configs.py sweep 1000000,6000000 > gpurun_out/config3_more_final.jsonl 2> gpurun_out/config3_final.err; echo "sweep exit $?"; cat gpurun_out/config3_more_final.jsonl | cut -c1-400
