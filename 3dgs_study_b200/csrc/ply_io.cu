@@ -3,8 +3,9 @@
 // only; compiled with the library so the format lives next to the kernels that consume it.
 //
 // File: "ply / format binary_little_endian 1.0 / element vertex P / property float <name> ... / end_header",
-// then P rows of little-endian fp32 in header order.  Rows are (de)interleaved by worker threads over
-// contiguous row ranges; the SH coefficients change layout between memory ([P, K, 3]) and file (channel-major).
+// then P rows of little-endian fp32 in header order.  Every worker thread (de)interleaves its own contiguous range
+// of rows through a small staging buffer and writes / reads it at its own file offset (pwrite / pread); the SH coefficients change layout between memory ([P, K, 3]) and file (channel-major).
+#include <atomic>
 #include <cerrno>
 #include <cstdio>
 #include <cstring>
@@ -12,6 +13,10 @@
 #include <string>
 #include <thread>
 #include <vector>
+
+#include <fcntl.h>
+#include <sys/types.h>
+#include <unistd.h>
 
 #include "../../include/b200splat_next.h"
 #include "splat_internal.cuh"
@@ -93,20 +98,45 @@ int count_rest(const Header& h) {
     return n;
 }
 
-void parallel_rows(int64_t P, const std::function<void(int64_t, int64_t)>& fn) {
+// Rows [0, P) split into one contiguous range per worker thread; fn(lo, hi) returns false on an I/O error.
+bool parallel_ranges(int64_t P, const std::function<bool(int64_t, int64_t)>& fn) {
     unsigned hw = std::thread::hardware_concurrency();
     int64_t nt = hw ? (int64_t)hw : 4;
-    if (nt > 32) nt = 32;
-    if (P < 65536 || nt < 2) { fn(0, P); return; }
+    if (nt > 16) nt = 16;
+    if (P < 65536 || nt < 2) return fn(0, P);
     std::vector<std::thread> th;
+    std::atomic<bool> ok{true};
     int64_t per = (P + nt - 1) / nt;
     for (int64_t t = 0; t < nt; ++t) {
         int64_t lo = t * per, hi = lo + per < P ? lo + per : P;
         if (lo >= hi) break;
-        th.emplace_back(fn, lo, hi);
+        th.emplace_back([&fn, &ok, lo, hi] { if (!fn(lo, hi)) ok = false; });
     }
     for (auto& t : th) t.join();
+    return ok;
 }
+
+bool pwrite_all(int fd, const void* buf, size_t n, off_t off) {
+    const char* p = (const char*)buf;
+    while (n > 0) {
+        ssize_t w = pwrite(fd, p, n, off);
+        if (w <= 0) { if (w < 0 && errno == EINTR) continue; return false; }
+        p += w; n -= (size_t)w; off += w;
+    }
+    return true;
+}
+
+bool pread_all(int fd, void* buf, size_t n, off_t off) {
+    char* p = (char*)buf;
+    while (n > 0) {
+        ssize_t r = pread(fd, p, n, off);
+        if (r <= 0) { if (r < 0 && errno == EINTR) continue; return false; }
+        p += r; n -= (size_t)r; off += r;
+    }
+    return true;
+}
+
+constexpr int64_t SUB_ROWS = 8192;   // rows per thread-local staging buffer (2 MB at SH3)
 
 }  // namespace
 
@@ -128,15 +158,17 @@ int b200splat_ply_write(const char* path, int64_t P, int32_t n_rest, const float
     for (int i = 0; i < 4; ++i) hdr += "property float rot_" + std::to_string(i) + "\n";
     hdr += "end_header\n";
 
-    FILE* f = fopen(path, "wb");
-    if (!f) return report_error(B200SPLAT_ERR_INVALID_ARG, (std::string("ply_write: cannot open ") + path + ": " + strerror(errno)).c_str());
-    bool ok = fwrite(hdr.data(), 1, hdr.size(), f) == hdr.size();
-    const int64_t CH = 1 << 16;               // rows per chunk
-    std::vector<float> buf((size_t)CH * cols);
-    for (int64_t r0 = 0; ok && r0 < P; r0 += CH) {
-        int64_t n = P - r0 < CH ? P - r0 : CH;
-        parallel_rows(n, [&](int64_t lo, int64_t hi) {
-            for (int64_t j = lo; j < hi; ++j) {
+    int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) return report_error(B200SPLAT_ERR_INVALID_ARG, (std::string("ply_write: cannot open ") + path + ": " + strerror(errno)).c_str());
+    bool ok = pwrite_all(fd, hdr.data(), hdr.size(), 0);
+    const off_t data0 = (off_t)hdr.size();
+    const size_t row_bytes = sizeof(float) * (size_t)cols;
+    // every worker interleaves its own contiguous range of rows and writes it at its own file offset
+    ok = ok && parallel_ranges(P, [&](int64_t lo, int64_t hi) {
+        std::vector<float> buf((size_t)SUB_ROWS * cols);
+        for (int64_t r0 = lo; r0 < hi; r0 += SUB_ROWS) {
+            int64_t n = hi - r0 < SUB_ROWS ? hi - r0 : SUB_ROWS;
+            for (int64_t j = 0; j < n; ++j) {
                 int64_t i = r0 + j;
                 float* o = buf.data() + (size_t)j * cols;
                 o[0] = xyz[3 * i]; o[1] = xyz[3 * i + 1]; o[2] = xyz[3 * i + 2];
@@ -150,10 +182,11 @@ int b200splat_ply_write(const char* path, int64_t P, int32_t n_rest, const float
                 t[1] = scale[3 * i]; t[2] = scale[3 * i + 1]; t[3] = scale[3 * i + 2];
                 t[4] = rot[4 * i]; t[5] = rot[4 * i + 1]; t[6] = rot[4 * i + 2]; t[7] = rot[4 * i + 3];
             }
-        });
-        ok = fwrite(buf.data(), sizeof(float) * cols, (size_t)n, f) == (size_t)n;
-    }
-    ok = (fclose(f) == 0) && ok;
+            if (!pwrite_all(fd, buf.data(), row_bytes * (size_t)n, data0 + (off_t)(row_bytes * (size_t)r0))) return false;
+        }
+        return true;
+    });
+    ok = (close(fd) == 0) && ok;
     if (!ok) return report_error(B200SPLAT_ERR_INVALID_ARG, (std::string("ply_write: write failed: ") + path).c_str());
     return B200SPLAT_OK;
 }
@@ -206,17 +239,19 @@ int b200splat_ply_read(const char* path, int64_t P, int32_t n_rest, float* xyz, 
         }
         off.push_back(o);
     }
-    const int64_t CH = 1 << 16;
-    std::vector<unsigned char> buf((size_t)CH * h.row_bytes);
-    bool ok = fseek(f, h.data_start, SEEK_SET) == 0;
-    for (int64_t r0 = 0; ok && r0 < P; r0 += CH) {
-        int64_t n = P - r0 < CH ? P - r0 : CH;
-        ok = fread(buf.data(), (size_t)h.row_bytes, (size_t)n, f) == (size_t)n;
-        if (!ok) break;
-        parallel_rows(n, [&](int64_t lo, int64_t hi) {
-            for (int64_t j = lo; j < hi; ++j) {
+    fclose(f);
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) return report_error(B200SPLAT_ERR_INVALID_ARG, (std::string("ply_read: cannot open ") + path + ": " + strerror(errno)).c_str());
+    const size_t row_bytes = (size_t)h.row_bytes;
+    const off_t data0 = (off_t)h.data_start;
+    bool ok = parallel_ranges(P, [&](int64_t lo, int64_t hi) {
+        std::vector<unsigned char> buf((size_t)SUB_ROWS * row_bytes);
+        for (int64_t r0 = lo; r0 < hi; r0 += SUB_ROWS) {
+            int64_t n = hi - r0 < SUB_ROWS ? hi - r0 : SUB_ROWS;
+            if (!pread_all(fd, buf.data(), row_bytes * (size_t)n, data0 + (off_t)(row_bytes * (size_t)r0))) return false;
+            for (int64_t j = 0; j < n; ++j) {
                 int64_t i = r0 + j;
-                const unsigned char* row = buf.data() + (size_t)j * h.row_bytes;
+                const unsigned char* row = buf.data() + (size_t)j * row_bytes;
                 auto get = [&](int idx) { float v; memcpy(&v, row + off[idx], 4); return v; };
                 xyz[3 * i] = get(0); xyz[3 * i + 1] = get(1); xyz[3 * i + 2] = get(2);
                 f_dc[3 * i] = get(3); f_dc[3 * i + 1] = get(4); f_dc[3 * i + 2] = get(5);
@@ -228,9 +263,10 @@ int b200splat_ply_read(const char* path, int64_t P, int32_t n_rest, float* xyz, 
                 scale[3 * i] = get(b + 1); scale[3 * i + 1] = get(b + 2); scale[3 * i + 2] = get(b + 3);
                 rot[4 * i] = get(b + 4); rot[4 * i + 1] = get(b + 5); rot[4 * i + 2] = get(b + 6); rot[4 * i + 3] = get(b + 7);
             }
-        });
-    }
-    fclose(f);
+        }
+        return true;
+    });
+    close(fd);
     if (!ok) return report_error(B200SPLAT_ERR_INVALID_ARG, "ply_read: file shorter than its header says");
     return B200SPLAT_OK;
 }
