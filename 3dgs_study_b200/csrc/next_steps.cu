@@ -1,13 +1,15 @@
 // next_steps.cu -- the steps either side of the rasterizer (include/b200splat_next.h): fused L1 + SSIM loss
-// forward / backward, one-launch Adam over all parameter groups, exact 3-nearest-neighbour mean squared
-// distance.  sm_100a; all of it HBM / shared-memory bound elementwise and stencil work.
+// forward / backward (and the training loss built on it), activations of the raw parameters, one-launch Adam over
+// all parameter groups, exact 3-nearest-neighbour mean squared distance.  sm_100a; all of it HBM / shared-memory
+// bound elementwise and stencil work.
 //
 // L1 + SSIM.  A block owns a 32x32 output tile of one plane: the two input tiles with a 5-pixel halo are staged
 // in shared memory once (zero outside the image = the zero padding of F.conv2d), the five products are filtered
 // along x into shared memory, then along y in registers (each thread produces a 4-row column strip from 14
 // staged values per quantity), and the SSIM map, its three partial derivatives and the block's sums leave the
 // SM once.  Algorithmic HBM bytes per pixel and plane: forward 8 in + 12 out, backward 20 in + 4 out.
-// The sums are reduced deterministically: per-block partials, then one block per plane in double.
+// The sums are reduced deterministically: per-block partials, then one block (per plane) in double.
+// Measured and profiled: DESIGN.md section 7.
 #include <cfloat>
 #include <cmath>
 #include <cub/cub.cuh>
