@@ -388,17 +388,17 @@ int b200splat_densify_stats(int32_t P, const float* dL_dmeans2D, const int32_t* 
 }
 
 int b200splat_render_stats(int32_t P, int32_t width, int32_t height, int32_t num_rendered, const void* geom,
-                           const void* binning, const void* image, uint64_t* out14, void* stream_) {
-    if (!out14 || P < 0 || width <= 0 || height <= 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad arguments");
+                           const void* binning, const void* image, uint64_t* out16, void* stream_) {
+    if (!out16 || P < 0 || width <= 0 || height <= 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad arguments");
     if (P == 0 || num_rendered <= 0) {
-        CU(cudaMemsetAsync(out14, 0, 14 * sizeof(uint64_t), (cudaStream_t)stream_), "clear stats");
+        CU(cudaMemsetAsync(out16, 0, 16 * sizeof(uint64_t), (cudaStream_t)stream_), "clear stats");
         return B200SPLAT_OK;
     }
     if (!geom || !binning || !image) return fail(B200SPLAT_ERR_INVALID_ARG, "null forward state");
     GeomView gv = carve_geom(const_cast<void*>(geom), P);
     BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, tiles_of(width, height));
     ImgView iv = carve_image(const_cast<void*>(image), width, height);
-    CU(launch_render_stats(width, height, gv, bv.vals_sorted, iv, reinterpret_cast<unsigned long long*>(out14), (cudaStream_t)stream_),
+    CU(launch_render_stats(width, height, gv, bv.vals_sorted, iv, reinterpret_cast<unsigned long long*>(out16), (cudaStream_t)stream_),
        "render stats");
     return B200SPLAT_OK;
 }

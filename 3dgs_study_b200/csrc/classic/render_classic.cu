@@ -162,8 +162,8 @@ cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32
     return cudaGetLastError();
 }
 
-cudaError_t launch_render_stats(int, int, GeomView, const uint32_t*, ImgView, unsigned long long* out14, cudaStream_t s) {
-    return cudaMemsetAsync(out14, 0, 14 * sizeof(unsigned long long), s);
+cudaError_t launch_render_stats(int, int, GeomView, const uint32_t*, ImgView, unsigned long long* out16, cudaStream_t s) {
+    return cudaMemsetAsync(out16, 0, 16 * sizeof(unsigned long long), s);
 }
 
 }  // namespace b200splat

@@ -218,8 +218,15 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_FWD) preprocess_fwd_kern
                     thr = -logf(255.0f * o) - THR_MARGIN;
                     const float tau2 = -2.0f * thr;
                     if (tau2 > 0.0f) {
-                        ex = sqrtf(tau2 * a) * 1.001f + 0.01f;
-                        ey = sqrtf(tau2 * c) * 1.001f + 0.01f;
+                        // extents of {A dx^2 + 2 B dx dy + C dy^2 <= tau2} for the STORED conic (the one the render
+                        // kernels evaluate), not for the covariance it was rounded from: max |dx| = sqrt(tau2 C / D),
+                        // max |dy| = sqrt(tau2 A / D), D = A C - B^2 in double (fp32 products are exact in double, so
+                        // a nearly degenerate conic loses nothing to cancellation).  D <= 0: unbounded, box = everything.
+                        const double dd = (double)conA * (double)conC - (double)conB * (double)conB;
+                        if (dd > 0.0) {
+                            ex = (float)sqrt((double)tau2 * (double)conC / dd) * 1.001f + 0.01f;
+                            ey = (float)sqrt((double)tau2 * (double)conA / dd) * 1.001f + 0.01f;
+                        } else { ex = 3.0e38f; ey = 3.0e38f; }
                     } else { ex = -1.0f; ey = -1.0f; }
                 } else { thr = __int_as_float(0x7f800000); ex = -1.0f; ey = -1.0f; }
                 rc = make_uint2((uint32_t)minx | ((uint32_t)miny << 16), (uint32_t)(maxx - minx) | ((uint32_t)(maxy - miny) << 16));

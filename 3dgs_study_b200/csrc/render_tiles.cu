@@ -550,12 +550,14 @@ __global__ void __launch_bounds__(NW * 32, BWD_MINB) render_bwd_kernel(
 //   out[11]    of those, power inside [thr, 0] (an exp is executed)
 //   out[12]    of those, alpha >= 1/255 (a blend / a gradient contribution)
 //   out[13]    (strip, Gaussian) pairs with at least one contribution (one reduction + nine red.global)
+//   out[14]    of the out[11] evaluations, those where the backward's alpha test (ex2.approx of power * log2 e, as
+//              render_bwd_kernel computes it) decides differently from the forward's (expf): a count, not a gate
 __global__ void __launch_bounds__(256) render_stats_kernel(const int2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                                                            const float4* __restrict__ rec, int W, int H, int gx,
                                                            const uint32_t* __restrict__ n_contrib,
                                                            unsigned long long* __restrict__ out) {
     __shared__ int s_max;
-    __shared__ unsigned long long s_cnt[14];
+    __shared__ unsigned long long s_cnt[16];
     __shared__ int s_strip[4];
     const int tile = blockIdx.x, t = threadIdx.x;
     const int ox = (tile % gx) * TILE, oy = (tile / gx) * TILE;
@@ -563,14 +565,14 @@ __global__ void __launch_bounds__(256) render_stats_kernel(const int2* __restric
     const bool inside = px < W && py < H;
     const int last = inside ? (int)n_contrib[(size_t)py * W + px] : 0;
     if (t == 0) s_max = 0;
-    if (t < 14) s_cnt[t] = 0ull;
+    if (t < 16) s_cnt[t] = 0ull;
     __syncthreads();
     atomicMax(&s_max, last);
     __syncthreads();
     const int2 range = ranges[tile];
     const int n = min(range.y - range.x, s_max);
     const int strip = t >> 6;                     // rows 4*strip .. 4*strip+3
-    unsigned long long ev = 0, ex = 0, co = 0;
+    unsigned long long ev = 0, ex = 0, co = 0, dis = 0;
     for (int j = 0; j < n; j++) {
         const uint32_t id = point_list[range.x + j];
         const float4 a = rec[3 * (size_t)id], b = rec[3 * (size_t)id + 1], c = rec[3 * (size_t)id + 2];
@@ -584,7 +586,10 @@ __global__ void __launch_bounds__(256) render_stats_kernel(const int2* __restric
             const float power = cfma(dx, cfma(b.x, dx, -cmul(b.y, dy)), cmul(cmul(b.z, dy), dy));
             if (power <= 0.0f && power >= b.w) {
                 ex++;
-                if (fminf(ALPHA_MAX, cmul(c.x, expf(power))) >= ALPHA_MIN) { co++; contrib = true; }
+                const bool fwd_valid = fminf(ALPHA_MAX, cmul(c.x, expf(power))) >= ALPHA_MIN;
+                const bool bwd_valid = -c.x * fast_ex2(power * 1.4426950408889634f) <= -ALPHA_MIN;
+                if (fwd_valid) { co++; contrib = true; }
+                if (fwd_valid != bwd_valid) dis++;
             }
         }
         if (contrib) s_strip[strip] = 1;
@@ -592,9 +597,9 @@ __global__ void __launch_bounds__(256) render_stats_kernel(const int2* __restric
         if (t == 0) { s_cnt[__popc(m)]++; s_cnt[9]++; s_cnt[13] += s_strip[0] + s_strip[1] + s_strip[2] + s_strip[3]; }
         __syncthreads();
     }
-    atomicAdd(&s_cnt[10], ev); atomicAdd(&s_cnt[11], ex); atomicAdd(&s_cnt[12], co);
+    atomicAdd(&s_cnt[10], ev); atomicAdd(&s_cnt[11], ex); atomicAdd(&s_cnt[12], co); atomicAdd(&s_cnt[14], dis);
     __syncthreads();
-    if (t < 14 && s_cnt[t]) atomicAdd(out + t, s_cnt[t]);
+    if (t < 16 && s_cnt[t]) atomicAdd(out + t, s_cnt[t]);
 }
 
 }  // namespace
@@ -630,12 +635,12 @@ cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32
 }
 
 cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
-                                unsigned long long* out14, cudaStream_t s) {
+                                unsigned long long* out16, cudaStream_t s) {
     const int gx = (W + TILE - 1) / TILE;
     const int T = tiles_of(W, H);
-    cudaError_t e = cudaMemsetAsync(out14, 0, 14 * sizeof(unsigned long long), s);
+    cudaError_t e = cudaMemsetAsync(out16, 0, 16 * sizeof(unsigned long long), s);
     if (e != cudaSuccess || T == 0) return e;
-    render_stats_kernel<<<T, 256, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, gx, iv.n_contrib, out14);
+    render_stats_kernel<<<T, 256, 0, s>>>(iv.ranges, vals_sorted, gv.rec, W, H, gx, iv.n_contrib, out16);
     return cudaGetLastError();
 }
 

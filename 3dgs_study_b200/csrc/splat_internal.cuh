@@ -99,7 +99,7 @@ cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, 
                                      const unsigned* const* counts, const float* campos, float* dL_dsh, float* dL_dgeom,
                                      int store, cudaStream_t s);
 cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
-                                unsigned long long* out14, cudaStream_t s);
+                                unsigned long long* out16, cudaStream_t s);
 cudaError_t launch_masked_colour_grad(int P, const int32_t* radii, GeomView gv, const float* acc, float* dcol, cudaStream_t s);
 cudaError_t launch_sh_grad_from_views(int P, int M, int D, const float* means3D, int n_views, const float* const* dcol,
                                       const float* campos, float* dL_dsh, cudaStream_t s);

@@ -493,14 +493,14 @@ def densify_stats(dL_dmeans2D, radii, xyz_gradient_accum, denom, max_radii2D):
 def render_stats(P, W, H, num_rendered, geomBuffer, binningBuffer, imageBuffer):
     """Inspection: workload counters of the render stage (see b200splat_render_stats in the header)."""
     dev = geomBuffer.device
-    out = torch.zeros(14, dtype=torch.int64, device=dev)
+    out = torch.zeros(16, dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
         rc = lib().b200splat_render_stats(int(P), int(W), int(H), int(num_rendered), _ptr(geomBuffer), _ptr(binningBuffer),
                                           _ptr(imageBuffer), _ptr(out), _stream_ptr(dev))
     _check(rc, "render_stats")
     v = [int(x) for x in out.cpu().tolist()]
     return {"pairs_by_subblocks": v[0:9], "pairs_visited": v[9], "pixel_evals": v[10], "exp_evals": v[11],
-            "contributions": v[12], "pairs_contributing": v[13]}
+            "contributions": v[12], "pairs_contributing": v[13], "alpha_test_disagreements": v[14]}
 
 
 def export_state(P, W, H, num_rendered, radii, geomBuffer, binningBuffer, imageBuffer):

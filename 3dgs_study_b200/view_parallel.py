@@ -17,7 +17,7 @@ Three exchange modes:
                 symmetric (peer-mapped) buffer; after one barrier every rank READS its peers' rows over NVLink in
                 the kernel that adds them into its dense gradients and rebuilds dL/dsh from the colour gradient and
                 the camera centre (b200splat_accumulate_packed).  No collective on the data path; the bytes on NVLink
-                follow the Gaussians a view actually touched, not P.  8 GPUs: 3650 views/s (85 % of 8x the 1-GPU rate).
+                follow the Gaussians a view actually touched, not P (measured scaling: BASELINE.md section 5).
   "allreduce"   every rank all-reduces the full 59 f32 / Gaussian (708 MB at 3 M SH3).  The plain baseline.
   "factorized"  (the NCCL flavour; default with an injected backend) the SH gradient of a view is the outer product
                 Y(dir(mean, campos_v)) (x) dcol_v, so ranks all-gather the [P,3] masked colour gradients
@@ -25,9 +25,11 @@ Three exchange modes:
                 11 f32 / Gaussian (rotation 4, mean 3, scale 3, opacity 1) as ONE flat buffer, and every rank
                 rebuilds the summed dL/dsh locally with b200splat_sh_grad_from_views while the all-reduce is
                 still in flight.  Same result (up to fp32 summation order), 3.4x fewer bytes on NVLink at 8 GPUs.
-                The densification statistics are accumulated locally and reduced on demand
-                (`reduce_densification_stats`), which is when the reference consumes them (every 100 iterations,
-                /root/reference/train.py:130-133); sums and maxima commute, so the values are identical.
+
+In EVERY mode the densification statistics are rank-local accumulators that `step()` adds to and never clears;
+`reduce_densification_stats()` returns their sum / max over the ranks when the caller is about to consume them
+(the reference does so every 100 iterations, /root/reference/train.py:130-133) and
+`reset_densification_stats()` clears them afterwards, as the reference's densification_postfix does.
 
 Works with any torch.distributed backend (NCCL on the GPU box, gloo in the CPU tests -- the reduction
 logic is backend-agnostic and is tested with world_size 2 on CPU with a stand-in rasterize function).
@@ -79,7 +81,12 @@ class _CudaBackend:
         return color, radii, g[0]
 
     def sh_grad_from_views(self, means3D, dcols, campos, M, degree):
-        return self.C.sh_grad_from_views(means3D, dcols, campos, M, degree)
+        # the C ABI takes at most B200SPLAT_MAX_VIEWS (16) views per launch: more (8 ranks x 3 views) go in groups
+        out = None
+        for lo in range(0, len(dcols), 16):
+            part = self.C.sh_grad_from_views(means3D, dcols[lo:lo + 16], campos[lo:lo + 16].contiguous(), M, degree)
+            out = part if out is None else out.add_(part)
+        return out
 
     def view_fwd_bwd_packed(self, cam, dL, lv, rows_ptr, count_ptr, dmeans2D, on_forward=None):
         """Forward + backward of one view; the gradients leave as packed rows (sparse exchange)."""
@@ -128,7 +135,6 @@ class ViewParallelStep:
         if exchange not in ("allreduce", "factorized", "packed"):
             raise ValueError("exchange must be 'allreduce', 'factorized' or 'packed'")
         self.exchange = exchange
-        self.stats_reduced = True
         self.last_radii = None
         self._side = None                    # side streams of the factorized / packed exchange
         self._packed = None                  # symmetric buffers of the packed exchange
@@ -187,7 +193,6 @@ class ViewParallelStep:
             return self._step_packed(cams, dL_images, reduce, on_forward)
         for t in self.leaves:
             t.grad = None
-        self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         color = None
         for cam, dL in zip(cams, dL_images):
             means2D = torch.zeros_like(self.leaves.means3D, requires_grad=True)
@@ -231,7 +236,6 @@ class ViewParallelStep:
         dev = lv.means3D.device
         G = self.world_size if reduce else 1
         nv = len(cams)
-        self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         main = torch.cuda.current_stream(dev)
         if self._side is None:
             self._side = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
@@ -266,7 +270,6 @@ class ViewParallelStep:
             color, radii = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, on_forward)
             self._accumulate_stats(dmeans2D, radii)
             self.last_radii = radii
-        self.stats_reduced = self.world_size == 1
         main.wait_event(cleared)
         # this rank's own rows go in first, before the barrier (i.e. while the slower peers are still rendering):
         # the first view is WRITTEN into the freshly cleared gradients (plain stores), further local views are added
@@ -340,7 +343,6 @@ class ViewParallelStep:
         cuda = dev.type == "cuda"
         G = self.world_size
         exchange = reduce and G > 1
-        self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
         nv = len(cams)
         sy = self._setup_symm(P, nv, dev) if exchange else None
         if sy:
@@ -431,7 +433,6 @@ class ViewParallelStep:
                 flat_done = self._reduce_flat(flat, exchange, cuda, dev)   # before the statistics: off the critical path
             self._accumulate_stats(dmeans2D, radii)
             self.last_radii = radii
-        self.stats_reduced = G == 1
         if cuda:
             if flat_done is not None:
                 torch.cuda.current_stream(dev).wait_event(flat_done)
@@ -462,15 +463,27 @@ class ViewParallelStep:
             dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
         return None
 
+    def reset_densification_stats(self):
+        """Zero the rank-local statistics: what the reference does after it has consumed them
+        (/root/reference/scene/gaussian_model.py:391-393, densification_postfix)."""
+        self.xyz_gradient_accum.zero_(); self.denom.zero_(); self.max_radii2D.zero_()
+
     def reduce_densification_stats(self):
-        """Factorized mode keeps xyz_gradient_accum / denom / max_radii2D rank-local; call this before they are
-        consumed (densification).  Sum and max commute with accumulation over steps."""
-        if self.world_size > 1 and not self.stats_reduced:
+        """-> (xyz_gradient_accum, denom, max_radii2D) over ALL ranks' views since the last reset.
+
+        In every exchange mode the three attributes are RANK-LOCAL accumulators that `step()` only ever adds to
+        (norm per view, then summed; `denom` counts visible views; `max_radii2D` is a running maximum), exactly as
+        the reference accumulates them between densification events (/root/reference/train.py:127,130-133).  This
+        call sum- / max-reduces COPIES, so it can be made at any time and any number of times; the caller consumes
+        the returned tensors and then calls `reset_densification_stats()`.  Sums and maxima commute with the
+        accumulation over steps, so the values equal a single process that rendered all the views."""
+        out = (self.xyz_gradient_accum.clone(), self.denom.clone(), self.max_radii2D.clone())
+        if self.world_size > 1:
             import torch.distributed as dist
-            dist.all_reduce(self.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=self.group)
-            dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=self.group)
-            dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=self.group)
-        self.stats_reduced = True
+            dist.all_reduce(out[0], op=dist.ReduceOp.SUM, group=self.group)
+            dist.all_reduce(out[1], op=dist.ReduceOp.SUM, group=self.group)
+            dist.all_reduce(out[2], op=dist.ReduceOp.MAX, group=self.group)
+        return out
 
     def all_reduce_grads(self):
         import torch.distributed as dist
@@ -479,9 +492,6 @@ class ViewParallelStep:
             if t.grad is None:
                 t.grad = torch.zeros_like(t)
             works.append(dist.all_reduce(t.grad, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
-        works.append(dist.all_reduce(self.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
-        works.append(dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
-        works.append(dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=self.group, async_op=True))
         for w in works:
             w.wait()
 
@@ -516,13 +526,14 @@ class ViewParallelStep:
                                         cam.tanfovx, cam.tanfovy, cam.image_height, cam.image_width, lv.shs,
                                         self.sh_degree, cam.camera_center, False, False, stage_times=st)
             R, color, radii, geom, binning, img, _ = res
-            C.rasterize_gaussians_backward(self.bg, lv.means3D, radii, None, lv.scales, lv.rotations,
+            g = C.rasterize_gaussians_backward(self.bg, lv.means3D, radii, None, lv.scales, lv.rotations,
                                            self.scale_modifier, None, cam.world_view_transform,
                                            cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, self.sh_degree,
                                            cam.camera_center, geom, R, binning, img, False, opacities=lv.opacities,
                                            image_height=cam.image_height, image_width=cam.image_width, stage_times=st)
             if it == 0:
-                stats = {"visible": int((radii > 0).sum().item()), "R": int(R)}
+                stats = {"visible": int((radii > 0).sum().item()), "R": int(R),
+                         "touched": int((g[3].abs().sum(dim=1) > 0).sum().item())}
                 stats.update(C.render_stats(lv.means3D.shape[0], cam.image_width, cam.image_height, R, geom, binning, img))
                 continue   # first pass is warm-up
             for k, v in st.as_dict().items():

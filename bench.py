@@ -49,13 +49,19 @@ def parse_args():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--exchange", default=None, choices=["allreduce", "factorized", "packed"],
-                    help="N>1 gradient exchange (default: factorized); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
+                    help="N>1 gradient exchange (default: packed rows over NVLink peer memory); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
     ap.add_argument("--peer-memory", action="store_true", help="factorized exchange through NVLink peer mappings (fused rebuild kernel + multimem all-reduce) instead of NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train-iter", action="store_true", help="skip the full-training-iteration measurement (N=1 only)")
-    ap.add_argument("--cpu-tile-stride", type=int, default=16, help="CPU legs render 1/stride of the tiles")
     ap.add_argument("--stages", action="store_true", help="print the per-stage table to stderr")
     return ap.parse_args()
+
+
+def config_of(a):
+    """The `config` object, identical in both arms (the driver compares them key by key)."""
+    return {"workload": workload_name(a), "gaussians": a.gaussians, "sh_degree": a.sh_degree, "width": a.width, "height": a.height,
+            "views_per_rank_per_step": 1,
+            "l2": "no flush needed: the inputs of a step (0.7 GB of Gaussians + 0.2 GB of per-view keys) exceed the 126 MB L2, and every step renders a different view of the orbit"}
 
 
 def workload_name(a):
@@ -326,12 +332,11 @@ def run_ours(a):
         "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "gaussians": P, "sh_degree": D, "width": W, "height": H,
-                   "visible": stats.get("visible"), "tile_pairs_R": stats.get("R"), "views_per_rank_per_step": 1,
-                   "parallelism": f"view-parallel x{world}, Gaussians replicated" + ((", exchange=" + stepper.exchange + ({"factorized": ": NCCL all-gather of [P,3] masked colour grads + all-reduce of 11 f32/Gaussian, dL/dsh rebuilt locally",
+        "config": config_of(a),
+        "workload_detail": {"visible": stats.get("visible"), "tile_pairs_R": stats.get("R"), "touched_gaussians": stats.get("touched"),
+                            "parallelism": f"view-parallel x{world}, Gaussians replicated" + ((", exchange=" + stepper.exchange + ({"factorized": ": NCCL all-gather of [P,3] masked colour grads + all-reduce of 11 f32/Gaussian, dL/dsh rebuilt locally",
                                                                            "packed": ": one 64-byte gradient row per Gaussian a view touched, read from every peer over NVLink by the kernel that adds them into the dense gradients (no collective on the data path)"}
-                                                                          .get(stepper.exchange, ": NCCL sum-allreduce of 59 f32/Gaussian grads"))) if world > 1 else ""),
-                   "l2_note": "inputs (0.7 GB of Gaussians + 0.2 GB of keys per view) exceed the 126 MB L2; a different view every step"},
+                                                                          .get(stepper.exchange, ": NCCL sum-allreduce of 59 f32/Gaussian grads"))) if world > 1 else "")},
         "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": round(ms_e2e / a.steps, 4),
                 "note": "Gaussians are model state resident in HBM (as in the reference); camera + upstream image gradient from pinned host, image + grad checksum to host, every step; the host reads step i's results after queueing step i+1"},
@@ -344,75 +349,139 @@ def run_ours(a):
     return line
 
 
+def csrc_sha16():
+    """Hash of the kernel sources the loaded library was built from: ncu-derived constants in profiles/ are only
+    attached to the bench line when they were captured on the same sources."""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "3dgs_study_b200", "csrc", "*.cu")) + glob.glob(os.path.join(ROOT, "3dgs_study_b200", "csrc", "*.cuh"))):
+        with open(f, "rb") as fh:
+            h.update(os.path.basename(f).encode() + b"\0" + fh.read())
+    return h.hexdigest()[:16]
+
+
+def fp32_peaks(peaks):
+    """FP32 / MUFU / atomic denominators: measured by tools/peaks.cu on a B200 of this pool (profiles/r02_peaks.json);
+    else the nominal figure 148 SMs x 128 lanes x 2 flop x SM clock."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_peaks.json")) as f:
+            pk = json.load(f)
+        return {"fp32_tflops": max(pk["ffma_tflops"], pk["ffma2_tflops"]), "ffma_tflops": pk["ffma_tflops"], "ffma2_tflops": pk["ffma2_tflops"],
+                "mufu_ex2_gops": pk["mufu_ex2_gops"], "red_f32_l2_gops": pk["red_f32_l2"]["g_f32_adds_s"], "source": "measured (tools/peaks.cu, profiles/r02_peaks.json)"}
+    except Exception:
+        mhz = peaks.get("sm_max_mhz", 1965.0) or 1965.0
+        return {"fp32_tflops": round(148 * 128 * 2 * mhz * 1e6 / 1e12, 1), "source": "nominal 148 x 128 x 2 x SM clock (no measured figure found)"}
+
+
 def roofline_from_stages(stages, stats, P, M, W, H):
-    """Dominant kernel vs the measured HBM peak.  Algorithmic bytes per launch = the arrays a stage must read and
-    write once (DESIGN.md section 2 lists them per kernel); V visible Gaussians, R (tile, Gaussian) pairs, Rv pairs
-    the render kernels actually visit (below each tile's deepest contributor), T tiles, N pixels."""
+    """Every stage against the roofline that binds it.
+
+    HBM-bound stages (preprocess fwd/bwd, depth order, emit, tile sort, ranges): algorithmic bytes / live stage time
+    vs the measured copy bandwidth.  Render forward / backward: FP32-issue bound -- SURVEY 8(d)'s flop counts
+    (fwd 12 E + 8 C, bwd 25 E' + 45 C; E pixel evaluations, C blends, both counted on this view by
+    b200splat_render_stats) / live stage time vs the measured FP32 FFMA rate; their HBM figure stays as a secondary
+    row.  V visible Gaussians, Nt Gaussians the backward touched, R (tile, Gaussian) pairs, Rv pairs the render
+    kernels visit, T tiles, N pixels."""
     peaks, which = measured_peaks()
+    fpk = fp32_peaks(peaks)
     V, R = stats.get("visible", 0), stats.get("R", 0)
     Rv = stats.get("pairs_visited", R)
     Rc = stats.get("pairs_contributing", 0)
+    Nt = stats.get("touched", V)
+    E, C = stats.get("pixel_evals", 0), stats.get("contributions", 0)
     T, N = ((W + 15) // 16) * ((H + 15) // 16), W * H
     kb = 2 if T <= 65536 else 4
     algo = {
-        "preprocess": 12 * P + V * (32 + 12 * M) + 20 * P + 48 * V,       # means | scale rot opacity SH | radii rect iota depth | record
-        "scan": 4 * 16 * P + 4 * P + 16 * P,                                # depth order: 4 radix passes (key+value in/out) + histogram + scan
-        "duplicate": 16 * P + (kb + 4) * R,                                 # order rect offsets | tile key + id per pair
-        "sort": kb * R + 2 * 2 * (kb + 4) * R,                              # histogram + 2 radix passes over (tile key, id)
+        "preprocess": 12 * P + V * (32 + 12 * M) + 20 * P + 48 * V,       # means | scale rot opacity SH | radii rect depth-key | record
+        "scan": stats.get("depth_sort_bytes", 4 * 16 * P + 4 * P + 16 * P),  # depth order of the visible Gaussians + scan of tiles touched
+        "duplicate": 16 * V + (kb + 4) * R,                                 # order rect offsets | tile key + id per pair
+        "sort": stats.get("tile_sort_bytes", kb * R + 2 * 2 * (kb + 4) * R),
         "ranges": kb * R + 8 * T + 4 * T,
         "render": 52 * Rv + 20 * N,                                         # id + 48-byte record per visited pair | colour, final T, n_contrib
         "render_bwd": 52 * Rv + 32 * N + 36 * Rc,                           # ... | final T, n_contrib, dL/dpixel | 9 red.f32 per contributing (strip, Gaussian)
-        "preprocess_bwd": V * (44 + 48 + 12 * M) + 4 * P + P * (52 + 12 * M),   # inputs + render sums + SH row | radii | all gradient rows
+        # per-Gaussian backward visits the TOUCHED Gaussians only: inputs + render sums + SH row in, gradient rows out;
+        # the zero-fill of the dense outputs (P rows) runs on a side stream during the render backward and is not this stage
+        "preprocess_bwd": Nt * (44 + 48 + 12 * M) + Nt * (52 + 12 * M) + 5 * P,
     }
+    flops = {"render": 12 * E + 8 * C, "render_bwd": 25 * E + 45 * C}
     rows = {}
     for k, ms in stages.items():
         if ms > 0 and k in algo:
             gbs = algo[k] / (ms * 1e-3) / 1e9
-            rows[k] = {"ms": round(ms, 4), "algo_bytes": int(algo[k]), "gbs": round(gbs, 1), "frac_hbm": round(gbs / peaks["hbm_gbs"], 4)}
+            rows[k] = {"ms": round(ms, 4), "bound": "hbm", "algo_bytes": int(algo[k]), "gbs": round(gbs, 1),
+                       "frac_hbm": round(gbs / peaks["hbm_gbs"], 4)}
+            if k in flops and flops[k] > 0:
+                tf = flops[k] / (ms * 1e-3) / 1e12
+                rows[k].update({"bound": "fp32_issue", "algo_flops": int(flops[k]), "tflops": round(tf, 2),
+                                "frac_fp32": round(tf / fpk["fp32_tflops"], 4)})
     if not rows:
         return None
     top = max(rows, key=lambda k: rows[k]["ms"])
-    out = {"kernel": top, "bound": "hbm", "achieved": rows[top]["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
-           "frac": rows[top]["frac_hbm"], "traffic": None, "peak_source": which,
-           "note": "the render kernels are FP32-issue bound, not HBM bound (DESIGN.md section 2; ncu: issue slots busy 75-83 %); "
-                   "their HBM fraction is reported because the contract asks for it, the issue-rate view is in `issue`",
-           "per_stage": rows}
-    # ncu-derived figures of the same kernels (profiles/, one --set full capture per round): DRAM traffic + issue rate
+    r = rows[top]
+    if r["bound"] == "fp32_issue":
+        out = {"kernel": top, "bound": "fp32_issue", "achieved": r["tflops"], "peak": fpk["fp32_tflops"], "unit": "TFLOP/s",
+               "frac": r["frac_fp32"], "traffic": None, "peak_source": fpk["source"],
+               "flops_per_launch": r["algo_flops"], "flops_formula": "SURVEY 8(d): fwd 12 E + 8 C, bwd 25 E' + 45 C (E, C counted on this view)",
+               "hbm": {"achieved": r["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": r["frac_hbm"], "peak_source": which,
+                       "note": "secondary: the render kernels move far less than HBM could deliver"}}
+    else:
+        out = {"kernel": top, "bound": "hbm", "achieved": r["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": r["frac_hbm"],
+               "traffic": None, "peak_source": which}
+    out["peaks"] = fpk
+    out["per_stage"] = rows
+    # ncu-derived figures (one --set full capture per build): attached only when captured on THESE kernel sources
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_ncu_kernels.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_ncu_kernels.json")) as f:
             prof = json.load(f)
         key = {"render_bwd": "render_bwd_kernel", "render": "render_fwd_kernel", "preprocess": "preprocess_fwd_kernel",
                "preprocess_bwd": "preprocess_bwd_kernel"}.get(top)
-        if key and key in prof:
+        if prof.get("csrc_sha16") != csrc_sha16():
+            out["ncu"] = {"dropped": "profiles/r02_ncu_kernels.json was captured on other kernel sources", "profile_sha": prof.get("csrc_sha16"),
+                          "build_sha": csrc_sha16()}
+        elif key and key in prof:
             out["traffic"] = prof[key]["dram_bytes"]
             out["issue"] = {"warp_inst_per_launch": prof[key]["warp_inst"], "issue_slots_busy_pct_ncu": prof[key]["issue_active_pct"],
                             "achieved_ginst_s": round(prof[key]["warp_inst"] / (rows[top]["ms"] * 1e-3) / 1e9, 1),
                             "peak_ginst_s": round(148 * 4 * (peaks.get("sm_max_mhz", 1965.0) or 1965.0) * 1e6 / 1e9, 1),
-                            "source": prof.get("source", "profiles/")}
+                            "source": prof.get("source", "profiles/r02_ncu_kernels.json")}
             out["issue"]["frac"] = round(out["issue"]["achieved_ginst_s"] / out["issue"]["peak_ginst_s"], 4)
     except Exception:
         pass
-    if stats.get("contributions"):
-        out["work"] = {"pairs_visited": Rv, "pixel_evals": stats.get("pixel_evals"), "blends": stats.get("contributions"),
-                       "strip_pairs_contributing": Rc,
-                       "gblends_per_s_fwd": round(stats["contributions"] / (rows["render"]["ms"] * 1e-3) / 1e9, 1) if "render" in rows else None,
-                       "gblends_per_s_bwd": round(stats["contributions"] / (rows["render_bwd"]["ms"] * 1e-3) / 1e9, 1) if "render_bwd" in rows else None}
+    if C:
+        out["work"] = {"pairs_visited": Rv, "pixel_evals": E, "blends": C, "lane_efficiency": round(C / max(E, 1), 4),
+                       "strip_pairs_contributing": Rc, "touched_gaussians": Nt,
+                       "alpha_test_disagreements_fwd_vs_bwd": stats.get("alpha_test_disagreements"),
+                       "gblends_per_s_fwd": round(C / (rows["render"]["ms"] * 1e-3) / 1e9, 1) if "render" in rows else None,
+                       "gblends_per_s_bwd": round(C / (rows["render_bwd"]["ms"] * 1e-3) / 1e9, 1) if "render_bwd" in rows else None}
     return out
 
 
 # -----------------------------------------------------------------------------------------------------
 # CPU legs (the only places bench.py executes oracle/): cpu_baseline of our arm and --impl reference
 # -----------------------------------------------------------------------------------------------------
+def host_threads():
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU legs set their
+    own thread count instead of inheriting that)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 class CpuOracleView:
-    """C oracle (oracle/splat_oracle.c, OpenMP over all host threads) on a BOUNDED SAMPLE of one view of the
-    same workload: all P Gaussians are preprocessed, binned and sorted and the per-Gaussian backward runs in
-    full; the tile render forward + backward runs on every `stride`-th tile and its time is scaled by
-    `stride`.  estimated full-view time = t_pre + t_bin + stride * (t_render + t_render_bwd) + t_pre_bwd."""
+    """C oracle (oracle/splat_oracle.c, OpenMP over all host threads) on one view of the same workload.  stride = 1
+    (the default for every reported number): the WHOLE view, every tile -- a measured wall time, nothing
+    extrapolated.  stride > 1 (warm-up only): the tile render forward + backward runs on every stride-th tile."""
 
     def __init__(self, a):
         from oracle import c_oracle as co
         synth = importlib.import_module("3dgs_study_b200.synth")
         self.co, self.a = co, a
+        self.cores = host_threads()
+        os.environ["OMP_NUM_THREADS"] = str(self.cores)
+        co.lib().orc_set_threads(self.cores)
+        torch.set_num_threads(self.cores)
         P, W, H, D = a.gaussians, a.width, a.height, a.sh_degree
         sc = synth.make_scene(P, D, seed=0)
         self.M = sc.shs.shape[1]
@@ -420,47 +489,40 @@ class CpuOracleView:
         self.cams = [synth.make_camera(W, H, yaw=2.0 * np.pi * k / 8) for k in range(8)]
         self.bg = np.zeros(3, np.float32)
         self.dL = synth.make_grad_image(W, H).numpy()
-        self.cores = os.cpu_count() or 1
 
-    def step(self, i):
+    def step(self, i, stride=1):
+        """-> wall seconds of one fwd+bwd view (all stages inside the timed region)."""
         co, a, A = self.co, self.a, self.arr
-        P, W, H, D, M, s = a.gaussians, a.width, a.height, a.sh_degree, self.M, max(1, a.cpu_tile_stride)
+        P, W, H, D, M, s = a.gaussians, a.width, a.height, a.sh_degree, self.M, max(1, stride)
         cam = self.cams[i % 8]
         v, p, c = cam.world_view_transform.numpy(), cam.full_proj_transform.numpy(), cam.camera_center.numpy()
         t0 = time.perf_counter()
         g = co.preprocess(P, D, M, W, H, A["means3D"], A["scales"], 1.0, A["rotations"], A["opacities"], A["shs"], None, None,
                           v, p, c, cam.tanfovx, cam.tanfovy)
-        t1 = time.perf_counter()
         b = co.bin_tiles(P, W, H, g)
-        t2 = time.perf_counter()
-        off = i % s
-        color, _, fT, nc = co.render(W, H, g, b, self.bg, tile_stride=s, tile_offset=off)
-        t3 = time.perf_counter()
-        rg = co.render_backward(P, W, H, g, b, self.bg, fT, nc, self.dL, tile_stride=s, tile_offset=off)
-        t4 = time.perf_counter()
+        color, _, fT, nc = co.render(W, H, g, b, self.bg, tile_stride=s, tile_offset=i % s)
+        rg = co.render_backward(P, W, H, g, b, self.bg, fT, nc, self.dL, tile_stride=s, tile_offset=i % s)
         co.preprocess_backward(P, D, M, W, H, A["means3D"], A["scales"], 1.0, A["rotations"], A["opacities"], A["shs"], None,
                                v, p, c, cam.tanfovx, cam.tanfovy, False, g, rg)
-        t5 = time.perf_counter()
-        est = (t1 - t0) + (t2 - t1) + s * ((t3 - t2) + (t4 - t3)) + (t5 - t4)
-        return est, t5 - t0
+        return time.perf_counter() - t0
 
-    def sample_desc(self):
+    def sample_desc(self, n):
         a = self.a
-        return (f"C oracle (OpenMP, {self.cores} threads) per step: all {a.gaussians} Gaussians preprocessed+binned+sorted and "
-                f"per-Gaussian backward in full; tile render fwd+bwd on 1/{a.cpu_tile_stride} of the tiles, that time x{a.cpu_tile_stride}")
+        return (f"C oracle port (OpenMP, {self.cores} threads), {n} whole views measured: all {a.gaussians} Gaussians preprocessed, binned, "
+                f"sorted; every tile rendered forward and backward; per-Gaussian backward -- wall time per view, nothing extrapolated")
 
 
-def cpu_baseline_quick(a, budget_s=25.0):
-    """cpu_baseline of our arm: 1 warm-up + as many sampled steps as fit in ~budget_s (at least 1)."""
+def cpu_baseline_quick(a, budget_s=20.0):
+    """cpu_baseline of our arm: 1 cheap warm-up (1/16 of the tiles) + as many WHOLE views as fit in ~budget_s (>= 2)."""
     ov = CpuOracleView(a)
-    ov.step(0)
-    ests, spent, i = [], 0.0, 1
-    while spent < budget_s and i <= 4:
-        est, wall = ov.step(i)
-        ests.append(est); spent += wall; i += 1
-    est = float(np.median(ests))
-    return {"value": round(1.0 / est, 5), "unit": UNIT, "cores": ov.cores, "kind": "port",
-            "sample": ov.sample_desc(), "est_ms_per_view": round(est * 1e3, 1)}
+    ov.step(0, stride=16)
+    walls, spent, i = [], 0.0, 1
+    while (spent < budget_s or len(walls) < 2) and i <= 8:
+        w = ov.step(i)
+        walls.append(w); spent += w; i += 1
+    w = float(np.median(walls))
+    return {"value": round(1.0 / w, 5), "unit": UNIT, "cores": ov.cores, "kind": "port",
+            "sample": ov.sample_desc(len(walls)), "ms_per_view": round(w * 1e3, 1)}
 
 
 def torch_oracle_config1():
@@ -486,24 +548,24 @@ def torch_oracle_config1():
 
 def run_reference(a):
     """--impl reference: the reference has no CPU rasterizer and its CUDA rasterizer source is absent from the
-    snapshot (unbuildable), so this arm times the oracle port on the host cores (kind "port")."""
+    snapshot (unbuildable), so this arm times the oracle port on the host cores (kind "port").  Every step is one
+    WHOLE view (all tiles): `ms_per_step` x steps is wall time actually spent.  Runs on rank 0 only and sets its own
+    thread count, so the figure does not depend on how it was launched (python or torchrun)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return None
     ov = CpuOracleView(a)
     for i in range(a.warmup):
-        ov.step(i)
-    ests = []
+        ov.step(i, stride=1 if i == a.warmup - 1 else 16)     # warm-up: cheap samples, then one whole view
+    t0 = time.perf_counter()
     for i in range(a.steps):
-        est, _ = ov.step(a.warmup + i)
-        ests.append(est)
-    ms = float(np.mean(ests)) * 1e3
+        ov.step(a.warmup + i)
+    ms = (time.perf_counter() - t0) * 1e3 / max(a.steps, 1)
     val = 1000.0 / ms
     return {"impl": "reference", "metric": METRIC, "value": round(val, 5), "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": round(ms, 2), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "gaussians": a.gaussians,
-                                                            "sh_degree": a.sh_degree, "width": a.width, "height": a.height},
-            "cpu_baseline": {"value": round(val, 5), "unit": UNIT, "cores": ov.cores, "kind": "port", "sample": ov.sample_desc()},
+            "dtype": "f32", "data": "synthetic", "config": config_of(a),
+            "cpu_baseline": {"value": round(val, 5), "unit": UNIT, "cores": ov.cores, "kind": "port", "sample": ov.sample_desc(a.steps)},
             "e2e": {"value": round(val, 5), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "reference CUDA rasterizer: unavailable on this box (submodule source absent from /root/reference)"}

@@ -248,13 +248,15 @@ B200SPLAT_API int b200splat_densify_stats(int32_t P, const float* dL_dmeans2D, c
                            float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
 
 /* Inspection: workload counters of the render stage of the view whose forward state is given, written
- * to out14 (device, 14 x u64): [0..8] (tile, Gaussian) pairs by number of 8x4-pixel sub-blocks the splat's
+ * to out16 (device, 16 x u64): [0..8] (tile, Gaussian) pairs by number of 8x4-pixel sub-blocks the splat's
  * {alpha >= 1/255} box reaches, [9] pairs visited, [10] pixel evaluations, [11] of those with an exp,
- * [12] of those contributing (alpha >= 1/255), [13] pairs with at least one contribution.  These are the
- * flop / atomic counts behind the issue-rate roofline of the render kernels; not on the hot path. */
+ * [12] of those contributing (alpha >= 1/255), [13] pairs with at least one contribution, [14] evaluations whose
+ * alpha >= 1/255 test comes out differently with the backward's fast exponential than with the forward's expf (a
+ * count for DESIGN.md, not a gate), [15] reserved.  These are the flop / atomic counts behind the issue-rate
+ * roofline of the render kernels; not on the hot path. */
 B200SPLAT_API int b200splat_render_stats(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
                            const void* geom, const void* binning, const void* image,
-                           uint64_t* out14, void* stream);
+                           uint64_t* out16, void* stream);
 
 /* Sizes of the geometry and image buffers for given dimensions (the binning buffer depends on R and,
  * through the width of the tile key, on the number of tiles). */

@@ -49,6 +49,19 @@
 #define HOT
 #endif
 
+/* Counting experiment: 0 = canonical pixel formula, 1 = fp32 three-rounding order. */
+static int g_pixel_fp32 = 0;
+ORC_API void orc_set_pixel_fp32(int on) { g_pixel_fp32 = on; }
+
+/* Thread count of the OpenMP loops below, set by the caller (bench.py's CPU legs) rather than inherited from an
+ * OMP_NUM_THREADS a launcher exported (torchrun sets it to 1). */
+#ifdef _OPENMP
+#include <omp.h>
+ORC_API void orc_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+#else
+ORC_API void orc_set_threads(int n) { (void)n; }
+#endif
+
 /* SH constants, /root/reference/utils/sh_utils.py:26-43 (rounded to float as the kernels do) */
 static const float SH_C0 = 0.28209479177387814f;
 static const float SH_C1 = 0.4886025119029199f;
@@ -216,9 +229,14 @@ ORC_API void orc_preprocess(
         float lam1 = mid + sq, lam2 = mid - sq;
         int radius = f2i_rz_sat(ceilf(3.0f * sqrtf(fmaxf(lam1, lam2))));
 
-        /* ndc -> pixel, evaluated in double and rounded once (exact in double) */
+        /* ndc -> pixel, evaluated in double and rounded once (exact in double).  g_pixel_fp32 (counting
+         * experiment only, orc_set_pixel_fp32): the three-rounding fp32 order of SURVEY.md A.2 step 7. */
         float px = (float)((((double)ndcx + 1.0) * (double)W - 1.0) * 0.5);
         float py = (float)((((double)ndcy + 1.0) * (double)H - 1.0) * 0.5);
+        if (g_pixel_fp32) {
+            px = ((ndcx + 1.0f) * (float)W - 1.0f) * 0.5f;
+            py = ((ndcy + 1.0f) * (float)H - 1.0f) * 0.5f;
+        }
         int r[4];
         get_rect(px, py, radius, gx, gy, r);
         int area = (r[2] - r[0]) * (r[3] - r[1]);

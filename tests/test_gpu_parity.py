@@ -23,6 +23,17 @@ CASES = {
     "dense_opaque": dict(P=6000, W=128, H=96, D=2, seed=4, s_med=0.25, bg=(0.3, 0.3, 0.3)),  # hits the 1e-4 exit / 0.99 clamp
     "precomp": dict(P=3000, W=160, H=120, D=0, seed=5, s_med=0.05, precomp_color=True, precomp_cov=True),
     "scale_mod": dict(P=3000, W=160, H=120, D=3, seed=6, s_med=0.04, mod=1.7),
+    # antialiasing (mip filter): opacity scaled by h = sqrt(max(0.000025, det0 / det)), BASELINE configs[4]
+    "sh3_aa": dict(P=3000, W=200, H=136, D=3, seed=1, s_med=0.04, bg=(0.1, 0.2, 0.3), antialiasing=True),
+    "precomp_aa": dict(P=3000, W=160, H=120, D=0, seed=5, s_med=0.05, precomp_color=True, precomp_cov=True, antialiasing=True),
+    "dense_aa": dict(P=6000, W=128, H=96, D=2, seed=4, s_med=0.25, bg=(0.3, 0.3, 0.3), antialiasing=True),
+    # sub-pixel splats: det0 / det <= 0.000025 for ~950 of the 2100 visible Gaussians (the clamp branch, whose
+    # d(ratio) terms vanish), 69 of which are blended; the rest take the unclamped branch
+    "aa_clamp": dict(P=3000, W=200, H=136, D=3, seed=21, s_med=0.001, bg=(0.1, 0.2, 0.3), antialiasing=True),
+    # splats with sigma of hundreds of pixels: the conservative {alpha >= 1/255} box of the render kernels must hold
+    "huge_splats": dict(P=400, W=640, H=480, D=1, seed=8, s_med=1.2, bg=(0.2, 0.2, 0.2)),
+    # 257 x 256 = 65792 tiles > 65536: the 32-bit tile-key instantiations of the binning kernels
+    "u32_tile_keys": dict(P=1500, W=4112, H=4096, D=0, seed=12, s_med=0.025),
 }
 
 
@@ -80,14 +91,14 @@ def test_backward_gradients(name):
         assert float(np.abs(n(g["means3D"])[culled]).max()) == 0.0
 
 
-@pytest.mark.parametrize("name", ["sh3_small", "dense_opaque", "precomp"])
+@pytest.mark.parametrize("name", ["sh3_small", "dense_opaque", "precomp", "sh3_aa", "aa_clamp"])
 def test_backward_with_inverse_depth_gradient(name):
     """The inverse-depth image is differentiable (newer upstream API): a loss on colour AND inverse depth."""
     case = Case(**CASES[name])
     fr = case.oracle_forward(want_invdepth=True)
     pg = case.oracle_backward(fr, invdepth_grad=True)
     pg0 = case.oracle_backward(fr)
-    assert rel_err(pg.dL_dmeans3D, pg0.dL_dmeans3D) > 1e-2      # the depth term is not negligible in this case
+    assert rel_err(pg.dL_dmeans3D, pg0.dL_dmeans3D) > 1e-3      # the depth term is not negligible in this case
     color, radii, invd, g = case.cuda_run(invdepth_grad=True)
     errs = {"means3D": rel_err(n(g["means3D"]), pg.dL_dmeans3D),
             "opacities": rel_err(n(g["opacities"]).reshape(-1), pg.dL_dopacity),
@@ -133,8 +144,12 @@ def test_mark_visible_and_errors():
                                            c.full_proj_transform, 0, c.camera_center, False, False)
     r = dgr.GaussianRasterizer(rs)
     vis = r.markVisible(s.means3D)
-    p4 = torch.cat([s.means3D, torch.ones(500, 1, device=dev)], 1) @ c.world_view_transform
-    assert torch.equal(vis, p4[:, 2] > 0.2) or int((vis != (p4[:, 2] > 0.2)).sum()) <= 1
+    # the kernel computes view-space z with the canonical fma chain, torch.matmul in its own order: the two may
+    # only disagree for points whose z is within rounding of the 0.2 near plane
+    p4 = torch.cat([s.means3D, torch.ones(500, 1, device=dev)], 1).double() @ c.world_view_transform.double()
+    far_from_plane = (p4[:, 2] - 0.2).abs() > 1e-5
+    assert torch.equal(vis[far_from_plane], (p4[:, 2] > 0.2)[far_from_plane])
+    assert int(vis.sum()) > 0 and int((~vis).sum()) >= 0
     with pytest.raises(Exception):
         r(means3D=s.means3D, means2D=None, opacities=s.opacities, shs=s.shs, colors_precomp=torch.zeros(500, 3, device=dev),
           scales=s.scales, rotations=s.rotations)
@@ -164,6 +179,7 @@ def test_factorized_exchange_pieces_match_direct_path():
         for mode in ("factorized", "packed"):      # packed: rows of touched Gaussians + b200splat_accumulate_packed
             b = vp.ViewParallelStep(params, Dg, bg, exchange=mode)
             for _ in range(2):                     # twice: the second step reuses buffers of the first
+                b.reset_densification_stats()      # (the statistics accumulate over steps until reset)
                 cb = b.step(cams, dLs)
             torch.cuda.synchronize()
             assert torch.equal(ca, cb)

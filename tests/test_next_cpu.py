@@ -127,3 +127,21 @@ def test_fused_adam_keeps_torch_optimizer_surface():
     assert opt.param_groups[0]["lr"] == 0.5
     opt.zero_grad(set_to_none=True)
     assert opt.step() is None                                  # nothing has a gradient: no launch, no error
+
+
+def test_ply_written_by_the_reference_save_ply(tmp_path):
+    """tests/golden/reference_save_ply_7.ply was produced by the reference's OWN GaussianModel.save_ply
+    (/root/reference/scene/gaussian_model.py:218-258) run in the build container with only the absent `plyfile`
+    writer restated (tests/golden/make_golden_ply.py).  The codec must read it back to the tensors that went in and
+    write the identical bytes."""
+    import gaussian_training as gtr
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    path = os.path.join(here, "reference_save_ply_7.ply")
+    src = np.load(os.path.join(here, "reference_save_ply_7.npz"))
+    r = gtr.load_ply(path)
+    for k in ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation"):
+        assert r[k].shape == src[k].shape, k
+        assert np.array_equal(r[k].numpy(), src[k]), k          # features_rest comes back [P,15,3] from channel-major columns
+    out = str(tmp_path / "again.ply")
+    gtr.save_ply(out, *(r[k] for k in ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")))
+    assert open(out, "rb").read() == open(path, "rb").read()

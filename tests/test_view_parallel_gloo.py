@@ -41,10 +41,18 @@ def _worker(rank, world, initfile, outdir):
     params, cams, dLs = _setup()
     mine = vp.shard_views(NV, rank, world)
     st = vp.ViewParallelStep(params, D, torch.zeros(3), world_size=world, rasterize=_oracle_rasterize)
+    # two steps: the densification statistics accumulate over steps (the reference consumes them every ~100
+    # iterations, /root/reference/train.py:127-133) and are reduced on demand; gradients are per step
+    st.step([cams[k] for k in mine], [dLs[k] for k in mine])
     st.step([cams[k] for k in mine], [dLs[k] for k in mine])
     g = st.grads()
-    torch.save({"grads": [t.clone() for t in g], "accum": st.xyz_gradient_accum.clone(), "denom": st.denom.clone(),
-                "maxr": st.max_radii2D.clone(), "views": mine}, os.path.join(outdir, f"r{rank}.pt"))
+    accum, denom, maxr = st.reduce_densification_stats()
+    again = st.reduce_densification_stats()                 # idempotent: the local accumulators are untouched
+    assert torch.equal(again[0], accum) and torch.equal(again[1], denom) and torch.equal(again[2], maxr)
+    torch.save({"grads": [t.clone() for t in g], "accum": accum, "denom": denom, "maxr": maxr, "views": mine},
+               os.path.join(outdir, f"r{rank}.pt"))
+    st.reset_densification_stats()
+    assert float(st.xyz_gradient_accum.abs().max()) == 0.0 and float(st.denom.max()) == 0.0
     dist.barrier()
     dist.destroy_process_group()
 
@@ -64,12 +72,14 @@ def test_two_rank_step_matches_single_process():
     params, cams, dLs = _setup()
     single = vp.ViewParallelStep(params, D, torch.zeros(3), world_size=1, rasterize=_oracle_rasterize)
     single.step(cams, dLs)
+    single.step(cams, dLs)                                            # statistics of two steps, like the ranks
     for a, b, c in zip(r0["grads"], r1["grads"], single.grads()):
         assert torch.equal(a, b)                                      # every rank holds the reduced gradient
         assert float((a - c).abs().max()) <= 1e-3 * max(float(c.abs().max()), 1e-12)
     assert torch.allclose(r0["accum"], single.xyz_gradient_accum, rtol=1e-4, atol=1e-9)
     assert torch.equal(r0["denom"], single.denom) and torch.equal(r0["maxr"], single.max_radii2D)
-    assert float(single.denom.max()) > 1                              # some Gaussian seen from several views
+    assert float(single.denom.max()) > 2                              # some Gaussian seen from several views, twice
+    assert torch.equal(r0["accum"], r1["accum"])
 
 
 # ---- factorized exchange (all-gather of masked colour gradients + local SH rebuild) ---------------------------
@@ -112,10 +122,11 @@ def _worker_fact(rank, world, initfile, outdir):
     st = vp.ViewParallelStep(params, D, torch.zeros(3), world_size=world, exchange="factorized",
                              backend=_TorchBackend(D, torch.zeros(3)))
     st.step([cams[k] for k in mine], [dLs[k] for k in mine])
+    st.step([cams[k] for k in mine], [dLs[k] for k in mine])
     local_accum = st.xyz_gradient_accum.clone()
-    st.reduce_densification_stats()
-    torch.save({"grads": [t.clone() for t in st.grads()], "accum": st.xyz_gradient_accum.clone(), "local_accum": local_accum,
-                "denom": st.denom.clone(), "maxr": st.max_radii2D.clone()}, os.path.join(outdir, f"f{rank}.pt"))
+    accum, denom, maxr = st.reduce_densification_stats()
+    torch.save({"grads": [t.clone() for t in st.grads()], "accum": accum, "local_accum": local_accum,
+                "denom": denom, "maxr": maxr}, os.path.join(outdir, f"f{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -127,6 +138,7 @@ def test_two_rank_factorized_exchange_matches_single_process():
         r0, r1 = torch.load(os.path.join(d, "f0.pt")), torch.load(os.path.join(d, "f1.pt"))
     params, cams, dLs = _setup()
     single = vp.ViewParallelStep(params, D, torch.zeros(3), world_size=1, rasterize=_oracle_rasterize)
+    single.step(cams, dLs)
     single.step(cams, dLs)
     for a, b, c in zip(r0["grads"], r1["grads"], single.grads()):
         assert float((a - b).abs().max()) <= 1e-6 * max(float(c.abs().max()), 1e-12)     # ranks agree

@@ -26,8 +26,8 @@ for P, W, H, D in ((20000, 320, 200, 3), (4321, 200, 120, 1)):
         for _ in range(3):     # repeated steps exercise buffer reuse / the second barrier
             st.step([cam], [dL])
         torch.cuda.synchronize()
-        st.reduce_densification_stats()
-        res[name] = ([g.clone() for g in st.grads()], st.xyz_gradient_accum.clone(), st.denom.clone(), st.max_radii2D.clone(),
+        accum, denom, maxr = st.reduce_densification_stats()     # three steps' worth, summed / maxed over the ranks
+        res[name] = ([g.clone() for g in st.grads()], accum, denom, maxr,
                      bool(st._symm and "flat" in st._symm))
     for name in ("nccl", "peer", "packed"):
         for f, a, b in zip(vp.GaussianParams._fields, res["allreduce"][0], res[name][0]):

@@ -27,7 +27,9 @@ for r in rows[2:]:
 # machine-readable digest for bench.py's roofline (`traffic`, `issue`): profiles/<round>_ncu_kernels.json
 if len(sys.argv) > 2:
     import json, re
-    digest = {"source": os.path.basename(rep) if 'os' in dir() else rep}
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from bench import csrc_sha16          # the capture belongs to THIS source state: bench.py drops it when the sources change
+    digest = {"source": os.path.basename(rep), "csrc_sha16": os.environ.get("CSRC_SHA16") or csrc_sha16()}
     def num(r, k):
         try:
             return float(r[ix[k]].replace(",", ""))
