@@ -57,37 +57,6 @@ struct StageTimer {
     }
 };
 
-// Host-side mailbox for the pair count R: a pinned 8-byte slot and an event per host thread, created on
-// first use and kept for the life of the thread (the only state the library keeps besides the error
-// string).  The forward copies R into the slot right after the preprocess kernel, records the event, then
-// keeps enqueueing work that does not depend on R (the depth sort) BEFORE waiting on the event, so the
-// host round trip and the binning-buffer allocation are hidden behind device work.
-struct Mailbox {
-    unsigned long long* slot = nullptr;
-    cudaEvent_t ev = nullptr;
-    int device = -1;
-    ~Mailbox() {
-        if (slot) cudaFreeHost(slot);
-        if (ev) cudaEventDestroy(ev);
-    }
-    cudaError_t ensure() {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        if (slot && dev == device) return cudaSuccess;
-        if (ev) { cudaEventDestroy(ev); ev = nullptr; }
-        if (!slot) {
-            e = cudaHostAlloc((void**)&slot, sizeof(unsigned long long), cudaHostAllocDefault);
-            if (e != cudaSuccess) { slot = nullptr; return e; }
-        }
-        e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
-        if (e != cudaSuccess) { ev = nullptr; return e; }
-        device = dev;
-        return cudaSuccess;
-    }
-};
-thread_local Mailbox g_mailbox;
-
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 int validate(const b200splat_view* v, const b200splat_gaussians* g) {
@@ -139,49 +108,51 @@ int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g, 
     if (rc) return rc;
     if (!out || !out->color || (g->P > 0 && !out->radii)) return fail(B200SPLAT_ERR_INVALID_ARG, "null outputs");
     if (!alloc || !alloc->alloc || !num_rendered) return fail(B200SPLAT_ERR_INVALID_ARG, "null allocator / num_rendered");
+    if (alloc->bin_capacity < 0 || alloc->bin_capacity > 0x7fffffffll) return fail(B200SPLAT_ERR_INVALID_ARG, "bin_capacity out of range");
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool debug = view->debug != 0;
     const int P = g->P, W = view->image_width, H = view->image_height;
+    if ((W + TILE - 1) / TILE > max_tile_bins() || (H + TILE - 1) / TILE > max_tile_bins())
+        return fail(B200SPLAT_ERR_INVALID_ARG, "image larger than 8192 x 8192 pixels");
 
     void* geom_mem = alloc->alloc(alloc->geom_ctx, b200splat_geom_bytes(P));
     void* img_mem = alloc->alloc(alloc->image_ctx, b200splat_image_bytes(W, H));
     if (!geom_mem || !img_mem) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (geometry / image buffer)");
     GeomView gv = carve_geom(geom_mem, P);
     ImgView iv = carve_image(img_mem, W, H);
-
     const int T = tiles_of(W, H);
-    unsigned long long* pair_counter = reinterpret_cast<unsigned long long*>(iv.counters + CTR_PAIRS);
-    CU(g_mailbox.ensure(), "pinned mailbox");
 
     StageTimer tm(times != nullptr, stream);
     tm.mark();
-    CU(cudaMemsetAsync(iv.counters, 0, 64 * sizeof(unsigned int), stream), "clear counters");
-    STAGE(launch_preprocess_fwd(*view, *g, gv, out->radii, pair_counter, stream), "preprocess");
+    CU(cudaMemsetAsync(iv.counters, 0, CTR_WORDS * sizeof(unsigned int), stream), "clear control block");
+    CU(cudaMemsetAsync(iv.ranges, 0, (size_t)(T > 0 ? T : 1) * sizeof(int2), stream), "clear ranges");
+    STAGE(launch_preprocess_fwd(*view, *g, gv, out->radii, iv.counters, stream), "preprocess");
     tm.mark();
-    unsigned long long R = 0;
-    if (P > 0) {
-        CU(cudaMemcpyAsync(g_mailbox.slot, pair_counter, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream), "read num_rendered");
-        CU(cudaEventRecord(g_mailbox.ev, stream), "record num_rendered");
-    }
-    // independent of R: runs on the device while the host waits for R and sizes the binning buffer
-    STAGE(launch_depth_order(gv, P, stream), "depth order");
+    STAGE(launch_depth_order(gv, P, iv.counters, stream), "depth order");
     tm.mark();
-    if (P > 0) {
-        CU(cudaEventSynchronize(g_mailbox.ev), "sync num_rendered");
-        R = *g_mailbox.slot;
-    }
-    if (R > 0x7fffffffull) return fail(B200SPLAT_ERR_INVALID_ARG, "more than 2^31-1 tile/Gaussian pairs");
-    *num_rendered = (int32_t)R;
 
-    void* bin_mem = alloc->alloc(alloc->binning_ctx, b200splat_binning_bytes((int32_t)R, W, H));
+    // Pair capacity of the binning buffer (b200splat.h "pair capacity").  bin_capacity > 0: the caller's bound, and
+    // this call never waits for the device -- R stays in the control block, where every later kernel reads it.
+    // bin_capacity == 0: exact -- one host round trip for R, after the depth order has been queued.
+    long long cap = alloc->bin_capacity;
+    if (cap == 0 && P > 0) {
+        unsigned long long R = 0;
+        CU(cudaMemcpyAsync(&R, iv.counters + CTR_PAIRS, sizeof(R), cudaMemcpyDeviceToHost, stream), "read num_rendered");
+        CU(cudaStreamSynchronize(stream), "sync num_rendered");
+        if (R > 0x7fffffffull) return fail(B200SPLAT_ERR_INVALID_ARG, "more than 2^31-1 tile/Gaussian pairs");
+        cap = (long long)R;
+    }
+    *num_rendered = (int32_t)cap;
+
+    void* bin_mem = alloc->alloc(alloc->binning_ctx, b200splat_binning_bytes((int32_t)cap, W, H));
     if (!bin_mem) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (binning buffer)");
-    BinView bv = carve_binning(bin_mem, (int)R, T);
+    BinView bv = carve_binning(bin_mem, (int)cap, T);
 
-    if (R > 0) STAGE(launch_emit(gv, P, W, H, bv, stream), "duplicateWithKeys");
+    if (cap > 0) STAGE(launch_emit(gv, P, W, H, bv, iv.counters, stream), "duplicateWithKeys");
     tm.mark();
-    STAGE(launch_tile_sort(bv, (int)R, T, stream), "sort");
+    STAGE(launch_tile_sort(bv, W, H, iv, stream), "sort");
     tm.mark();
-    STAGE(launch_ranges(bv, (int)R, iv, W, H, stream), "identifyTileRanges");
+    STAGE(launch_tile_order(iv, W, H, stream), "identifyTileRanges");
     tm.mark();
     STAGE(launch_render_fwd(*view, gv, bv, iv, out->color, out->invdepth, stream), "render");
     tm.mark();
@@ -193,14 +164,36 @@ int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g, 
     return B200SPLAT_OK;
 }
 
+size_t b200splat_image_status_offset(int32_t width, int32_t height) {
+    ImgView iv = carve_image(nullptr, width, height);
+    return (size_t)((char*)(iv.counters + CTR_STATUS) - (char*)nullptr);
+}
+
+int b200splat_forward_status(const void* image, int32_t width, int32_t height, int64_t* num_pairs, int64_t* capacity,
+                             int32_t* overflow, void* stream_) {
+    if (!image || width <= 0 || height <= 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad arguments");
+    ImgView iv = carve_image(const_cast<void*>(image), width, height);
+    unsigned int w[4] = {0, 0, 0, 0};
+    unsigned long long R = 0;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CU(cudaMemcpyAsync(&R, iv.counters + CTR_PAIRS, sizeof(R), cudaMemcpyDeviceToHost, stream), "read pair count");
+    CU(cudaMemcpyAsync(w, iv.counters + CTR_STATUS, sizeof(w), cudaMemcpyDeviceToHost, stream), "read status");
+    CU(cudaStreamSynchronize(stream), "status sync");
+    if (num_pairs) *num_pairs = (int64_t)R;
+    if (capacity) *capacity = (int64_t)w[2];
+    if (overflow) *overflow = (int32_t)w[3];
+    return B200SPLAT_OK;
+}
+
 // Internal side stream (per thread and device) for work that runs beside the caller's stream inside one call;
 // always forked from and joined back into the caller's stream, so the call stays stream-ordered for the caller.
 struct SideStream {
     cudaStream_t stream = nullptr;
     cudaEvent_t fork = nullptr, join = nullptr;
 };
+static thread_local SideStream g_side_streams[64];
 static cudaError_t side_stream(SideStream** out) {
-    static thread_local SideStream per_device[64];
+    SideStream* per_device = g_side_streams;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -212,6 +205,23 @@ static cudaError_t side_stream(SideStream** out) {
     }
     *out = &ss;
     return cudaSuccess;
+}
+
+// Releases what the calling host thread holds inside the library: its helper streams and events.
+void b200splat_shutdown(void) {
+    int cur = 0;
+    const bool have = cudaGetDevice(&cur) == cudaSuccess;
+    for (int d = 0; d < 64; d++) {
+        SideStream& ss = g_side_streams[d];
+        if (!ss.stream) continue;
+        if (have) cudaSetDevice(d);
+        cudaStreamSynchronize(ss.stream);
+        cudaStreamDestroy(ss.stream);
+        if (ss.fork) cudaEventDestroy(ss.fork);
+        if (ss.join) cudaEventDestroy(ss.join);
+        ss = SideStream();
+    }
+    if (have) cudaSetDevice(cur);
 }
 
 int b200splat_backward(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
@@ -412,13 +422,11 @@ int b200splat_export_state(int32_t P, int32_t width, int32_t height, int32_t num
         GeomView gv = carve_geom(const_cast<void*>(geom), P);
         CU(launch_export_geom(P, radii, gv, *out, stream), "export geometry");
     }
-    if (geom && P > 0) {
+    if (geom && image && P > 0) {
         GeomView gv = carve_geom(const_cast<void*>(geom), P);
-        BinView bv = carve_binning(const_cast<void*>(binning), num_rendered, tiles_of(width, height));
-        const int R = binning ? num_rendered : 0;
-        CU(launch_export_binning(P, R, gv, bv, *out, stream), "export binning");
-        if (out->vals_sorted && R > 0)
-            CU(cudaMemcpyAsync(out->vals_sorted, bv.vals_sorted, sizeof(uint32_t) * (size_t)R, cudaMemcpyDeviceToDevice, stream), "export vals");
+        BinView bv = carve_binning(const_cast<void*>(binning), binning ? num_rendered : 0, tiles_of(width, height));
+        ImgView iv = carve_image(const_cast<void*>(image), width, height);
+        CU(launch_export_binning(P, width, height, gv, bv, iv, *out, stream), "export binning");
     }
     if (image) {
         ImgView iv = carve_image(const_cast<void*>(image), width, height);

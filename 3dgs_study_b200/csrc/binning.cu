@@ -1,4 +1,5 @@
-// binning.cu -- tile binning, sm_100a.  HBM-bound integer work.
+// binning.cu -- tile binning, sm_100a.  HBM / L2-bound integer work; every kernel is hand-written (no library
+// sort or scan), and nothing waits on the host.
 //
 // Stands in for the binning stages of _C.rasterize_gaussians named by BASELINE.json's north_star
 // ("duplicateWithKeys pass emitting 64-bit tile|depth keys, then a radix sort and identifyTileRanges").
@@ -6,25 +7,288 @@
 // Gaussian id), exactly what a stable sort of (tile << 32 | depth) keys emitted in Gaussian order
 // yields -- but the traffic is a fraction of it (see splat_internal.cuh "Binning order"):
 //
-//   1. depth order   stable radix sort of the P (depth bits, id) pairs      4 passes x 16 B x P
-//   2. offsets       inclusive scan of tiles touched, in depth order          gather + 4 B x P
+//   1. depth order   stable LSD radix sort of the V visible (depth bits, id) pairs, 3 passes.  The first pass reads
+//                    the P depth keys in index order, drops the culled ones and supplies the ids itself (no iota
+//                    array, no separate compaction); the digit width adapts to the key range seen by the
+//                    preprocess kernel (min / max in the control block): 26 significant bits -> 3 x 9.
+//   2. offsets       inclusive scan of tiles touched, in depth order (reduce / spine / apply kernels)
 //   3. emit          block-cooperative duplicateWithKeys: a block owns 256 consecutive Gaussians of the
 //                    depth order and therefore a CONTIGUOUS output range; consecutive threads write
-//                    consecutive (tile key, id) slots (binary search in the block's offsets), so the
-//                    writes are fully coalesced and a huge splat cannot serialise one thread
-//   4. tile sort     stable radix sort on the tile bits only                  2 passes x 12 B x R
-//   5. ranges        identifyTileRanges on the sorted tile keys
+//                    consecutive (tile id, Gaussian id) slots, so the writes are fully coalesced
+//   4. tile sort     stable LSD sort on the tile id, 2 passes: by tile column (tile % gx), then by tile row
+//                    (tile / gx).  The second pass writes only the Gaussian ids (nobody needs sorted keys) and
+//                    publishes the tile ranges itself: all pairs of a tile are contiguous in its output, so the
+//                    first / last position a block writes for a tile go to ranges[] through atomicMax.
+//   5. tile order    longest list first (also turns the atomicMax encoding of the range starts back into starts)
 //
-// The 64-bit keys are never materialised on the hot path; b200splat_export_state rebuilds them for
-// the parity tests from (sorted tile key, depth of the sorted id).
-#include <cub/cub.cuh>
-
+// One radix pass = three kernels, none of which can wait on another block (no decoupled look-back, no spinning):
+//   count    per block of 4096 elements, a shared-memory digit histogram -> matrix[digit][block]
+//   colscan  one warp per digit: exclusive scan of its matrix row over the blocks, row total -> totals[digit]
+//   scatter  per block: digit bases (scan of totals) + its matrix column = where its elements of each digit go;
+//            stable ranks inside the block from warp-level match_any (a warp owns 512 consecutive elements,
+//            16 rounds of 32 in order) + a prefix over the 8 warps; the tile passes stage the block in shared
+//            memory in sorted order so that every digit leaves as one contiguous run.
+// The element counts (V, R) live in the image buffer's control block and are read by the kernels; grids are
+// sized for the host-known bounds (P, pair capacity) and surplus blocks exit at once.
 #include "splat_internal.cuh"
 
 namespace b200splat {
 
 namespace {
 
+constexpr unsigned FULLMASK = 0xffffffffu;
+constexpr int RS_THREADS = 256, RS_WARPS = RS_THREADS / 32, RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;              // 4096 elements per block
+constexpr int DEPTH_MAXBINS = 2048;                         // 3 passes x <= 11 bits cover any 32-bit key range
+constexpr int TILE_MAXBINS = 512;                           // tile columns / rows: images up to 8192 x 8192
+
+inline int radix_blocks(size_t n) { return (int)((n + RS_TILE - 1) / RS_TILE) > 0 ? (int)((n + RS_TILE - 1) / RS_TILE) : 1; }
+
+// Element count of a pass: a device word (u64 when `wide`) clipped to a host-known bound.
+struct Count {
+    const unsigned* ptr;
+    unsigned bound;
+    int wide;
+};
+__device__ __forceinline__ unsigned load_count(Count c) {
+    if (!c.ptr) return c.bound;
+    unsigned v = __ldg(c.ptr);
+    if (c.wide && __ldg(c.ptr + 1) != 0u) v = 0xffffffffu;
+    return min(v, c.bound);
+}
+
+// ---- digit extraction ------------------------------------------------------------------------------
+struct DepthTraits {
+    using KeyT = uint32_t;
+    static constexpr int MAXBINS = DEPTH_MAXBINS;
+    static constexpr bool STAGE = false;
+    const unsigned* ctr;      // control block: key range of the visible Gaussians
+    int pass;
+    uint32_t kmin, mask;      // set by init()
+    int shift, nbins;
+    __device__ __forceinline__ void init() {
+        const uint32_t kmn = ~__ldg(ctr + CTR_KMIN_NEG), kmx = __ldg(ctr + CTR_KMAX);
+        const uint32_t span = kmx >= kmn ? kmx - kmn : 0u;
+        const int bits = 32 - __clz((int)span);             // __clz(0) = 32
+        const int w = max(1, (bits + 2) / 3);               // three passes cover `bits`; w <= 11
+        kmin = kmn; shift = pass * w; mask = (1u << w) - 1u; nbins = 1 << w;
+    }
+    __device__ __forceinline__ bool valid(uint32_t k) const { return k != 0xffffffffu; }
+    __device__ __forceinline__ uint32_t digit(uint32_t k) const { return ((k - kmin) >> shift) & mask; }
+    __device__ __forceinline__ int bins() const { return nbins; }
+};
+
+template <typename K>
+struct TileTraits {
+    using KeyT = K;
+    static constexpr int MAXBINS = TILE_MAXBINS;
+    static constexpr bool STAGE = true;
+    int gx, nbins, by_row;
+    unsigned long long magic;  // floor(2^32 / gx) + 1: tile / gx = (tile * magic) >> 32 exactly for tile < 2^20, gx <= 512
+    __device__ __forceinline__ void init() {}
+    __device__ __forceinline__ bool valid(K) const { return true; }
+    __device__ __forceinline__ uint32_t digit(K k) const {
+        const uint32_t t = (uint32_t)k;
+        const uint32_t q = (uint32_t)(((unsigned long long)t * magic) >> 32);
+        return by_row ? q : t - q * (uint32_t)gx;
+    }
+    __device__ __forceinline__ int bins() const { return nbins; }
+};
+
+// In-place exclusive scan of s[0..n), n <= 2048, by a 256-thread block (s fully written and synchronised by the
+// caller; synchronised again on return).
+__device__ __forceinline__ void block_excl_scan(uint32_t* s, int n, uint32_t* s_warp) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (n + RS_THREADS - 1) / RS_THREADS;      // <= 8
+    const int b0 = tid * per;
+    uint32_t v[8], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        v[k] = (k < per && b0 + k < n) ? s[b0 + k] : 0u;
+        sum += v[k];
+    }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULLMASK, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t run = incl - sum;
+    for (int w = 0; w < warp; w++) run += s_warp[w];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        if (k < per && b0 + k < n) { s[b0 + k] = run; run += v[k]; }
+    }
+    __syncthreads();
+}
+
+// ---- one radix pass: count / colscan / scatter ---------------------------------------------------------
+template <class TR>
+__global__ void __launch_bounds__(RS_THREADS) radix_count_kernel(TR tr, const typename TR::KeyT* __restrict__ keys, Count cnt,
+                                                                 int stride, uint32_t* __restrict__ matrix) {
+    __shared__ unsigned s_hist[TR::MAXBINS];
+    const unsigned n = load_count(cnt);
+    const unsigned base = blockIdx.x * (unsigned)RS_TILE;
+    if (base >= n) return;
+    tr.init();
+    const int bins = tr.bins(), tid = threadIdx.x;
+    for (int d = tid; d < bins; d += RS_THREADS) s_hist[d] = 0u;
+    __syncthreads();
+#pragma unroll 4
+    for (int e = 0; e < RS_ITEMS; e++) {
+        const unsigned idx = base + e * RS_THREADS + tid;
+        if (idx < n) {
+            const typename TR::KeyT k = keys[idx];
+            if (tr.valid(k)) atomicAdd(&s_hist[tr.digit(k)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int d = tid; d < bins; d += RS_THREADS) matrix[(size_t)d * stride + blockIdx.x] = s_hist[d];
+}
+
+template <class TR>
+__global__ void __launch_bounds__(RS_THREADS) radix_colscan_kernel(TR tr, Count cnt, int stride, uint32_t* __restrict__ matrix,
+                                                                   uint32_t* __restrict__ totals) {
+    const int lane = threadIdx.x & 31;
+    const int d = (blockIdx.x * RS_THREADS + threadIdx.x) >> 5;          // one warp per digit
+    tr.init();
+    if (d >= tr.bins()) return;
+    const unsigned n = load_count(cnt);
+    const int nb = (int)((n + RS_TILE - 1) / RS_TILE);
+    uint32_t* row = matrix + (size_t)d * stride;
+    uint32_t run = 0;
+    for (int b0 = 0; b0 < nb; b0 += 32) {
+        const int b = b0 + lane;
+        const uint32_t v = b < nb ? row[b] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULLMASK, incl, s);
+            if (lane >= s) incl += t;
+        }
+        if (b < nb) row[b] = run + incl - v;
+        run += __shfl_sync(FULLMASK, incl, 31);
+    }
+    if (lane == 0) totals[d] = run;
+}
+
+template <class TR>
+__global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(TR tr, const typename TR::KeyT* __restrict__ keys_in,
+                                                                   const uint32_t* __restrict__ vals_in,
+                                                                   typename TR::KeyT* __restrict__ keys_out,
+                                                                   uint32_t* __restrict__ vals_out, Count cnt, int stride,
+                                                                   const uint32_t* __restrict__ matrix,
+                                                                   const uint32_t* __restrict__ totals, int2* __restrict__ ranges) {
+    using KeyT = typename TR::KeyT;
+    constexpr int MB = TR::MAXBINS;
+    __shared__ uint32_t s_base[MB];                          // global position of this block's first element of each digit
+    __shared__ uint16_t s_whist[RS_WARPS][MB];               // per-warp digit counts -> exclusive prefix over the warps
+    __shared__ uint32_t s_lstart[TR::STAGE ? MB : 1];        // first slot of each digit in the block's sorted order
+    __shared__ KeyT s_key[TR::STAGE ? RS_TILE : 1];
+    __shared__ uint32_t s_val[TR::STAGE ? RS_TILE : 1];
+    __shared__ uint32_t s_warp[RS_WARPS];
+    const unsigned n = load_count(cnt);
+    const unsigned base = blockIdx.x * (unsigned)RS_TILE;
+    if (base >= n) return;
+    tr.init();
+    const int bins = tr.bins(), tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int d = tid; d < bins; d += RS_THREADS) {
+        s_base[d] = __ldg(totals + d);
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) s_whist[w][d] = 0;
+    }
+    __syncthreads();
+    block_excl_scan(s_base, bins, s_warp);
+    for (int d = tid; d < bins; d += RS_THREADS) s_base[d] += __ldg(matrix + (size_t)d * stride + blockIdx.x);
+
+    // a warp owns 512 consecutive elements: 16 rounds of 32, in order
+    KeyT k[RS_ITEMS];
+    uint32_t v[RS_ITEMS], rank[RS_ITEMS];
+    const unsigned wbase = base + warp * (RS_ITEMS * 32);
+#pragma unroll
+    for (int e = 0; e < RS_ITEMS; e++) {
+        const unsigned idx = wbase + e * 32 + lane;
+        const bool in = idx < n;
+        k[e] = in ? keys_in[idx] : (KeyT)0;
+        v[e] = vals_in ? (in ? __ldg(vals_in + idx) : 0u) : idx;
+    }
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int e = 0; e < RS_ITEMS; e++) {
+        const unsigned idx = wbase + e * 32 + lane;
+        const bool ok = idx < n && tr.valid(k[e]);
+        const uint32_t dd = ok ? tr.digit(k[e]) : 0xffffffffu;
+        const unsigned peers = __match_any_sync(FULLMASK, dd);
+        const uint32_t prev = ok ? s_whist[warp][dd] : 0u;
+        __syncwarp();
+        rank[e] = ok ? prev + __popc(peers & lt) : 0xffffffffu;
+        if (ok && lane == __ffs(peers) - 1) s_whist[warp][dd] = (uint16_t)(prev + __popc(peers));
+        __syncwarp();
+    }
+    __syncthreads();
+    for (int d = tid; d < bins; d += RS_THREADS) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) {
+            const uint32_t c = s_whist[w][d];
+            s_whist[w][d] = (uint16_t)run;
+            run += c;
+        }
+        if (TR::STAGE) s_lstart[d] = run;
+    }
+    __syncthreads();
+    if (!TR::STAGE) {
+#pragma unroll
+        for (int e = 0; e < RS_ITEMS; e++) {
+            if (rank[e] != 0xffffffffu) {
+                const uint32_t dd = tr.digit(k[e]);
+                const uint32_t pos = s_base[dd] + s_whist[warp][dd] + rank[e];
+                if (keys_out) keys_out[pos] = k[e];
+                vals_out[pos] = v[e];
+            }
+        }
+        return;
+    }
+    block_excl_scan(s_lstart, bins, s_warp);
+#pragma unroll
+    for (int e = 0; e < RS_ITEMS; e++) {
+        if (rank[e] != 0xffffffffu) {
+            const uint32_t dd = tr.digit(k[e]);
+            const uint32_t li = s_lstart[dd] + s_whist[warp][dd] + rank[e];
+            s_key[li] = k[e];
+            s_val[li] = v[e];
+        }
+    }
+    __syncthreads();
+    const int m = (int)min((unsigned)RS_TILE, n - base);     // every element of a staged pass is valid
+    for (int i = tid; i < m; i += RS_THREADS) {
+        const KeyT key = s_key[i];
+        const uint32_t dd = tr.digit(key);
+        const uint32_t pos = s_base[dd] + ((uint32_t)i - s_lstart[dd]);
+        vals_out[pos] = s_val[i];
+        if (keys_out) keys_out[pos] = key;
+        if (ranges) {
+            // all pairs of a tile are contiguous in this pass's output: start = min position, end = max position + 1.
+            // The start is kept as max(~position) so that zero-filled ranges are the identity (launch_tile_order decodes).
+            if (i == 0 || s_key[i - 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].x), ~pos);
+            if (i == m - 1 || s_key[i + 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].y), pos + 1u);
+        }
+    }
+}
+
+template <class TR>
+cudaError_t radix_pass(TR tr, const typename TR::KeyT* keys_in, const uint32_t* vals_in, typename TR::KeyT* keys_out,
+                       uint32_t* vals_out, Count cnt, int blocks, uint32_t* matrix, uint32_t* totals, int2* ranges,
+                       cudaStream_t s) {
+    radix_count_kernel<TR><<<blocks, RS_THREADS, 0, s>>>(tr, keys_in, cnt, blocks, matrix);
+    radix_colscan_kernel<TR><<<(TR::MAXBINS * 32 + RS_THREADS - 1) / RS_THREADS, RS_THREADS, 0, s>>>(tr, cnt, blocks, matrix, totals);
+    radix_scatter_kernel<TR><<<blocks, RS_THREADS, 0, s>>>(tr, keys_in, vals_in, keys_out, vals_out, cnt, blocks, matrix, totals, ranges);
+    return cudaGetLastError();
+}
+
+// ---- inclusive scan (reduce / spine / apply), 4096 elements per block -----------------------------------------
 // tiles touched by the j-th Gaussian of the depth order
 struct TilesInDepthOrder {
     const uint32_t* order;
@@ -42,41 +306,109 @@ struct TilesInIndexOrder {
         return (wh & 0xffffu) * (wh >> 16);
     }
 };
-template <typename Op>
-using TilesIt = cub::TransformInputIterator<uint32_t, Op, cub::CountingInputIterator<uint32_t>>;
 
-size_t scan_temp_bytes(int P) {
-    size_t a = 0, b = 0;
-    TilesIt<TilesInDepthOrder> it(cub::CountingInputIterator<uint32_t>(0), TilesInDepthOrder{nullptr, nullptr});
-    cub::DeviceScan::InclusiveSum(nullptr, a, it, (uint32_t*)nullptr, P > 0 ? P : 1);
-    TilesIt<TilesInIndexOrder> it2(cub::CountingInputIterator<uint32_t>(0), TilesInIndexOrder{nullptr});
-    cub::DeviceScan::InclusiveSum(nullptr, b, it2, (uint32_t*)nullptr, P > 0 ? P : 1);
-    return a > b ? a : b;
+template <class F>
+__global__ void __launch_bounds__(RS_THREADS) scan_reduce_kernel(F f, Count cnt, uint32_t* __restrict__ part) {
+    __shared__ uint32_t s_warp[RS_WARPS];
+    const unsigned n = load_count(cnt);
+    const unsigned base = blockIdx.x * (unsigned)RS_TILE;
+    if (base >= n) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t sum = 0;
+#pragma unroll 4
+    for (int e = 0; e < RS_ITEMS; e++) {
+        const unsigned idx = base + e * RS_THREADS + tid;
+        if (idx < n) sum += f(idx);
+    }
+    sum = __reduce_add_sync(FULLMASK, sum);
+    if (lane == 0) s_warp[warp] = sum;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) t += s_warp[w];
+        part[blockIdx.x] = t;
+    }
 }
 
-size_t depth_sort_temp_bytes(int P) {
-    size_t bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr,
-                                    (uint32_t*)nullptr, P > 0 ? P : 1, 0, 32);
-    return bytes;
+// exclusive scan of the block partials, one block (any number of partials)
+__global__ void __launch_bounds__(1024) scan_spine_kernel(Count cnt, uint32_t* __restrict__ part) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    const unsigned n = load_count(cnt);
+    const int nb = (int)((n + RS_TILE - 1) / RS_TILE);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0u;
+    __syncthreads();
+    for (int b0 = 0; b0 < nb; b0 += 1024) {
+        const int b = b0 + tid;
+        const uint32_t v = b < nb ? part[b] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULLMASK, incl, s);
+            if (lane >= s) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t wb = s_carry;
+        for (int w = 0; w < warp; w++) wb += s_warp[w];
+        if (b < nb) part[b] = wb + incl - v;
+        __syncthreads();
+        if (tid == 1023) s_carry = wb + incl;
+        __syncthreads();
+    }
 }
 
-int tile_bits(int num_tiles) {
-    int bits = 1;
-    while (bits < 32 && ((unsigned)(num_tiles - 1) >> bits) != 0) bits++;
-    return bits;
+template <class F>
+__global__ void __launch_bounds__(RS_THREADS) scan_apply_kernel(F f, Count cnt, const uint32_t* __restrict__ part,
+                                                                uint32_t* __restrict__ out) {
+    __shared__ uint32_t s_warp[RS_WARPS];
+    const unsigned n = load_count(cnt);
+    const unsigned base = blockIdx.x * (unsigned)RS_TILE;
+    if (base >= n) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned wbase = base + warp * (RS_ITEMS * 32);
+    uint32_t v[RS_ITEMS];
+#pragma unroll
+    for (int e = 0; e < RS_ITEMS; e++) {
+        const unsigned idx = wbase + e * 32 + lane;
+        v[e] = idx < n ? f(idx) : 0u;
+    }
+    uint32_t run = 0;
+#pragma unroll
+    for (int e = 0; e < RS_ITEMS; e++) {
+        uint32_t incl = v[e];
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULLMASK, incl, s);
+            if (lane >= s) incl += t;
+        }
+        v[e] = run + incl;
+        run += __shfl_sync(FULLMASK, incl, 31);
+    }
+    if (lane == 0) s_warp[warp] = run;
+    __syncthreads();
+    uint32_t wb = __ldg(part + blockIdx.x);
+    for (int w = 0; w < warp; w++) wb += s_warp[w];
+#pragma unroll
+    for (int e = 0; e < RS_ITEMS; e++) {
+        const unsigned idx = wbase + e * 32 + lane;
+        if (idx < n) out[idx] = wb + v[e];
+    }
 }
 
-template <typename KeyT>
-size_t tile_sort_temp_bytes(int R, int num_tiles) {
-    size_t bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (KeyT*)nullptr, (KeyT*)nullptr, (uint32_t*)nullptr,
-                                    (uint32_t*)nullptr, R > 0 ? R : 1, 0, tile_bits(num_tiles));
-    return bytes;
+template <class F>
+cudaError_t inclusive_scan(F f, Count cnt, int blocks, uint32_t* part, uint32_t* out, cudaStream_t s) {
+    scan_reduce_kernel<F><<<blocks, RS_THREADS, 0, s>>>(f, cnt, part);
+    scan_spine_kernel<<<1, 1024, 0, s>>>(cnt, part);
+    scan_apply_kernel<F><<<blocks, RS_THREADS, 0, s>>>(f, cnt, part, out);
+    return cudaGetLastError();
 }
 
 }  // namespace
 
+// ---- buffer layouts -------------------------------------------------------------------------------------
 GeomView carve_geom(void* base, int P) {
     GeomView g;
     size_t off = 0;
@@ -85,30 +417,35 @@ GeomView carve_geom(void* base, int P) {
     g.depths = (float*)(b + off); off += align256(n * sizeof(float));
     g.rec = (float4*)(b + off); off += align256(n * 3 * sizeof(float4));
     g.rect = (uint2*)(b + off); off += align256(n * sizeof(uint2));
-    g.iota = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
-    g.depth_sorted = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
-    g.order = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.dkey_a = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.dval_a = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.dkey_b = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.dval_b = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.order = g.dval_a;
     g.offsets = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
-    g.scan_tmp_bytes = scan_temp_bytes(P);
-    g.scan_tmp = (void*)(b + off); off += align256(g.scan_tmp_bytes);
-    g.dsort_tmp_bytes = depth_sort_temp_bytes(P);
-    g.dsort_tmp = (void*)(b + off); off += align256(g.dsort_tmp_bytes);
+    g.dblocks = radix_blocks(n);
+    g.scan_part = (uint32_t*)(b + off); off += align256(((size_t)g.dblocks + 1) * sizeof(uint32_t));
+    g.dmatrix = (uint32_t*)(b + off); off += align256((size_t)DEPTH_MAXBINS * g.dblocks * sizeof(uint32_t));
+    g.dtotals = (uint32_t*)(b + off); off += align256((size_t)DEPTH_MAXBINS * sizeof(uint32_t));
     g.total = off;
     return g;
 }
 
-BinView carve_binning(void* base, int R, int num_tiles) {
+BinView carve_binning(void* base, int cap, int num_tiles) {
     BinView v;
     size_t off = 0;
     char* b = (char*)base;
-    size_t n = (size_t)(R > 0 ? R : 1);
+    size_t n = (size_t)(cap > 0 ? cap : 1);
+    v.cap = cap > 0 ? cap : 0;
     v.key_bytes = num_tiles <= 65536 ? 2 : 4;
-    v.keys_unsorted = (void*)(b + off); off += align256(n * v.key_bytes);
-    v.keys_sorted = (void*)(b + off); off += align256(n * v.key_bytes);
-    v.vals_unsorted = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
-    v.vals_sorted = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
-    v.sort_tmp_bytes = v.key_bytes == 2 ? tile_sort_temp_bytes<uint16_t>(R, num_tiles) : tile_sort_temp_bytes<uint32_t>(R, num_tiles);
-    v.sort_tmp = (void*)(b + off); off += align256(v.sort_tmp_bytes);
+    v.key_a = (void*)(b + off); off += align256(n * v.key_bytes);
+    v.val_a = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    v.key_b = (void*)(b + off); off += align256(n * v.key_bytes);
+    v.val_b = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    v.vals_sorted = v.val_a;
+    v.tblocks = radix_blocks(n);
+    v.tmatrix = (uint32_t*)(b + off); off += align256((size_t)TILE_MAXBINS * v.tblocks * sizeof(uint32_t));
+    v.ttotals = (uint32_t*)(b + off); off += align256((size_t)TILE_MAXBINS * sizeof(uint32_t));
     v.total = off;
     return v;
 }
@@ -122,7 +459,7 @@ ImgView carve_image(void* base, int W, int H) {
     v.ranges = (int2*)(b + off); off += align256((T > 0 ? T : 1) * sizeof(int2));
     v.final_T = (float*)(b + off); off += align256((N > 0 ? N : 1) * sizeof(float));
     v.n_contrib = (uint32_t*)(b + off); off += align256((N > 0 ? N : 1) * sizeof(uint32_t));
-    v.counters = (unsigned int*)(b + off); off += align256(64 * sizeof(unsigned int));
+    v.counters = (unsigned int*)(b + off); off += align256(CTR_WORDS * sizeof(unsigned int));
     const size_t Tn = T > 0 ? T : 1;
     v.tile_order = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
     v.total = off;
@@ -136,17 +473,27 @@ constexpr int EMIT_THREADS = 256;
 // Block-cooperative duplicateWithKeys.  Block b owns depth-order positions [256 b, 256 b + 256) and the
 // output slots [offsets[256 b - 1], offsets[256 b + 255]).  Slot k of Gaussian g (rect minx, miny, w, h)
 // is tile (miny + k / w) * gx + minx + k % w: row-major over the rectangle, as the oracle emits.
+// V (visible Gaussians) comes from the control block; slots at or beyond the pair capacity are not written.
 template <typename KeyT>
-__global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int P, int gx, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int gx, const uint32_t* __restrict__ order,
                                                                  const uint2* __restrict__ rect,
                                                                  const uint32_t* __restrict__ offsets,
-                                                                 KeyT* __restrict__ keys, uint32_t* __restrict__ vals) {
+                                                                 KeyT* __restrict__ keys, uint32_t* __restrict__ vals,
+                                                                 unsigned cap, unsigned int* __restrict__ counters) {
     __shared__ uint32_t s_end[EMIT_THREADS];     // inclusive offsets of this block's Gaussians
     __shared__ uint32_t s_id[EMIT_THREADS];
     __shared__ uint2 s_rect[EMIT_THREADS];
     const int tid = threadIdx.x;
+    const int V = (int)__ldg(counters + CTR_VISIBLE);
     const int j0 = blockIdx.x * EMIT_THREADS;
-    const int j = min(j0 + tid, P - 1);
+    if (blockIdx.x == 0 && tid == 0) {           // status of the view (b200splat_forward_status)
+        const unsigned lo = __ldg(counters + CTR_PAIRS), hi = __ldg(counters + CTR_PAIRS + 1);
+        counters[CTR_STATUS] = lo; counters[CTR_STATUS + 1] = hi;
+        counters[CTR_STATUS + 2] = cap;
+        counters[CTR_STATUS + 3] = (hi != 0u || lo > cap) ? 1u : 0u;
+    }
+    if (j0 >= V) return;
+    const int j = min(j0 + tid, V - 1);
     const uint32_t id = __ldg(order + j);
     s_id[tid] = id;
     s_rect[tid] = __ldg(rect + id);
@@ -155,7 +502,7 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int P, int gx, 
     __syncthreads();
     // Each thread owns four consecutive output slots (aligned to 4 so full groups go out as one vector store
     // per array): one binary search and one division for the first slot, then a linear walk.
-    const uint32_t end = s_end[EMIT_THREADS - 1];
+    const uint32_t end = min(s_end[EMIT_THREADS - 1], cap);
     for (uint32_t gs = (base & ~3u) + 4u * tid; gs < end; gs += 4u * EMIT_THREADS) {
         const uint32_t s0 = max(gs, base);
         int lo = 0, hi = EMIT_THREADS - 1;          // first g with s_end[g] > s0
@@ -205,38 +552,11 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int P, int gx, 
     }
 }
 
-// identifyTileRanges: each thread owns EPT consecutive sorted keys (one 16-byte load) plus the key before them.
-template <typename KeyT>
-__global__ void __launch_bounds__(256) identify_tile_ranges_kernel(int R, const KeyT* __restrict__ keys,
-                                                                   int2* __restrict__ ranges) {
-    constexpr int EPT = 16 / sizeof(KeyT);
-    const int j0 = (blockIdx.x * blockDim.x + threadIdx.x) * EPT;
-    if (j0 >= R) return;
-    KeyT k[EPT];
-    if (j0 + EPT <= R) {
-        *reinterpret_cast<uint4*>(k) = *reinterpret_cast<const uint4*>(keys + j0);
-    } else {
-#pragma unroll
-        for (int e = 0; e < EPT; e++) k[e] = j0 + e < R ? keys[j0 + e] : (KeyT)0;
-    }
-    uint32_t prev = j0 > 0 ? (uint32_t)keys[j0 - 1] : 0u;
-    if (j0 == 0) ranges[(uint32_t)k[0]].x = 0;
-#pragma unroll
-    for (int e = 0; e < EPT; e++) {
-        const int j = j0 + e;
-        if (j < R) {
-            const uint32_t t = (uint32_t)k[e];
-            if (j > 0 && t != prev) { ranges[prev].y = j; ranges[t].x = j; }
-            if (j == R - 1) ranges[t].y = R;
-            prev = t;
-        }
-    }
-}
-
 // Tile order for the render kernels: longest list first, to the nearest half power of two (the order only
 // shapes the schedule, never the result).  One block: bucket = 2 log2(len) rounded down, histogram, scan,
-// scatter -- a few microseconds instead of a general sort.
-__global__ void __launch_bounds__(1024) tile_order_kernel(int T, const int2* __restrict__ ranges, uint32_t* __restrict__ order) {
+// scatter -- a few microseconds instead of a general sort.  Also finishes the ranges: the second tile pass left
+// every start as max(~position) (zero for an empty tile), which becomes the start itself here.
+__global__ void __launch_bounds__(1024) tile_order_kernel(int T, int2* __restrict__ ranges, uint32_t* __restrict__ order) {
     __shared__ unsigned s_count[64], s_base[64];
     const int t = threadIdx.x;
     if (t < 64) s_count[t] = 0;
@@ -248,7 +568,9 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(int T, const int2* __r
         return 62 - (2 * lg + half);          // longest lists -> smallest bucket index
     };
     for (int i = t; i < T; i += blockDim.x) {
-        const int2 r = ranges[i];
+        int2 r = ranges[i];
+        r.x = r.y > 0 ? (int)~(unsigned)r.x : 0;
+        ranges[i] = r;
         atomicAdd(&s_count[bucket((unsigned)(r.y - r.x))], 1u);
     }
     __syncthreads();
@@ -263,12 +585,12 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(int T, const int2* __r
     }
 }
 
-template <typename KeyT>
-__global__ void export_keys_kernel(int R, const KeyT* __restrict__ tile_keys, const uint32_t* __restrict__ vals,
-                                   const float* __restrict__ depths, uint64_t* __restrict__ out) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= R) return;
-    out[j] = ((uint64_t)tile_keys[j] << 32) | (uint64_t)__float_as_uint(depths[vals[j]]);
+// parity / inspection: the 64-bit keys (tile << 32 | depth bits) of every sorted pair, rebuilt per tile
+__global__ void __launch_bounds__(128) export_keys_kernel(const int2* __restrict__ ranges, const uint32_t* __restrict__ vals,
+                                                          const float* __restrict__ depths, uint64_t* __restrict__ out) {
+    const int2 r = ranges[blockIdx.x];
+    for (int j = r.x + threadIdx.x; j < r.y; j += blockDim.x)
+        out[j] = ((uint64_t)blockIdx.x << 32) | (uint64_t)__float_as_uint(depths[vals[j]]);
 }
 
 __global__ void export_tiles_kernel(int P, const uint2* __restrict__ rect, uint32_t* __restrict__ out) {
@@ -278,75 +600,83 @@ __global__ void export_tiles_kernel(int P, const uint2* __restrict__ rect, uint3
     out[i] = (wh & 0xffffu) * (wh >> 16);
 }
 
-}  // namespace
-
-cudaError_t launch_depth_order(GeomView gv, int P, cudaStream_t s) {
-    if (P == 0) return cudaSuccess;
-    size_t bytes = gv.dsort_tmp_bytes;
-    cudaError_t e = cub::DeviceRadixSort::SortPairs(gv.dsort_tmp, bytes, reinterpret_cast<const uint32_t*>(gv.depths),
-                                                    gv.depth_sorted, gv.iota, gv.order, P, 0, 32, s);
-    if (e != cudaSuccess) return e;
-    TilesIt<TilesInDepthOrder> it(cub::CountingInputIterator<uint32_t>(0), TilesInDepthOrder{gv.order, gv.rect});
-    bytes = gv.scan_tmp_bytes;
-    return cub::DeviceScan::InclusiveSum(gv.scan_tmp, bytes, it, gv.offsets, P, s);
+__global__ void copy_u32_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, Count cnt) {
+    const unsigned n = load_count(cnt);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = src[i];
 }
 
-cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, cudaStream_t s) {
+}  // namespace
+
+cudaError_t launch_depth_order(GeomView gv, int P, const unsigned int* counters, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    const int blocks = gv.dblocks;
+    const Count all{nullptr, (unsigned)P, 0};                         // first pass: every key, culled ones dropped
+    const Count vis{counters + CTR_VISIBLE, (unsigned)P, 0};          // then the V visible
+    DepthTraits t0{counters, 0}, t1{counters, 1}, t2{counters, 2};
+    cudaError_t e;
+    e = radix_pass(t0, reinterpret_cast<const uint32_t*>(gv.depths), (const uint32_t*)nullptr, gv.dkey_a, gv.dval_a, all, blocks,
+                   gv.dmatrix, gv.dtotals, nullptr, s);
+    if (e != cudaSuccess) return e;
+    e = radix_pass(t1, (const uint32_t*)gv.dkey_a, (const uint32_t*)gv.dval_a, gv.dkey_b, gv.dval_b, vis, blocks, gv.dmatrix,
+                   gv.dtotals, nullptr, s);
+    if (e != cudaSuccess) return e;
+    e = radix_pass(t2, (const uint32_t*)gv.dkey_b, (const uint32_t*)gv.dval_b, (uint32_t*)nullptr, gv.order, vis, blocks, gv.dmatrix,
+                   gv.dtotals, nullptr, s);
+    if (e != cudaSuccess) return e;
+    return inclusive_scan(TilesInDepthOrder{gv.order, gv.rect}, vis, blocks, gv.scan_part, gv.offsets, s);
+}
+
+cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, unsigned int* counters, cudaStream_t s) {
     if (P == 0) return cudaSuccess;
     const int gx = (W + TILE - 1) / TILE;
     const int blocks = (P + EMIT_THREADS - 1) / EMIT_THREADS;
     if (bv.key_bytes == 2)
-        emit_keys_kernel<uint16_t><<<blocks, EMIT_THREADS, 0, s>>>(P, gx, gv.order, gv.rect, gv.offsets,
-                                                                  (uint16_t*)bv.keys_unsorted, bv.vals_unsorted);
+        emit_keys_kernel<uint16_t><<<blocks, EMIT_THREADS, 0, s>>>(gx, gv.order, gv.rect, gv.offsets, (uint16_t*)bv.key_a, bv.val_a,
+                                                                  (unsigned)bv.cap, counters);
     else
-        emit_keys_kernel<uint32_t><<<blocks, EMIT_THREADS, 0, s>>>(P, gx, gv.order, gv.rect, gv.offsets,
-                                                                  (uint32_t*)bv.keys_unsorted, bv.vals_unsorted);
+        emit_keys_kernel<uint32_t><<<blocks, EMIT_THREADS, 0, s>>>(gx, gv.order, gv.rect, gv.offsets, (uint32_t*)bv.key_a, bv.val_a,
+                                                                  (unsigned)bv.cap, counters);
     return cudaGetLastError();
 }
 
-cudaError_t launch_tile_sort(BinView bv, int R, int num_tiles, cudaStream_t s) {
-    if (R == 0) return cudaSuccess;
-    size_t bytes = bv.sort_tmp_bytes;
-    const int bits = tile_bits(num_tiles);
-    if (bv.key_bytes == 2)
-        return cub::DeviceRadixSort::SortPairs(bv.sort_tmp, bytes, (const uint16_t*)bv.keys_unsorted, (uint16_t*)bv.keys_sorted,
-                                               bv.vals_unsorted, bv.vals_sorted, R, 0, bits, s);
-    return cub::DeviceRadixSort::SortPairs(bv.sort_tmp, bytes, (const uint32_t*)bv.keys_unsorted, (uint32_t*)bv.keys_sorted,
-                                           bv.vals_unsorted, bv.vals_sorted, R, 0, bits, s);
+template <typename K>
+static cudaError_t tile_sort_impl(BinView bv, int gx, int gy, ImgView iv, cudaStream_t s) {
+    const Count pairs{iv.counters + CTR_PAIRS, (unsigned)bv.cap, 1};
+    const unsigned long long magic = (1ull << 32) / (unsigned long long)gx + 1ull;
+    TileTraits<K> by_col{gx, gx, 0, magic}, by_row{gx, gy, 1, magic};
+    cudaError_t e = radix_pass(by_col, (const K*)bv.key_a, (const uint32_t*)bv.val_a, (K*)bv.key_b, bv.val_b, pairs, bv.tblocks,
+                               bv.tmatrix, bv.ttotals, nullptr, s);
+    if (e != cudaSuccess) return e;
+    return radix_pass(by_row, (const K*)bv.key_b, (const uint32_t*)bv.val_b, (K*)nullptr, bv.vals_sorted, pairs, bv.tblocks,
+                      bv.tmatrix, bv.ttotals, iv.ranges, s);
 }
 
-cudaError_t launch_ranges(BinView bv, int R, ImgView iv, int W, int H, cudaStream_t s) {
-    const size_t T = (size_t)tiles_of(W, H);
+cudaError_t launch_tile_sort(BinView bv, int W, int H, ImgView iv, cudaStream_t s) {
+    if (bv.cap == 0) return cudaSuccess;
+    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
+    return bv.key_bytes == 2 ? tile_sort_impl<uint16_t>(bv, gx, gy, iv, s) : tile_sort_impl<uint32_t>(bv, gx, gy, iv, s);
+}
+
+int max_tile_bins() { return TILE_MAXBINS; }
+
+cudaError_t launch_tile_order(ImgView iv, int W, int H, cudaStream_t s) {
+    const int T = tiles_of(W, H);
     if (T == 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(iv.ranges, 0, T * sizeof(int2), s);
-    if (e != cudaSuccess) return e;
-    if (R > 0) {
-        if (bv.key_bytes == 2)
-            identify_tile_ranges_kernel<uint16_t><<<(R + 256 * 8 - 1) / (256 * 8), 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, iv.ranges);
-        else
-            identify_tile_ranges_kernel<uint32_t><<<(R + 256 * 4 - 1) / (256 * 4), 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, iv.ranges);
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-    }
     // longest list first: the render kernels' critical path is their heaviest tile
-    tile_order_kernel<<<1, 1024, 0, s>>>((int)T, iv.ranges, iv.tile_order);
+    tile_order_kernel<<<1, 1024, 0, s>>>(T, iv.ranges, iv.tile_order);
     return cudaGetLastError();
 }
 
 // Parity / inspection only: rebuild the 64-bit keys, tiles touched and the index-order offsets.
-cudaError_t launch_export_binning(int P, int R, GeomView gv, BinView bv, const b200splat_state_out& o, cudaStream_t s) {
-    if (o.keys_sorted && R > 0) {
-        if (bv.key_bytes == 2)
-            export_keys_kernel<uint16_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint16_t*)bv.keys_sorted, bv.vals_sorted, gv.depths, o.keys_sorted);
-        else
-            export_keys_kernel<uint32_t><<<(R + 255) / 256, 256, 0, s>>>(R, (const uint32_t*)bv.keys_sorted, bv.vals_sorted, gv.depths, o.keys_sorted);
-    }
+cudaError_t launch_export_binning(int P, int W, int H, GeomView gv, BinView bv, ImgView iv, const b200splat_state_out& o, cudaStream_t s) {
+    const int T = tiles_of(W, H);
+    if (o.keys_sorted && bv.cap > 0 && T > 0) export_keys_kernel<<<T, 128, 0, s>>>(iv.ranges, bv.vals_sorted, gv.depths, o.keys_sorted);
+    if (o.vals_sorted && bv.cap > 0)
+        copy_u32_kernel<<<296, 256, 0, s>>>(bv.vals_sorted, o.vals_sorted, Count{iv.counters + CTR_PAIRS, (unsigned)bv.cap, 1});
     if (o.tiles_touched && P > 0) export_tiles_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, gv.rect, o.tiles_touched);
     if (o.point_offsets && P > 0) {
         // the forward's scan scratch is dead once the forward has finished
-        TilesIt<TilesInIndexOrder> it(cub::CountingInputIterator<uint32_t>(0), TilesInIndexOrder{gv.rect});
-        size_t bytes = gv.scan_tmp_bytes;
-        cudaError_t e = cub::DeviceScan::InclusiveSum(gv.scan_tmp, bytes, it, o.point_offsets, P, s);
+        cudaError_t e = inclusive_scan(TilesInIndexOrder{gv.rect}, Count{nullptr, (unsigned)P, 0}, gv.dblocks, gv.scan_part, o.point_offsets, s);
         if (e != cudaSuccess) return e;
     }
     return cudaGetLastError();

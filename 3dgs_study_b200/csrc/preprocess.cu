@@ -126,13 +126,12 @@ __device__ __forceinline__ void project_cov(const ViewConsts& vc, float tx, floa
 __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_FWD) preprocess_fwd_kernel(PreParams p, float* __restrict__ depths,
                                                                      float4* __restrict__ rec,
                                                                      uint2* __restrict__ rect,
-                                                                     uint32_t* __restrict__ iota,
                                                                      int32_t* __restrict__ radii,
-                                                                     unsigned long long* __restrict__ pair_counter,
+                                                                     unsigned int* __restrict__ counters,
                                                                      int coop, int qs) {
     extern __shared__ float4 s_sh4[];
     __shared__ ViewConsts vc;
-    __shared__ uint32_t s_pairs[PRE_THREADS / 32];
+    __shared__ uint32_t s_pairs[PRE_THREADS / 32], s_vis[PRE_THREADS / 32], s_kmax[PRE_THREADS / 32], s_kminn[PRE_THREADS / 32];
     load_view_consts(vc, p.view, p.proj, p.campos);
     const int i = blockIdx.x * PRE_THREADS + threadIdx.x;
     const bool in_range = i < p.P;
@@ -215,7 +214,7 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_FWD) preprocess_fwd_kern
                 //   ex, ey: half extents of the axis-aligned box of {power >= thr}
                 float thr, ex, ey;
                 if (o > 0.0f) {
-                    thr = -logf(255.0f * o) - THR_MARGIN;
+                    thr = fmaxf(-80.0f, -logf(255.0f * o) - THR_MARGIN);     // >= -80: the argument range of canon_exp
                     const float tau2 = -2.0f * thr;
                     if (tau2 > 0.0f) {
                         // extents of {A dx^2 + 2 B dx dy + C dy^2 <= tau2} for the STORED conic (the one the render
@@ -269,17 +268,32 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_FWD) preprocess_fwd_kern
     if (in_range) {
         radii[i] = radius;
         rect[i] = rc;
-        iota[i] = (uint32_t)i;
-        depths[i] = area ? tz : __uint_as_float(0xffffffffu);   // as u32: the depth-sort key, culled last
+        depths[i] = area ? tz : __uint_as_float(0xffffffffu);   // as u32: the depth-sort key; 0xffffffff = culled
     }
-    // pair count R: one atomic per block
+    // Control block of the view (one atomic per quantity and block, each on its own 128-byte line): pair count R,
+    // visible count V and the range of the depth keys, from which the depth sort derives its digit width.
+    const uint32_t key = __float_as_uint(tz);
     uint32_t sum = __reduce_add_sync(0xffffffffu, area);
-    if ((threadIdx.x & 31) == 0) s_pairs[threadIdx.x >> 5] = sum;
+    uint32_t nvis = __popc(__ballot_sync(0xffffffffu, area != 0));
+    uint32_t kmax = __reduce_max_sync(0xffffffffu, area ? key : 0u);
+    uint32_t kminn = __reduce_max_sync(0xffffffffu, area ? ~key : 0u);
+    if ((threadIdx.x & 31) == 0) {
+        s_pairs[threadIdx.x >> 5] = sum; s_vis[threadIdx.x >> 5] = nvis;
+        s_kmax[threadIdx.x >> 5] = kmax; s_kminn[threadIdx.x >> 5] = kminn;
+    }
     __syncthreads();
     if (threadIdx.x < 32) {
-        sum = threadIdx.x < PRE_THREADS / 32 ? s_pairs[threadIdx.x] : 0u;
-        sum = __reduce_add_sync(0xffffffffu, sum);
-        if (threadIdx.x == 0 && sum) atomicAdd(pair_counter, (unsigned long long)sum);
+        const bool w = threadIdx.x < PRE_THREADS / 32;
+        sum = __reduce_add_sync(0xffffffffu, w ? s_pairs[threadIdx.x] : 0u);
+        nvis = __reduce_add_sync(0xffffffffu, w ? s_vis[threadIdx.x] : 0u);
+        kmax = __reduce_max_sync(0xffffffffu, w ? s_kmax[threadIdx.x] : 0u);
+        kminn = __reduce_max_sync(0xffffffffu, w ? s_kminn[threadIdx.x] : 0u);
+        if (nvis) {
+            if (threadIdx.x == 0) atomicAdd(reinterpret_cast<unsigned long long*>(counters + CTR_PAIRS), (unsigned long long)sum);
+            else if (threadIdx.x == 1) atomicAdd(counters + CTR_VISIBLE, nvis);
+            else if (threadIdx.x == 2) atomicMax(counters + CTR_KMAX, kmax);
+            else if (threadIdx.x == 3) atomicMax(counters + CTR_KMIN_NEG, kminn);
+        }
     }
 }
 
@@ -383,8 +397,10 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
         const float a = pj.cov00 + 0.3f, b = pj.cov01, c = pj.cov11 + 0.3f;
         const float det = a * c - b * b;
         const float d2inv = 1.0f / (det * det + 0.0000001f);
-        float dL_da = d2inv * (-c * c * LA + b * c * LB + (det - a * c) * LC);
-        float dL_dc = d2inv * (-a * a * LC + a * b * LB + (det - a * c) * LA);
+        // det - a c = -b^2 exactly; written that way, because the fp32 difference loses everything for the common
+        // nearly axis-aligned splat (b^2 << a c) and the error is amplified by a / c for an elongated one
+        float dL_da = d2inv * (-c * c * LA + b * c * LB - b * b * LC);
+        float dL_dc = d2inv * (-a * a * LC + a * b * LB - b * b * LA);
         float dL_db = d2inv * (2.f * b * c * LA - (det + 2.f * b * b) * LB + 2.f * a * b * LC);
         if (p.antialiasing) {
             const float det0 = pj.cov00 * pj.cov11 - pj.cov01 * pj.cov01;
@@ -765,6 +781,8 @@ __global__ void gather_counts_kernel(PackedSources src, unsigned* __restrict__ l
     if ((int)threadIdx.x < src.n) local_counts[threadIdx.x] = *reinterpret_cast<const volatile unsigned*>(src.count[threadIdx.x]);
 }
 
+__device__ unsigned g_packed_counts[64];  // local copies of the sources' row counts (gather_counts_kernel)
+
 constexpr int ACC_WARPS = 4;              // warps per block of accumulate_packed_kernel
 constexpr int ACC_RS4 = 13;               // 16-byte words per staged dL/dsh row (odd: conflict-free)
 
@@ -924,7 +942,7 @@ PreParams make_params(const b200splat_view& v, const b200splat_gaussians& g) {
 }  // namespace
 
 cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gaussians& g, GeomView gv,
-                                  int32_t* radii, unsigned long long* pair_counter, cudaStream_t s) {
+                                  int32_t* radii, unsigned int* counters, cudaStream_t s) {
     if (g.P == 0) return cudaSuccess;
     PreParams p = make_params(v, g);
     const int M3 = 3 * g.M;
@@ -935,8 +953,8 @@ cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gauss
         if (e != cudaSuccess) return e;
     }
     cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(p, gv.depths, gv.rec, gv.rect, gv.iota,
-                                                                                         radii, pair_counter, coop, coop_shift(M3 >> 2));
+    preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(p, gv.depths, gv.rec, gv.rect,
+                                                                                         radii, counters, coop, coop_shift(M3 >> 2));
     return cudaGetLastError();
 }
 
@@ -978,10 +996,11 @@ cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, 
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    // per device: two slots of 32 words (store / add launches may be queued back to back), lives as long as the process
-    static thread_local unsigned* counts_buf[64] = {nullptr};
-    if (!counts_buf[dev & 63] && (e = cudaMalloc(&counts_buf[dev & 63], 64 * sizeof(unsigned))) != cudaSuccess) return e;
-    unsigned* lc = counts_buf[dev & 63] + (store ? 32 : 0);
+    // two slots of 32 words (store / add launches may be queued back to back) in the module's own device memory:
+    // nothing is allocated, nothing to free
+    unsigned* lc = nullptr;
+    if ((e = cudaGetSymbolAddress((void**)&lc, g_packed_counts)) != cudaSuccess) return e;
+    lc += store ? 32 : 0;
     gather_counts_kernel<<<1, 32, 0, s>>>(src, lc);
     const bool vec_ok = ((3 * M) & 3) == 0;     // the store flavour relies on the 16-byte path
     if (store && vec_ok && n_src == 1)

@@ -84,6 +84,28 @@ __device__ __forceinline__ float fast_ex2(float x) {
     return r;
 }
 
+// Canonical exponential (DESIGN.md "Canonical arithmetic"; oracle/splat_oracle.c implements the same sequence):
+// the alpha >= 1/255 cutoff and the 1e-4 transmittance exit are discontinuous, so the forward's exp must agree
+// with the oracle's to the bit -- libm-style expf implementations do not (a few flipped pixels per full-size view).
+// Cephes-style: n = round(x log2 e) through the 1.5 * 2^23 trick, r = x - n ln 2 in two fma, degree-7 Horner,
+// 2^n by adding n to the exponent field.  x must lie in [-87, 0]: callers mask lanes whose power is below the
+// record's threshold (>= -80) instead of clamping.
+__device__ __forceinline__ float canon_exp(float x) {
+    const float t = __fmaf_rn(x, 1.4426950408889634f, 12582912.0f);
+    const float n = __fsub_rn(t, 12582912.0f);
+    float r = __fmaf_rn(n, -0.693359375f, x);
+    r = __fmaf_rn(n, 2.12194440e-4f, r);
+    float p = 1.9875691500e-4f;
+    p = __fmaf_rn(p, r, 1.3981999507e-3f);
+    p = __fmaf_rn(p, r, 8.3334519073e-3f);
+    p = __fmaf_rn(p, r, 4.1665795894e-2f);
+    p = __fmaf_rn(p, r, 1.6666665459e-1f);
+    p = __fmaf_rn(p, r, 5.0000001201e-1f);
+    p = __fmaf_rn(p, r, 1.0f);
+    p = __fmaf_rn(p, r, 1.0f);
+    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+
 // Packed pairs of fp32 (sm_100 FFMA2 / FMUL2 / FADD2: two IEEE fp32 results per lane per issue slot).  The render
 // kernels are bound by the issue rate, and the pixels of a lane run the same straight-line arithmetic, so the two
 // pixels of a row go through one instruction stream.
@@ -242,9 +264,10 @@ __global__ void __launch_bounds__(NW * 32) render_fwd_kernel(
                         // a strip's cells.  (Measured: -9 % forward; the backward, tried the same way, gains nothing.)
                         if (NP > 1 && !__any_sync(FULL, pw[s] >= b.w && pw[s] <= 0.0f && T[s] > 0.0f)) continue;
                         // exact tests: power <= 0, alpha >= 1/255, T (1 - alpha) >= 1e-4; a finished pixel has T < 0
-                        const float alpha = fminf(ALPHA_MAX, cmul(c.x, expf(pw[s])));
+                        const float alpha = fminf(ALPHA_MAX, cmul(c.x, canon_exp(pw[s])));
                         const float test_T = cmul(T[s], csub(1.0f, alpha));
-                        const bool valid = alpha >= ALPHA_MIN && pw[s] <= 0.0f;
+                        // power below the threshold: alpha < 1/255 for certain, and canon_exp's argument range ends there
+                        const bool valid = alpha >= ALPHA_MIN && pw[s] <= 0.0f && pw[s] >= b.w;
                         const bool blend = valid && !(test_T < T_EPS);
                         const float w = blend ? cmul(alpha, T[s]) : 0.0f;     // adding c * 0 leaves the sums unchanged
                         C0[s] = cfma(c.y, w, C0[s]);
@@ -586,7 +609,7 @@ __global__ void __launch_bounds__(256) render_stats_kernel(const int2* __restric
             const float power = cfma(dx, cfma(b.x, dx, -cmul(b.y, dy)), cmul(cmul(b.z, dy), dy));
             if (power <= 0.0f && power >= b.w) {
                 ex++;
-                const bool fwd_valid = fminf(ALPHA_MAX, cmul(c.x, expf(power))) >= ALPHA_MIN;
+                const bool fwd_valid = fminf(ALPHA_MAX, cmul(c.x, canon_exp(power))) >= ALPHA_MIN;
                 const bool bwd_valid = -c.x * fast_ex2(power * 1.4426950408889634f) <= -ALPHA_MIN;
                 if (fwd_valid) { co++; contrib = true; }
                 if (fwd_valid != bwd_valid) dis++;

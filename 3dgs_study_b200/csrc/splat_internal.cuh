@@ -3,29 +3,35 @@
 // State layout in HBM (all chunks 256-byte aligned inside the caller-allocated opaque buffers):
 //
 //   geometry buffer (per Gaussian, P entries)
-//     depths   f32[P]        view-space z; culled Gaussians hold the bit pattern 0xFFFFFFFF so that the
-//                            same array, read as u32, is the depth-sort key (culled sort last)
+//     depths   f32[P]        view-space z; culled Gaussians hold the bit pattern 0xFFFFFFFF.  Read as u32 it is the
+//                            depth-sort key (positive floats order like their bit patterns)
 //     rec      float4[3P]    packed 48-byte splat record, gathered by the render kernels:
 //                              rec[3i+0] = (px, py, ex, ey)   pixel centre, half extents of {alpha >= 1/255}
 //                              rec[3i+1] = (hA, B, hC, thr)   hA = -A/2, hC = -C/2 (exact), power threshold
 //                              rec[3i+2] = (o, r, g, b)       effective opacity, colour
 //     rect     uint2[P]      tile rectangle (minx | miny << 16, w | h << 16); w*h = tiles touched (0 = culled)
-//     iota     u32[P]        0..P-1 (value input of the depth sort)
-//     depth_sorted u32[P]    sorted depth keys (scratch), order u32[P] Gaussian ids by (depth, id)
-//     offsets  u32[P]        inclusive scan of tiles touched IN DEPTH ORDER
-//     scan_tmp / dsort_tmp   CUB scratch
-//   binning buffer (per (tile, Gaussian) pair, R entries; tile keys are u16 when T <= 65536, else u32)
-//     keys_unsorted[R], keys_sorted[R], vals_unsorted u32[R], vals_sorted u32[R], sort_tmp
+//     dkey_a/b u32[P] x2, dval_a/b u32[P] x2   ping-pong arrays of the depth sort; after its three passes
+//                            dval_a = `order`: the ids of the V visible Gaussians by (depth bits, id)
+//     offsets  u32[P]        inclusive scan of tiles touched IN DEPTH ORDER (V entries)
+//     scan_part, dmatrix, dtotals   block partials of the scan; digit-count matrix / totals of the depth-sort passes
+//   binning buffer (per (tile, Gaussian) pair, `cap` entries -- the pair CAPACITY, >= the pair count R unless the
+//   overflow flag is raised; tile keys are u16 when T <= 65536, else u32)
+//     key_a[cap], val_a[cap]   pairs as emitted (depth order); val_a is overwritten by the final, sorted ids
+//     key_b[cap], val_b[cap]   pairs after the first (tile column) pass
+//     tmatrix, ttotals         digit-count matrix / totals of the two tile passes
 //   image buffer
 //     ranges   int2[T]       [start, end) of each tile in the sorted list
-//     final_T  f32[H*W], n_contrib u32[H*W], counters u32[64] (work counters; [32..33] = u64 pair count R)
+//     final_T  f32[H*W], n_contrib u32[H*W], tile_order u32[T]
+//     counters u32[256]      control block, every hot word on its own 128-byte line (CTR_* below): pair count R
+//                            (u64), visible count V, min / max depth key, capacity + overflow status
 //
 // Binning order.  The list of every tile must end up sorted by (depth bits, Gaussian id), i.e. exactly
 // the order a stable sort of the 64-bit (tile << 32 | depth) keys emitted in Gaussian order gives.  We
-// get the same order with far less traffic: Gaussians are sorted ONCE by depth (stable, P elements),
-// pairs are emitted in that order with only the tile id as key, and a stable sort on the tile bits
-// (13 bits at 1080p: two 8-bit passes over 6-byte pairs instead of six passes over 12-byte pairs)
-// finishes the job.
+// get the same order with far less traffic: Gaussians are sorted ONCE by depth (stable, V elements),
+// pairs are emitted in that order with only the tile id as key, and a stable two-pass sort on the tile
+// id (by tile column, then by tile row) finishes the job.  Every sort pass and every scan is a kernel of
+// this library (binning.cu); nothing on this path calls a library sort or scan, and nothing waits on the
+// host for R (b200splat.h "pair capacity").
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -50,13 +56,21 @@ inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 int report_error(int code, const char* msg);
 
 struct GeomView {
-    float* depths; float4* rec; uint2* rect; uint32_t* iota; uint32_t* depth_sorted; uint32_t* order;
-    uint32_t* offsets; void* scan_tmp; void* dsort_tmp;
-    size_t scan_tmp_bytes; size_t dsort_tmp_bytes; size_t total;
+    float* depths; float4* rec; uint2* rect;
+    uint32_t* dkey_a; uint32_t* dval_a; uint32_t* dkey_b; uint32_t* dval_b;
+    uint32_t* order;            // = dval_a: result of the depth sort
+    uint32_t* offsets; uint32_t* scan_part;
+    uint32_t* dmatrix; uint32_t* dtotals;
+    int dblocks;                // row stride of dmatrix = radix blocks covering P keys
+    size_t total;
 };
 struct BinView {
-    void* keys_unsorted; void* keys_sorted; uint32_t* vals_unsorted; uint32_t* vals_sorted;
-    void* sort_tmp; size_t sort_tmp_bytes; size_t total; int key_bytes;
+    void* key_a; uint32_t* val_a; void* key_b; uint32_t* val_b;
+    uint32_t* vals_sorted;      // = val_a
+    uint32_t* tmatrix; uint32_t* ttotals;
+    int tblocks;                // row stride of tmatrix = radix blocks covering cap pairs
+    int cap;
+    size_t total; int key_bytes;
 };
 struct ImgView {
     int2* ranges; float* final_T; uint32_t* n_contrib; unsigned int* counters;
@@ -65,19 +79,29 @@ struct ImgView {
 };
 
 GeomView carve_geom(void* base, int P);
-BinView carve_binning(void* base, int R, int num_tiles);
+BinView carve_binning(void* base, int cap, int num_tiles);
 ImgView carve_image(void* base, int W, int H);
 inline int tiles_of(int W, int H) { return ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE); }
-constexpr int CTR_RENDER_FWD = 0, CTR_RENDER_BWD = 16, CTR_PAIRS = 32;   // slots of ImgView::counters
+// slots of ImgView::counters (u32 index); each group sits on its own 128-byte line
+constexpr int CTR_WORDS = 256;
+constexpr int CTR_PAIRS = 32;      // u64: pair count R = sum of tiles touched
+constexpr int CTR_VISIBLE = 64;    // V = Gaussians with tiles touched > 0
+constexpr int CTR_KMIN_NEG = 96;   // max over visible of ~depth key  (min key = ~this; 0 = none)
+constexpr int CTR_KMAX = 128;      // max over visible of depth key
+constexpr int CTR_STATUS = 160;    // written by the emit stage: [0..1] R (u64), [2] pair capacity of the binning buffer,
+                                   // [3] 1 if R > capacity: the view's outputs are unspecified (never out of bounds)
+int max_tile_bins();               // tile columns / rows the tile sort supports
 
 // ---- stage launchers (each enqueues on `s`, returns the launch status) ---------------------------
-// preprocess also accumulates the pair count R into pair_counter (u64, zeroed by the caller)
+// preprocess also accumulates R, V and the min / max depth key into iv.counters (cleared by the caller)
 cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gaussians& g, GeomView gv,
-                                  int32_t* radii, unsigned long long* pair_counter, cudaStream_t s);
-cudaError_t launch_depth_order(GeomView gv, int P, cudaStream_t s);   // depth sort + scan of tiles in that order
-cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, cudaStream_t s);
-cudaError_t launch_tile_sort(BinView bv, int R, int num_tiles, cudaStream_t s);
-cudaError_t launch_ranges(BinView bv, int R, ImgView iv, int W, int H, cudaStream_t s);
+                                  int32_t* radii, unsigned int* counters, cudaStream_t s);
+// stable sort of the visible Gaussians by (depth bits, id) + inclusive scan of tiles touched in that order
+cudaError_t launch_depth_order(GeomView gv, int P, const unsigned int* counters, cudaStream_t s);
+cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, unsigned int* counters, cudaStream_t s);
+// stable sort of the pairs by tile id (two passes) + tile ranges + tile order; iv.ranges cleared by the caller
+cudaError_t launch_tile_sort(BinView bv, int W, int H, ImgView iv, cudaStream_t s);
+cudaError_t launch_tile_order(ImgView iv, int W, int H, cudaStream_t s);
 cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, ImgView iv, float* out_color,
                               float* out_invdepth, cudaStream_t s);
 // packed per-Gaussian gradient accumulator written by the render backward, 12 floats / Gaussian:
@@ -107,7 +131,7 @@ cudaError_t launch_densify_stats(int P, const float* dmeans2D, const int32_t* ra
                                  float* max_radii, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
 cudaError_t launch_export_geom(int P, const int32_t* radii, GeomView gv, const b200splat_state_out& o, cudaStream_t s);
-cudaError_t launch_export_binning(int P, int R, GeomView gv, BinView bv, const b200splat_state_out& o, cudaStream_t s);
+cudaError_t launch_export_binning(int P, int W, int H, GeomView gv, BinView bv, ImgView iv, const b200splat_state_out& o, cudaStream_t s);
 
 // ---- canonical fp32 arithmetic (DESIGN.md "Canonical arithmetic") --------------------------------
 // Every rounding point is an explicit intrinsic, so the compiler can neither contract nor

@@ -50,7 +50,7 @@ class _ForwardOut(ctypes.Structure):
 
 class _Allocators(ctypes.Structure):
     _fields_ = [("alloc", _alloc_fn_t), ("geom_ctx", ctypes.c_void_p), ("binning_ctx", ctypes.c_void_p),
-                ("image_ctx", ctypes.c_void_p)]
+                ("image_ctx", ctypes.c_void_p), ("bin_capacity", ctypes.c_int64)]
 
 
 class StageTimes(ctypes.Structure):
@@ -130,6 +130,12 @@ def lib():
         L.b200splat_render_stats.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.c_void_p]
+        L.b200splat_forward_status.restype = ctypes.c_int
+        L.b200splat_forward_status.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p,
+                                               ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_image_status_offset.restype = ctypes.c_size_t
+        L.b200splat_image_status_offset.argtypes = [ctypes.c_int32, ctypes.c_int32]
+        L.b200splat_shutdown.restype = None
         L.b200splat_export_state.restype = ctypes.c_int
         L.b200splat_export_state.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -202,10 +208,48 @@ def _stream_ptr(device) -> int:
     return int(torch.cuda.current_stream(device).cuda_stream)
 
 
+# ---- pair capacity policy (include/b200splat.h "Pair capacity") ------------------------------------------------
+# The first view of a (device, P, W, H) configuration is rendered in exact mode (one host round trip for the pair
+# count R).  Every later view gets a binning buffer sized from the largest R seen so far with head room and is
+# enqueued WITHOUT waiting for the device; its status words {R, capacity, overflow} are copied to pinned host
+# memory behind it and looked at when the next view is about to be enqueued -- by then they have long landed.
+# An overflow (R grew by more than the head room from one view to the next) therefore surfaces one call late, as a
+# RuntimeError, the way an asynchronous CUDA error does; B200SPLAT_EXACT=1 (or exact=True) turns the policy off.
+_CAP_HEADROOM, _CAP_SLACK, _CAP_QUANTUM = 1.5, 1 << 18, 1 << 16
+_cap_state = {}
+
+
+def _grow(R: int) -> int:
+    c = int(R * _CAP_HEADROOM) + _CAP_SLACK
+    return min((c + _CAP_QUANTUM - 1) // _CAP_QUANTUM * _CAP_QUANTUM, 0x7fffffff)
+
+
+def reset_capacity_policy():
+    """Forget the pair-capacity history (the next view of every configuration is rendered in exact mode again)."""
+    _cap_state.clear()
+
+
+def forward_status(imageBuffer, image_height, image_width):
+    """-> (R, capacity, overflow) of the view whose image buffer is given (b200splat_forward_status; synchronises)."""
+    dev = imageBuffer.device
+    R, cap, over = ctypes.c_int64(0), ctypes.c_int64(0), ctypes.c_int32(0)
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_forward_status(_ptr(imageBuffer), int(image_width), int(image_height), ctypes.byref(R),
+                                            ctypes.byref(cap), ctypes.byref(over), _stream_ptr(dev))
+    _check(rc, "forward_status")
+    return int(R.value), int(cap.value), bool(over.value)
+
+
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                        prefiltered, debug, antialiasing=False, want_invdepth=False, stage_times: StageTimes = None):
-    """-> (num_rendered, out_color [3,H,W], radii [P] i32, geomBuffer, binningBuffer, imgBuffer, invdepth|None)"""
+                        prefiltered, debug, antialiasing=False, want_invdepth=False, stage_times: StageTimes = None,
+                        exact: Optional[bool] = None, bin_capacity: Optional[int] = None):
+    """-> (num_rendered, out_color [3,H,W], radii [P] i32, geomBuffer, binningBuffer, imgBuffer, invdepth|None)
+
+    num_rendered is the pair capacity of the binning buffer (what the backward needs): the exact pair count R when
+    the view was rendered in exact mode, an upper bound otherwise; forward_status(imgBuffer, H, W) gives R itself.
+    exact=True: wait for R (one host round trip).  bin_capacity=n: allocate for n pairs, never wait, the caller
+    checks forward_status for overflow.  Neither (default): the capacity policy above."""
     if not means3D.is_cuda:
         raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
     dev = means3D.device
@@ -226,6 +270,33 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     campos = _f32c(campos, "campos", dev)
     M = int(sh.shape[1]) if sh is not None else 0
 
+    # ---- capacity of the binning buffer
+    st = None
+    if bin_capacity is not None:
+        cap = int(bin_capacity)
+        if cap <= 0:
+            raise RuntimeError("bin_capacity must be positive")
+    elif exact or (exact is None and os.environ.get("B200SPLAT_EXACT") == "1") or debug or stage_times is not None or P == 0:
+        cap = 0
+    else:
+        key = (dev.index if dev.index is not None else torch.cuda.current_device(), P, W, H)
+        st = _cap_state.get(key)
+        if st is None:
+            cap = 0
+            st = _cap_state[key] = {"hint": 0, "pinned": torch.zeros(4, dtype=torch.int32).pin_memory(), "pending": False}
+        else:
+            if st["pending"]:
+                lo, hi, cap_prev, over = (int(x) & 0xffffffff for x in st["pinned"].tolist())
+                R_prev = lo | (hi << 32)
+                st["hint"] = max(st["hint"], _grow(R_prev))
+                if over:
+                    st["pending"] = False
+                    raise RuntimeError(
+                        f"b200splat: the PREVIOUS forward call on this device produced {R_prev} (tile, Gaussian) pairs, more than the "
+                        f"{cap_prev} its binning buffer was sized for; its image and everything derived from it are invalid. "
+                        "The capacity has been raised; re-render that view, or set B200SPLAT_EXACT=1.")
+            cap = st["hint"]
+
     out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
     radii = torch.empty((P,), dtype=torch.int32, device=dev)
     invdepth = torch.empty((1, H, W), dtype=torch.float32, device=dev) if want_invdepth else None
@@ -237,7 +308,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                    _ptr(cov3D_precomp))
     out = _ForwardOut(_ptr(out_color), _ptr(radii), _ptr(invdepth))
     ta = _TensorAllocator(dev)
-    allocs = _Allocators(ta.cb, 1, 2, 3)
+    allocs = _Allocators(ta.cb, 1, 2, 3, cap)
     num_rendered = ctypes.c_int32(0)
     with torch.cuda.device(dev):
         rc = lib().b200splat_forward(ctypes.addressof(view), ctypes.addressof(g), ctypes.addressof(out),
@@ -249,7 +320,15 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         raise ta.error
     _check(rc, "forward")
     empty = torch.empty(0, dtype=torch.uint8, device=dev)
-    return (int(num_rendered.value), out_color, radii, bufs.get(1, empty), bufs.get(2, empty), bufs.get(3, empty), invdepth)
+    img = bufs.get(3, empty)
+    if st is not None:
+        if cap == 0:                   # the exact first view: R is known on the host
+            st["hint"] = _grow(int(num_rendered.value))
+        else:                          # status words follow the view to pinned memory; read before the next one
+            off = lib().b200splat_image_status_offset(W, H)
+            st["pinned"].copy_(img[off:off + 16].view(torch.int32), non_blocking=True)
+            st["pending"] = True
+    return (int(num_rendered.value), out_color, radii, bufs.get(1, empty), bufs.get(2, empty), img, invdepth)
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
@@ -504,10 +583,11 @@ def render_stats(P, W, H, num_rendered, geomBuffer, binningBuffer, imageBuffer):
 
 
 def export_state(P, W, H, num_rendered, radii, geomBuffer, binningBuffer, imageBuffer):
-    """Parity/inspection helper: unpack the opaque forward state into named tensors."""
+    """Parity/inspection helper: unpack the opaque forward state into named tensors.  num_rendered: as returned by
+    rasterize_gaussians (the pair capacity); the sorted lists hold the view's true pair count R entries ("R")."""
     dev = radii.device
     T = ((W + 15) // 16) * ((H + 15) // 16)
-    R = int(num_rendered)
+    R = forward_status(imageBuffer, H, W)[0] if imageBuffer.numel() else 0
     o = {
         "means2D": torch.zeros((P, 2), dtype=torch.float32, device=dev),
         "depths": torch.zeros((P,), dtype=torch.float32, device=dev),
@@ -523,7 +603,8 @@ def export_state(P, W, H, num_rendered, radii, geomBuffer, binningBuffer, imageB
     }
     so = _StateOut(*[_ptr(o[n]) for n, _ in _StateOut._fields_])
     with torch.cuda.device(dev):
-        rc = lib().b200splat_export_state(P, W, H, R, _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
+        rc = lib().b200splat_export_state(P, W, H, int(num_rendered), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer),
                                           _ptr(imageBuffer), ctypes.addressof(so), _stream_ptr(dev))
     _check(rc, "export_state")
+    o["R"] = R
     return o

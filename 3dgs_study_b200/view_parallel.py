@@ -503,11 +503,12 @@ class ViewParallelStep:
 
     # -- measurement helpers (CUDA path only) ------------------------------------------------------------
     def launches_per_view(self=None) -> int:
-        """Kernels of THIS library launched per view fwd+bwd: preprocess, duplicateWithKeys (emit), identifyTileRanges,
-        tile order, render fwd, render bwd, compaction of the touched Gaussians, per-Gaussian bwd, densification
-        statistics -- plus, in the packed exchange, the count gather + accumulate kernels for the rank's own rows and
-        for its peers' (CUB scan / sort passes and memsets are library / driver work and are not counted)."""
-        n = 9
+        """Kernels of THIS library launched per view fwd+bwd (memsets are driver work and are not counted): preprocess 1;
+        depth order 3 radix passes x (count, column scan, scatter) = 9; offsets scan 3; duplicateWithKeys 1; tile sort
+        2 passes x 3 = 6; tile order 1; render forward 1; render backward, compaction of the touched Gaussians,
+        per-Gaussian backward 3; densification statistics 1 -- plus, in the packed exchange, the count gather +
+        accumulate kernels for the rank's own rows and for its peers'."""
+        n = 1 + 9 + 3 + 1 + 6 + 1 + 1 + 3 + 1
         if self is not None and getattr(self, "exchange", None) == "packed":
             n += 2 + (2 if self.world_size > 1 else 0)
         return n
@@ -519,12 +520,16 @@ class ViewParallelStep:
         C = dgr._C
         lv = GaussianParams(*[t.detach() for t in self.leaves])
         acc, stats = {}, {}
+        cap = None          # first pass: exact (waits for R); timed passes: that R with head room, no host wait
         for it in range(iters + 1):
             st = C.StageTimes()
             res = C.rasterize_gaussians(self.bg, lv.means3D, None, lv.opacities, lv.scales, lv.rotations,
                                         self.scale_modifier, None, cam.world_view_transform, cam.full_proj_transform,
                                         cam.tanfovx, cam.tanfovy, cam.image_height, cam.image_width, lv.shs,
-                                        self.sh_degree, cam.camera_center, False, False, stage_times=st)
+                                        self.sh_degree, cam.camera_center, False, False, stage_times=st,
+                                        exact=cap is None, bin_capacity=cap)
+            if cap is None:
+                cap = max(1, int(1.25 * res[0]) + 65536)
             R, color, radii, geom, binning, img, _ = res
             g = C.rasterize_gaussians_backward(self.bg, lv.means3D, radii, None, lv.scales, lv.rotations,
                                            self.scale_modifier, None, cam.world_view_transform,
@@ -532,7 +537,7 @@ class ViewParallelStep:
                                            cam.camera_center, geom, R, binning, img, False, opacities=lv.opacities,
                                            image_height=cam.image_height, image_width=cam.image_width, stage_times=st)
             if it == 0:
-                stats = {"visible": int((radii > 0).sum().item()), "R": int(R),
+                stats = {"visible": int((radii > 0).sum().item()), "R": C.forward_status(img, cam.image_height, cam.image_width)[0],
                          "touched": int((g[3].abs().sum(dim=1) > 0).sum().item())}
                 stats.update(C.render_stats(lv.means3D.shape[0], cam.image_width, cam.image_height, R, geom, binning, img))
                 continue   # first pass is warm-up

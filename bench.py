@@ -41,9 +41,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "classic"],
-                    help="classic = this repo's baseline-algorithm comparator build (tools/build_classic.sh); a stand-in, "
-                         "not the reference")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
@@ -580,20 +578,9 @@ def main():
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py (impl ours) needs a CUDA GPU: the product has no CPU fallback")
-    if a.impl == "classic":
-        lib = os.path.join(ROOT, "3dgs_study_b200", "variants", "libb200splat_classic.so")
-        if not os.path.exists(lib):
-            raise SystemExit("build the comparator first: tools/build_classic.sh")
-        os.environ["B200SPLAT_LIB"] = lib
     line = run_ours(a)
     if line is None:
         return
-    if a.impl == "classic":
-        line["impl"] = "classic"
-        line["note"] = ("baseline-algorithm comparator of THIS repo (csrc/classic/): 64-bit key sort over all bits, blocking pair-count "
-                        "read-back, one thread per pixel, nine global atomics per (pixel, Gaussian) in the backward; a stand-in, "
-                        "not the reference's rasterizer (unavailable on this box)")
-        line.pop("roofline", None)
     if int(os.environ.get("WORLD_SIZE", "1")) == 1 and not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_quick(a)
         try:

@@ -23,14 +23,30 @@
  * Memory: every pointer in b200splat_view / b200splat_gaussians / outputs / gradients is a DEVICE
  * pointer owned by the caller, valid on `stream`'s device.  Scratch that must survive until the
  * backward pass is obtained through the caller's allocator callbacks (one per opaque buffer), so
- * the caller's caching allocator owns it.  The library keeps no state between calls except a
- * thread-local error string.
+ * the caller's caching allocator owns it.
  *
- * Threading / streams: re-entrant; all work is enqueued on `stream` (a cudaStream_t passed as
- * void*).  b200splat_forward waits ONCE on the host for the number of tile/Gaussian pairs (needed to
- * size the binning buffer, like the call it replaces), but it waits on an event recorded right after
- * the preprocess kernel while the depth sort is already queued behind it, so the device does not idle.
- * Per host thread the library keeps one pinned 8-byte slot and one event for that hand-off.
+ * State: the library keeps no state between calls except, per host thread, an error string and (once a backward
+ * pass has run) one helper stream + two events per device; b200splat_shutdown() releases those.
+ * b200splat_accumulate_packed stages the row counts of its sources in 256 bytes of the module's own device memory
+ * and is therefore not to be called concurrently from several host threads on the same device.
+ *
+ * Threading / streams: re-entrant; all work is enqueued on `stream` (a cudaStream_t passed as void*).
+ *
+ * Pair capacity.  The binning buffer holds one entry per (tile, Gaussian) pair; their number R is only known on
+ * the device, after the preprocess kernel.  The call being replaced reads R back and blocks the host once per
+ * view.  Here the caller chooses (b200splat_allocators.bin_capacity):
+ *   bin_capacity == 0   exact: ONE host round trip for R (after the preprocess kernel and the depth sort have been
+ *                       queued), the binning buffer is allocated for exactly R pairs, *num_rendered = R.
+ *   bin_capacity  > 0   the binning buffer is allocated for that many pairs before R is known and the call never
+ *                       waits for the device: R stays in the image buffer's control block, where the binning and
+ *                       render kernels read it.  *num_rendered = bin_capacity (the value the backward needs to find
+ *                       its way around the binning buffer).  If a view produces more pairs than the capacity, no
+ *                       kernel writes out of bounds, the view's outputs are unspecified, and the overflow is
+ *                       recorded: b200splat_forward_status reports R, the capacity and the flag (the same four
+ *                       words can be copied asynchronously from the image buffer at b200splat_image_status_offset).
+ *                       A caller that renders a sequence of similar views sizes the capacity from the R of the
+ *                       previous views with head room and checks the flag one call late -- the policy of the
+ *                       Python operator in this repo (diff_gaussian_rasterization/_C.py).
  */
 #ifndef B200SPLAT_H
 #define B200SPLAT_H
@@ -42,7 +58,7 @@
 extern "C" {
 #endif
 
-#define B200SPLAT_VERSION 2
+#define B200SPLAT_VERSION 3
 
 #if defined(__GNUC__)
 #define B200SPLAT_API __attribute__((visibility("default")))
@@ -105,26 +121,40 @@ typedef struct b200splat_allocators {
     void* geom_ctx;
     void* binning_ctx;
     void* image_ctx;
+    int64_t bin_capacity;   /* 0: exact (one host round trip for R); > 0: pairs to allocate for, no host wait */
 } b200splat_allocators;
 
 /* Optional per-stage device times in milliseconds (NULL to skip).  Requesting them adds one
  * synchronisation at the end of the call. */
 typedef struct b200splat_stage_times {
     float preprocess_ms;
-    float scan_ms;       /* depth order: stable sort of the Gaussians by depth + scan of tiles touched */
-    float duplicate_ms;  /* duplicateWithKeys (includes any host wait for the pair count)              */
-    float sort_ms;       /* stable sort of the (tile, Gaussian) pairs on the tile bits                 */
-    float ranges_ms;
+    float scan_ms;       /* depth order: stable sort of the visible Gaussians by depth + scan of tiles touched */
+    float duplicate_ms;  /* duplicateWithKeys (in exact mode: includes the host round trip for the pair count)  */
+    float sort_ms;       /* stable sort of the (tile, Gaussian) pairs by tile id, tile ranges                   */
+    float ranges_ms;     /* tile order                                                                          */
     float render_ms;
     float render_bwd_ms;
     float preprocess_bwd_ms;
 } b200splat_stage_times;
 
-/* Forward.  On success *num_rendered = number of (tile, Gaussian) pairs R. */
+/* Forward.  On success *num_rendered = the pair capacity of the binning buffer: the number of (tile, Gaussian)
+ * pairs R in exact mode, alloc->bin_capacity otherwise ("Pair capacity" above).  Pass it unchanged to the backward.
+ * Images up to 8192 x 8192 pixels. */
 B200SPLAT_API int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g,
                       const b200splat_forward_out* out, const b200splat_allocators* alloc,
                       int32_t* num_rendered, b200splat_stage_times* times /* nullable */,
                       void* stream);
+
+/* Pair count R, pair capacity and overflow flag of the view whose image buffer is given.  Synchronises `stream`.
+ * Any output pointer may be NULL. */
+B200SPLAT_API int b200splat_forward_status(const void* image, int32_t width, int32_t height, int64_t* num_pairs,
+                      int64_t* capacity, int32_t* overflow, void* stream);
+/* Byte offset, inside the image buffer, of the four u32 status words {R low, R high, capacity, overflow} the forward
+ * leaves there: a caller may copy them to pinned host memory on its own stream instead of synchronising. */
+B200SPLAT_API size_t b200splat_image_status_offset(int32_t width, int32_t height);
+
+/* Releases what the calling host thread holds inside the library (helper streams and events). */
+B200SPLAT_API void b200splat_shutdown(void);
 
 /* Gradient outputs; each pointer may be NULL if the caller does not need it, except
  * dL_dmeans3D.  Every non-NULL output is fully written (zeros for culled Gaussians): the caller
@@ -191,6 +221,8 @@ typedef struct b200splat_state_out {
     uint32_t* n_contrib;      /* [H,W]                                    */
 } b200splat_state_out;
 
+/* num_rendered: the value the forward returned (the pair capacity); keys_sorted / vals_sorted need room for R
+ * entries (b200splat_forward_status). */
 B200SPLAT_API int b200splat_export_state(int32_t P, int32_t width, int32_t height, int32_t num_rendered,
                            const int32_t* radii, const void* geom, const void* binning,
                            const void* image, const b200splat_state_out* out, void* stream);

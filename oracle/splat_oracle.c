@@ -314,6 +314,34 @@ ORC_API int64_t orc_bin(int P, int W, int H, const float* means2D, const float* 
     return n;
 }
 
+/* Canonical exponential (DESIGN.md "Canonical arithmetic").  The blend loop is discontinuous in alpha = o exp(power)
+ * (the 1/255 cutoff) and in the running transmittance (the 1e-4 exit), so two exp implementations that differ in
+ * the last bit -- glibc's expf and CUDA's expf do -- flip a decision once in ~10^7 evaluations, i.e. a few pixels
+ * per full-size view, each by up to 4e-3.  exp is therefore part of the canonical arithmetic: range reduction by
+ * ln 2 in two pieces and a degree-7 polynomial (the Cephes expf scheme), every operation an fp32 fma / add with
+ * one rounding, identical here and in render_tiles.cu (canon_exp).  <= 0.89 ulp from the true exp on [-20, 0]. */
+static inline float canon_exp(float x) {
+    x = fmaxf(x, -80.0f);
+    float t = fmaf(x, 1.4426950408889634f, 12582912.0f);      /* 1.5 * 2^23: the low bits of t are round(x log2 e) */
+    float n = t - 12582912.0f;
+    float r = fmaf(n, -0.693359375f, x);
+    r = fmaf(n, 2.12194440e-4f, r);
+    float p = 1.9875691500e-4f;
+    p = fmaf(p, r, 1.3981999507e-3f);
+    p = fmaf(p, r, 8.3334519073e-3f);
+    p = fmaf(p, r, 4.1665795894e-2f);
+    p = fmaf(p, r, 1.6666665459e-1f);
+    p = fmaf(p, r, 5.0000001201e-1f);
+    p = fmaf(p, r, 1.0f);
+    p = fmaf(p, r, 1.0f);
+    uint32_t tb, pb;
+    memcpy(&tb, &t, 4); memcpy(&pb, &p, 4);
+    pb += tb << 23;                                            /* times 2^n: n added to the exponent field */
+    float out; memcpy(&out, &pb, 4);
+    return out;
+}
+ORC_API float orc_canon_exp(float x) { return canon_exp(x); }
+
 /* ------------------------------------------------------------------------------------------ */
 /* Render forward                                                                              */
 /* ------------------------------------------------------------------------------------------ */
@@ -351,7 +379,7 @@ HOT ORC_API void orc_render(int W, int H, const int32_t* ranges, const uint32_t*
                 float dx, dy;
                 float power = gauss_power(means2D[2 * id], means2D[2 * id + 1], co[0], co[1], co[2], pxf, pyf, &dx, &dy);
                 if (power > 0.0f) continue;
-                float alpha = fminf(0.99f, co[3] * expf(power));
+                float alpha = fminf(0.99f, co[3] * canon_exp(power));
                 if (alpha < 1.0f / 255.0f) continue;
                 float test_T = T * (1.0f - alpha);
                 if (test_T < 0.0001f) break;
@@ -414,7 +442,7 @@ HOT ORC_API void orc_render_backward(int P, int W, int H, const int32_t* ranges,
                 float dxf, dyf;
                 float power = gauss_power(means2D[2 * id], means2D[2 * id + 1], co[0], co[1], co[2], pxf, pyf, &dxf, &dyf);
                 if (power > 0.0f) continue;
-                float Gf = expf(power);
+                float Gf = canon_exp(power);
                 float alphaf = fminf(0.99f, co[3] * Gf);
                 if (alphaf < 1.0f / 255.0f) continue;
                 double G = Gf, alpha = alphaf, dx = dxf, dy = dyf;
@@ -539,8 +567,8 @@ ORC_API void orc_preprocess_backward(
         double LA = dL_dconic[3 * i], LB = dL_dconic[3 * i + 1], LC = dL_dconic[3 * i + 2];
         double dL_da = 0, dL_db = 0, dL_dc = 0;
         double d2inv = 1.0 / (det * det + 0.0000001);
-        dL_da = d2inv * (-c * c * LA + b * c * LB + (det - a * c) * LC);
-        dL_dc = d2inv * (-a * a * LC + a * b * LB + (det - a * c) * LA);
+        dL_da = d2inv * (-c * c * LA + b * c * LB - b * b * LC);   /* det - a c = -b^2 */
+        dL_dc = d2inv * (-a * a * LC + a * b * LB - b * b * LA);
         dL_db = d2inv * (2.0 * b * c * LA - (det + 2.0 * b * b) * LB + 2.0 * a * b * LC);
 
         double dLo = dL_dopacity_io[i];

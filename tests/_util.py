@@ -103,7 +103,7 @@ class Case:
         torch.cuda.synchronize()
         return color, radii, invdepth, grads
 
-    def cuda_state(self, device="cuda:0", want_invdepth=False):
+    def cuda_state(self, device="cuda:0", want_invdepth=False, exact=True, bin_capacity=None):
         """Forward through `_C.rasterize_gaussians` and unpack the opaque state for the integer gates."""
         import diff_gaussian_rasterization as dgr
         dev = torch.device(device)
@@ -114,8 +114,9 @@ class Case:
                                          None if cov is not None else s.scales, None if cov is not None else s.rotations,
                                          self.mod, cov, c.world_view_transform, c.full_proj_transform, c.tanfovx, c.tanfovy,
                                          self.H, self.W, None if colors is not None else s.shs, self.D, c.camera_center,
-                                         False, False, antialiasing=self.aa, want_invdepth=want_invdepth)
-        R, color, radii, geom, binning, img, invd = res
-        st = dgr._C.export_state(self.P, self.W, self.H, R, radii, geom, binning, img)
+                                         False, False, antialiasing=self.aa, want_invdepth=want_invdepth, exact=exact,
+                                         bin_capacity=bin_capacity)
+        cap, color, radii, geom, binning, img, invd = res
+        st = dgr._C.export_state(self.P, self.W, self.H, cap, radii, geom, binning, img)
         torch.cuda.synchronize()
-        return R, color, radii, invd, st
+        return st["R"], color, radii, invd, st

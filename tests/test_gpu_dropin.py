@@ -22,25 +22,29 @@ synth = importlib.import_module("3dgs_study_b200.synth")
 
 
 class _Model:
-    """The slice of GaussianModel that render() touches (/root/reference/scene/gaussian_model.py:92-125)."""
+    """The slice of GaussianModel that render() touches (/root/reference/scene/gaussian_model.py:35-61, 92-125):
+    raw parameters and the activations the getters apply -- exp (scaling), normalize (rotation), sigmoid (opacity)."""
 
     def __init__(self, sc, dev, max_sh_degree, active_sh_degree):
         self.max_sh_degree, self.active_sh_degree = max_sh_degree, active_sh_degree
+        g = torch.Generator().manual_seed(99)
         self._xyz = sc.means3D.to(dev).clone().requires_grad_()
-        self._features = sc.shs.to(dev).clone().requires_grad_()           # [P, M, 3]
-        self._opacity = sc.opacities.to(dev).clone().requires_grad_()
-        self._scaling = sc.scales.to(dev).clone().requires_grad_()
-        self._rotation = sc.rotations.to(dev).clone().requires_grad_()
+        self._features = sc.shs.to(dev).clone().requires_grad_()           # [P, M, 3] = cat(features_dc, features_rest)
+        o = sc.opacities.clamp(1e-4, 1 - 1e-4)
+        self._opacity = torch.log(o / (1 - o)).to(dev).requires_grad_()     # inverse_sigmoid
+        self._scaling = torch.log(sc.scales).to(dev).requires_grad_()
+        # raw quaternions are NOT unit length in a trained model: the getter normalises
+        self._rotation = (sc.rotations * (0.5 + torch.rand(sc.rotations.shape[0], 1, generator=g))).to(dev).requires_grad_()
 
     get_xyz = property(lambda s: s._xyz)
     get_features = property(lambda s: s._features)
-    get_opacity = property(lambda s: s._opacity)
-    get_scaling = property(lambda s: s._scaling)
-    get_rotation = property(lambda s: s._rotation)
+    get_opacity = property(lambda s: torch.sigmoid(s._opacity))
+    get_scaling = property(lambda s: torch.exp(s._scaling))
+    get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))
 
     def get_covariance(self, scaling_modifier=1.0):
         from oracle import torch_ref as tr
-        return tr.build_covariance(self._scaling, scaling_modifier, self._rotation)
+        return tr.build_covariance(self.get_scaling, scaling_modifier, self._rotation)   # gaussian_model.py:116-118
 
     def leaves(self):
         return {"xyz": self._xyz, "features": self._features, "opacity": self._opacity, "scaling": self._scaling,
@@ -95,6 +99,7 @@ def _one(pipe_kw, P=6000, W=320, H=200, max_deg=3, active=3, seed=4, debug=False
     dL = synth.make_grad_image(W, H, seed=9).to(dev)
     (pkg["render"] * dL).sum().backward()
     torch.cuda.synchronize()
+    pkg["model"] = pc
     return pkg, {k: v.grad.clone() for k, v in pc.leaves().items()}
 
 
@@ -158,17 +163,19 @@ def test_viewspace_points_grad_consumer():
     a2 = torch.zeros(P, device="cuda"); d2 = torch.zeros(P, device="cuda"); m2 = torch.zeros(P, device="cuda")
     dgr._C.densify_stats(vsp.grad.contiguous(), radii, a2, d2, m2)
     assert torch.allclose(accum.view(-1), a2, rtol=1e-6, atol=0) and torch.equal(denom.view(-1), d2) and torch.equal(maxr, m2)
-    # oracle: same scene, same upstream gradient
-    sc = synth.make_scene(P, 3, seed=6, s_med=0.035)
+    # oracle: the activated values the model handed to the operator, same upstream gradient
+    pc = pkg["model"]
     cam = synth.make_camera(256, 160, yaw=0.3)
     nn = lambda t: t.detach().cpu().numpy()
     bg = np.array([0.15, 0.1, 0.3], np.float32)
-    fr = co.forward(P, 3, 16, 256, 160, bg, nn(sc.means3D), nn(sc.shs), None, nn(sc.opacities), nn(sc.scales), 1.0,
-                    nn(sc.rotations), None, nn(cam.world_view_transform), nn(cam.full_proj_transform), nn(cam.camera_center),
+    args = (nn(pc.get_xyz), nn(pc.get_features))
+    fr = co.forward(P, 3, 16, 256, 160, bg, args[0], args[1], None, nn(pc.get_opacity), nn(pc.get_scaling), 1.0,
+                    nn(pc.get_rotation), None, nn(cam.world_view_transform), nn(cam.full_proj_transform), nn(cam.camera_center),
                     cam.tanfovx, cam.tanfovy)
-    pg = co.backward(fr, P, 3, 16, 256, 160, bg, nn(sc.means3D), nn(sc.shs), nn(sc.opacities), nn(sc.scales), 1.0,
-                     nn(sc.rotations), None, nn(cam.world_view_transform), nn(cam.full_proj_transform), nn(cam.camera_center),
+    pg = co.backward(fr, P, 3, 16, 256, 160, bg, args[0], args[1], nn(pc.get_opacity), nn(pc.get_scaling), 1.0,
+                     nn(pc.get_rotation), None, nn(cam.world_view_transform), nn(cam.full_proj_transform), nn(cam.camera_center),
                      cam.tanfovx, cam.tanfovy, nn(synth.make_grad_image(256, 160, seed=9)))
     assert np.array_equal(nn(radii), fr.geom.radii)
+    assert np.array_equal(nn(pkg["render"]), fr.color)                  # bit-exact forward
     err = np.abs(nn(vsp.grad)[:, :2] - pg.dL_dmean2D).max() / np.abs(pg.dL_dmean2D).max()
     assert err <= 1e-3, err

@@ -61,6 +61,62 @@ def test_forward_state_bit_exact_and_image(name):
     assert float(np.abs(n(color) - fr.color).max()) <= IMG_TOL
     assert float(np.abs(n(invd) - fr.invdepth).max()) <= IMG_TOL
     assert float(np.abs(n(st["final_T"]) - fr.final_T).max()) <= IMG_TOL
+    # stronger than the 1e-5 gate: with exp part of the canonical arithmetic the whole forward is bit-exact
+    # (a flipped alpha >= 1/255 decision would move a pixel by up to 4e-3, so "nearly equal" is not a stable state)
+    _bit_exact_forward(color, invd, st, fr)
+
+
+def _bit_exact_forward(color, invd, st, fr):
+    diff = {"color": int((n(color) != fr.color).sum()), "final_T": int((n(st["final_T"]) != fr.final_T).sum())}
+    if invd is not None and fr.invdepth is not None:
+        diff["invdepth"] = int((n(invd) != fr.invdepth).sum())
+    assert not any(diff.values()), f"forward outputs differ from the oracle in some bit: {diff}"
+
+
+def test_capacity_modes_match_exact_mode_and_report_overflow():
+    """b200splat.h "Pair capacity": a caller-supplied capacity (no host wait) gives the same state as exact mode; a
+    capacity that is too small is flagged, writes nothing out of bounds, and the Python policy raises one call late."""
+    import diff_gaussian_rasterization as dgr
+    C = dgr._C
+    case = Case(**CASES["sh3_ragged_edges"])
+    fr = case.oracle_forward(want_invdepth=True)
+    R0, color0, radii0, invd0, st0 = case.cuda_state(want_invdepth=True)              # exact
+    R1, color1, radii1, invd1, st1 = case.cuda_state(want_invdepth=True, exact=False, bin_capacity=R0 + 12345)
+    assert R0 == R1 == fr.binning.keys.size
+    _integer_gates(case, fr, R1, radii1, st1)
+    assert torch.equal(color0, color1) and torch.equal(invd0, invd1)
+    dev = torch.device("cuda:0")
+    s, c = case.scene.to(dev), case.cam.to(dev)
+
+    def fwd(mod=1.0, **kw):
+        return C.rasterize_gaussians(case.bg.to(dev), s.means3D, None, s.opacities, s.scales, s.rotations, mod, None,
+                                     c.world_view_transform, c.full_proj_transform, c.tanfovx, c.tanfovy, case.H, case.W, s.shs,
+                                     case.D, c.camera_center, False, False, **kw)
+    res = fwd(bin_capacity=R0 // 3)                                                  # too small: flagged, in bounds
+    torch.cuda.synchronize()
+    assert C.forward_status(res[5], case.H, case.W) == (R0, R0 // 3, True)
+    assert C.forward_status(fwd(exact=True)[5], case.H, case.W) == (R0, R0, False)
+    # the policy: exact first view, then capacities from the largest R seen
+    C.reset_capacity_policy()
+    a = fwd()
+    assert a[0] == R0                                                                # exact: num_rendered = R
+    b = fwd()
+    assert b[0] >= int(1.5 * R0) and torch.equal(a[1], b[1]) and torch.equal(a[1], color0)
+    torch.cuda.synchronize()
+    assert C.forward_status(b[5], case.H, case.W)[2] is False
+    big = fwd(mod=4.0)                                                               # splats 4x larger: far more pairs
+    torch.cuda.synchronize()
+    Rbig, capbig, over = C.forward_status(big[5], case.H, case.W)
+    assert over and Rbig > capbig
+    with pytest.raises(RuntimeError, match="PREVIOUS forward"):
+        fwd(mod=4.0)
+    ok = fwd(mod=4.0)                                                                # capacity raised: fine now
+    torch.cuda.synchronize()
+    assert C.forward_status(ok[5], case.H, case.W) == (Rbig, ok[0], False)
+    ex = fwd(mod=4.0, exact=True)
+    assert torch.equal(ok[1], ex[1])
+    C.reset_capacity_policy()
+    C.lib().b200splat_shutdown()
 
 
 @pytest.mark.parametrize("name", list(CASES))
