@@ -20,7 +20,7 @@ constexpr int PRE_THREADS = PRE_T;
 #define PRE_MINB_FWD 8
 #endif
 #ifndef PRE_MINB_BWD
-#define PRE_MINB_BWD 5
+#define PRE_MINB_BWD 3     // the fp64 geometry chain wants registers; the kernel visits few Gaussians and is latency-bound
 #endif
 
 // row stride (floats) of an SH row staged in shared memory: an odd number of 16-byte words
@@ -389,107 +389,138 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
             s3[0] = __ldg(p.scales + 3 * i); s3[1] = __ldg(p.scales + 3 * i + 1); s3[2] = __ldg(p.scales + 3 * i + 2);
             cov3d_from_scale_rot(s3[0], s3[1], s3[2], p.mod, q, c6);
         }
+        // The chain conic -> cov2D -> (cov3D, mean) -> (scale, rotation) runs in DOUBLE from the fp32 inputs: for an
+        // elongated splat a c ~ b^2, and the determinant, its square and the combinations of (LA, LB, LC) below lose
+        // 3-4 digits to cancellation in fp32 -- enough to break the 1e-3 gradient gate on the largest splats of a
+        // full-size view (measured: 1.06e-3 on dL/drotation).  Only the ~7 % of Gaussians a view touches come here,
+        // so the fp64 work is a few microseconds.  The clamp decisions use the forward's fp32 values.
         const float limx = cmul(1.3f, p.tanfovx), limy = cmul(1.3f, p.tanfovy);
-        Proj2D pj;
-        project_cov(vc, tx, ty, tz, c6, p.focal_x, p.focal_y, limx, limy, pj);
-        const float xmul = (pj.txtz < -limx || pj.txtz > limx) ? 0.f : 1.f;
-        const float ymul = (pj.tytz < -limy || pj.tytz > limy) ? 0.f : 1.f;
-        const float a = pj.cov00 + 0.3f, b = pj.cov01, c = pj.cov11 + 0.3f;
-        const float det = a * c - b * b;
-        const float d2inv = 1.0f / (det * det + 0.0000001f);
-        // det - a c = -b^2 exactly; written that way, because the fp32 difference loses everything for the common
-        // nearly axis-aligned splat (b^2 << a c) and the error is amplified by a / c for an elongated one
-        float dL_da = d2inv * (-c * c * LA + b * c * LB - b * b * LC);
-        float dL_dc = d2inv * (-a * a * LC + a * b * LB - b * b * LA);
-        float dL_db = d2inv * (2.f * b * c * LA - (det + 2.f * b * b) * LB + 2.f * a * b * LC);
+        const float txtz = cdiv(tx, tz), tytz = cdiv(ty, tz);
+        const double xmul = (txtz < -limx || txtz > limx) ? 0.0 : 1.0;
+        const double ymul = (tytz < -limy || tytz > limy) ? 0.0 : 1.0;
+        const double dtzv = tz;
+        const double txc = (double)cmul(fminf(limx, fmaxf(-limx, txtz)), tz), tyc = (double)cmul(fminf(limy, fmaxf(-limy, tytz)), tz);
+        const double fx = p.focal_x, fy = p.focal_y;
+        const double J00 = fx / dtzv, J02 = -(fx * txc) / (dtzv * dtzv), J11 = fy / dtzv, J12 = -(fy * tyc) / (dtzv * dtzv);
+        double M0[3], M1[3], N0[3], N1[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            M0[k] = J00 * (double)vc.view[4 * k + 0] + J02 * (double)vc.view[4 * k + 2];
+            M1[k] = J11 * (double)vc.view[4 * k + 1] + J12 * (double)vc.view[4 * k + 2];
+        }
+        {
+            const double S[3][3] = {{c6[0], c6[1], c6[2]}, {c6[1], c6[3], c6[4]}, {c6[2], c6[4], c6[5]}};
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                N0[k] = M0[0] * S[0][k] + M0[1] * S[1][k] + M0[2] * S[2][k];
+                N1[k] = M1[0] * S[0][k] + M1[1] * S[1][k] + M1[2] * S[2][k];
+            }
+        }
+        const double cov00 = N0[0] * M0[0] + N0[1] * M0[1] + N0[2] * M0[2];
+        const double cov01 = N0[0] * M1[0] + N0[1] * M1[1] + N0[2] * M1[2];
+        const double cov11 = N1[0] * M1[0] + N1[1] * M1[1] + N1[2] * M1[2];
+        const double a = cov00 + 0.3, b = cov01, c = cov11 + 0.3;
+        const double det = a * c - b * b;
+        const double d2inv = 1.0 / (det * det + 0.0000001);
+        const double dLA = LA, dLB = LB, dLC = LC;
+        // det - a c = -b^2
+        double dL_da = d2inv * (-c * c * dLA + b * c * dLB - b * b * dLC);
+        double dL_dc = d2inv * (-a * a * dLC + a * b * dLB - b * b * dLA);
+        double dL_db = d2inv * (2.0 * b * c * dLA - (det + 2.0 * b * b) * dLB + 2.0 * a * b * dLC);
         if (p.antialiasing) {
-            const float det0 = pj.cov00 * pj.cov11 - pj.cov01 * pj.cov01;
-            const float ratio = det0 / det;
-            const float h = sqrtf(fmaxf(0.000025f, ratio));
-            const float dL_dh = __ldg(p.opacities + i) * dLo;
-            dLo = h * dLo;
-            if (ratio > 0.000025f) {
-                const float dL_dratio = dL_dh * 0.5f / h;
-                const float inv2 = 1.0f / (det * det);
-                dL_da += dL_dratio * (pj.cov11 * det - det0 * c) * inv2;
-                dL_dc += dL_dratio * (pj.cov00 * det - det0 * a) * inv2;
-                dL_db += dL_dratio * (-2.f * pj.cov01 * det + det0 * 2.f * pj.cov01) * inv2;
+            const double det0 = cov00 * cov11 - cov01 * cov01;
+            const double ratio = det0 / det;
+            const double h = sqrt(ratio > 0.000025 ? ratio : 0.000025);
+            const double dL_dh = (double)__ldg(p.opacities + i) * (double)dLo;
+            dLo = (float)(h * (double)dLo);
+            if (ratio > 0.000025) {
+                const double dL_dratio = dL_dh * 0.5 / h;
+                const double inv2 = 1.0 / (det * det);
+                dL_da += dL_dratio * (cov11 * det - det0 * c) * inv2;
+                dL_dc += dL_dratio * (cov00 * det - det0 * a) * inv2;
+                dL_db += dL_dratio * (-2.0 * cov01 * det + det0 * 2.0 * cov01) * inv2;
             }
         }
         dop = dLo;
 
-        const float* M0 = pj.M0; const float* M1 = pj.M1;
-        dc6[0] = M0[0] * M0[0] * dL_da + M0[0] * M1[0] * dL_db + M1[0] * M1[0] * dL_dc;
-        dc6[3] = M0[1] * M0[1] * dL_da + M0[1] * M1[1] * dL_db + M1[1] * M1[1] * dL_dc;
-        dc6[5] = M0[2] * M0[2] * dL_da + M0[2] * M1[2] * dL_db + M1[2] * M1[2] * dL_dc;
-        dc6[1] = 2.f * M0[0] * M0[1] * dL_da + (M0[0] * M1[1] + M0[1] * M1[0]) * dL_db + 2.f * M1[0] * M1[1] * dL_dc;
-        dc6[2] = 2.f * M0[0] * M0[2] * dL_da + (M0[0] * M1[2] + M0[2] * M1[0]) * dL_db + 2.f * M1[0] * M1[2] * dL_dc;
-        dc6[4] = 2.f * M0[1] * M0[2] * dL_da + (M0[1] * M1[2] + M0[2] * M1[1]) * dL_db + 2.f * M1[1] * M1[2] * dL_dc;
+        double dc6d[6];
+        dc6d[0] = M0[0] * M0[0] * dL_da + M0[0] * M1[0] * dL_db + M1[0] * M1[0] * dL_dc;
+        dc6d[3] = M0[1] * M0[1] * dL_da + M0[1] * M1[1] * dL_db + M1[1] * M1[1] * dL_dc;
+        dc6d[5] = M0[2] * M0[2] * dL_da + M0[2] * M1[2] * dL_db + M1[2] * M1[2] * dL_dc;
+        dc6d[1] = 2.0 * M0[0] * M0[1] * dL_da + (M0[0] * M1[1] + M0[1] * M1[0]) * dL_db + 2.0 * M1[0] * M1[1] * dL_dc;
+        dc6d[2] = 2.0 * M0[0] * M0[2] * dL_da + (M0[0] * M1[2] + M0[2] * M1[0]) * dL_db + 2.0 * M1[0] * M1[2] * dL_dc;
+        dc6d[4] = 2.0 * M0[1] * M0[2] * dL_da + (M0[1] * M1[2] + M0[2] * M1[1]) * dL_db + 2.0 * M1[1] * M1[2] * dL_dc;
+#pragma unroll
+        for (int k = 0; k < 6; k++) dc6[k] = (float)dc6d[k];
 
         // cov2D -> (J Wv) -> J -> view-space point -> mean
-        float dJ00 = 0.f, dJ02 = 0.f, dJ11 = 0.f, dJ12 = 0.f;
+        double dJ00 = 0.0, dJ02 = 0.0, dJ11 = 0.0, dJ12 = 0.0;
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            const float dM0 = 2.f * dL_da * pj.N0[k] + dL_db * pj.N1[k];
-            const float dM1 = dL_db * pj.N0[k] + 2.f * dL_dc * pj.N1[k];
-            dJ00 += dM0 * vc.view[4 * k + 0]; dJ02 += dM0 * vc.view[4 * k + 2];
-            dJ11 += dM1 * vc.view[4 * k + 1]; dJ12 += dM1 * vc.view[4 * k + 2];
+            const double dM0 = 2.0 * dL_da * N0[k] + dL_db * N1[k];
+            const double dM1 = dL_db * N0[k] + 2.0 * dL_dc * N1[k];
+            dJ00 += dM0 * (double)vc.view[4 * k + 0]; dJ02 += dM0 * (double)vc.view[4 * k + 2];
+            dJ11 += dM1 * (double)vc.view[4 * k + 1]; dJ12 += dM1 * (double)vc.view[4 * k + 2];
         }
-        const float itz = 1.0f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
-        const float dtx = xmul * (-p.focal_x * itz2) * dJ02;
-        const float dty = ymul * (-p.focal_y * itz2) * dJ12;
-        float dtz = -p.focal_x * itz2 * dJ00 - p.focal_y * itz2 * dJ11 + (2.f * p.focal_x * pj.txc) * itz3 * dJ02 +
-                    (2.f * p.focal_y * pj.tyc) * itz3 * dJ12;
-        dtz += -a2.y * itz2;   // inverse-depth channel (zero unless a depth gradient was supplied)
-        dmean[0] = vc.view[0] * dtx + vc.view[1] * dty + vc.view[2] * dtz;
-        dmean[1] = vc.view[4] * dtx + vc.view[5] * dty + vc.view[6] * dtz;
-        dmean[2] = vc.view[8] * dtx + vc.view[9] * dty + vc.view[10] * dtz;
+        const double itz = 1.0 / dtzv, itz2 = itz * itz, itz3 = itz2 * itz;
+        const double dtx = xmul * (-fx * itz2) * dJ02;
+        const double dty = ymul * (-fy * itz2) * dJ12;
+        double dtz = -fx * itz2 * dJ00 - fy * itz2 * dJ11 + (2.0 * fx * txc) * itz3 * dJ02 + (2.0 * fy * tyc) * itz3 * dJ12;
+        dtz += -(double)a2.y * itz2;   // inverse-depth channel (zero unless a depth gradient was supplied)
+        double dmd[3];
+        dmd[0] = (double)vc.view[0] * dtx + (double)vc.view[1] * dty + (double)vc.view[2] * dtz;
+        dmd[1] = (double)vc.view[4] * dtx + (double)vc.view[5] * dty + (double)vc.view[6] * dtz;
+        dmd[2] = (double)vc.view[8] * dtx + (double)vc.view[9] * dty + (double)vc.view[10] * dtz;
 
         // mean2D (NDC) -> mean3D through the full projection
         {
-            const float hx = vc.proj[0] * x + vc.proj[4] * y + vc.proj[8] * z + vc.proj[12];
-            const float hy = vc.proj[1] * x + vc.proj[5] * y + vc.proj[9] * z + vc.proj[13];
-            const float hw = vc.proj[3] * x + vc.proj[7] * y + vc.proj[11] * z + vc.proj[15];
-            const float mw = 1.0f / (hw + 0.0000001f);
-            const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
-            dmean[0] += (vc.proj[0] * mw - vc.proj[3] * mul1) * dndc[0] + (vc.proj[1] * mw - vc.proj[3] * mul2) * dndc[1];
-            dmean[1] += (vc.proj[4] * mw - vc.proj[7] * mul1) * dndc[0] + (vc.proj[5] * mw - vc.proj[7] * mul2) * dndc[1];
-            dmean[2] += (vc.proj[8] * mw - vc.proj[11] * mul1) * dndc[0] + (vc.proj[9] * mw - vc.proj[11] * mul2) * dndc[1];
+            const double dx = x, dy = y, dz = z;
+            const double hx = vc.proj[0] * dx + vc.proj[4] * dy + vc.proj[8] * dz + vc.proj[12];
+            const double hy = vc.proj[1] * dx + vc.proj[5] * dy + vc.proj[9] * dz + vc.proj[13];
+            const double hw = vc.proj[3] * dx + vc.proj[7] * dy + vc.proj[11] * dz + vc.proj[15];
+            const double mw = 1.0 / (hw + 0.0000001);
+            const double mul1 = hx * mw * mw, mul2 = hy * mw * mw;
+            const double gxn = dndc[0], gyn = dndc[1];
+            dmd[0] += (vc.proj[0] * mw - vc.proj[3] * mul1) * gxn + (vc.proj[1] * mw - vc.proj[3] * mul2) * gyn;
+            dmd[1] += (vc.proj[4] * mw - vc.proj[7] * mul1) * gxn + (vc.proj[5] * mw - vc.proj[7] * mul2) * gyn;
+            dmd[2] += (vc.proj[8] * mw - vc.proj[11] * mul1) * gxn + (vc.proj[9] * mw - vc.proj[11] * mul2) * gyn;
         }
+        dmean[0] = (float)dmd[0]; dmean[1] = (float)dmd[1]; dmean[2] = (float)dmd[2];
 
         // cov3D -> scale, rotation
         if (!p.cov3D_precomp) {
-            const float r = q.x, qx = q.y, qy = q.z, qz = q.w;
-            const float R[3][3] = {
-                {1.f - 2.f * (qy * qy + qz * qz), 2.f * (qx * qy - r * qz), 2.f * (qx * qz + r * qy)},
-                {2.f * (qx * qy + r * qz), 1.f - 2.f * (qx * qx + qz * qz), 2.f * (qy * qz - r * qx)},
-                {2.f * (qx * qz - r * qy), 2.f * (qy * qz + r * qx), 1.f - 2.f * (qx * qx + qy * qy)}};
-            const float s[3] = {p.mod * s3[0], p.mod * s3[1], p.mod * s3[2]};
-            const float G3[3][3] = {{dc6[0], 0.5f * dc6[1], 0.5f * dc6[2]},
-                                    {0.5f * dc6[1], dc6[3], 0.5f * dc6[4]},
-                                    {0.5f * dc6[2], 0.5f * dc6[4], dc6[5]}};
-            float g[3][3];
+            const double r = q.x, qx = q.y, qy = q.z, qz = q.w;
+            const double R[3][3] = {
+                {1.0 - 2.0 * (qy * qy + qz * qz), 2.0 * (qx * qy - r * qz), 2.0 * (qx * qz + r * qy)},
+                {2.0 * (qx * qy + r * qz), 1.0 - 2.0 * (qx * qx + qz * qz), 2.0 * (qy * qz - r * qx)},
+                {2.0 * (qx * qz - r * qy), 2.0 * (qy * qz + r * qx), 1.0 - 2.0 * (qx * qx + qy * qy)}};
+            const double sm = p.mod;
+            const double sd[3] = {sm * s3[0], sm * s3[1], sm * s3[2]};
+            const double G3[3][3] = {{dc6d[0], 0.5 * dc6d[1], 0.5 * dc6d[2]},
+                                     {0.5 * dc6d[1], dc6d[3], 0.5 * dc6d[4]},
+                                     {0.5 * dc6d[2], 0.5 * dc6d[4], dc6d[5]}};
+            double g[3][3];
 #pragma unroll
             for (int j = 0; j < 3; j++) {
-                float ds = 0.f;
+                double ds = 0.0;
 #pragma unroll
                 for (int a2i = 0; a2i < 3; a2i++) {
-                    float vsum = 0.f;
+                    double vsum = 0.0;
 #pragma unroll
-                    for (int k = 0; k < 3; k++) vsum += G3[a2i][k] * (R[k][j] * s[j]);
-                    const float dLm = 2.f * vsum;
+                    for (int k = 0; k < 3; k++) vsum += G3[a2i][k] * (R[k][j] * sd[j]);
+                    const double dLm = 2.0 * vsum;
                     ds += R[a2i][j] * dLm;
-                    g[a2i][j] = dLm * s[j];
+                    g[a2i][j] = dLm * sd[j];
                 }
-                dsc[j] = p.mod * ds;
+                dsc[j] = (float)(sm * ds);
             }
-            drot[0] = 2.f * (-qz * g[0][1] + qy * g[0][2] + qz * g[1][0] - qx * g[1][2] - qy * g[2][0] + qx * g[2][1]);
-            drot[1] = 2.f * (qy * g[0][1] + qz * g[0][2] + qy * g[1][0] - 2.f * qx * g[1][1] - r * g[1][2] + qz * g[2][0] +
-                             r * g[2][1] - 2.f * qx * g[2][2]);
-            drot[2] = 2.f * (-2.f * qy * g[0][0] + qx * g[0][1] + r * g[0][2] + qx * g[1][0] + qz * g[1][2] - r * g[2][0] +
-                             qz * g[2][1] - 2.f * qy * g[2][2]);
-            drot[3] = 2.f * (-2.f * qz * g[0][0] - r * g[0][1] + qx * g[0][2] + r * g[1][0] - 2.f * qz * g[1][1] +
-                             qy * g[1][2] + qx * g[2][0] + qy * g[2][1]);
+            drot[0] = (float)(2.0 * (-qz * g[0][1] + qy * g[0][2] + qz * g[1][0] - qx * g[1][2] - qy * g[2][0] + qx * g[2][1]));
+            drot[1] = (float)(2.0 * (qy * g[0][1] + qz * g[0][2] + qy * g[1][0] - 2.0 * qx * g[1][1] - r * g[1][2] + qz * g[2][0] +
+                                     r * g[2][1] - 2.0 * qx * g[2][2]));
+            drot[2] = (float)(2.0 * (-2.0 * qy * g[0][0] + qx * g[0][1] + r * g[0][2] + qx * g[1][0] + qz * g[1][2] - r * g[2][0] +
+                                     qz * g[2][1] - 2.0 * qy * g[2][2]));
+            drot[3] = (float)(2.0 * (-2.0 * qz * g[0][0] - r * g[0][1] + qx * g[0][2] + r * g[1][0] - 2.0 * qz * g[1][1] +
+                                     qy * g[1][2] + qx * g[2][0] + qy * g[2][1]));
         }
     }
     if (coop) {   // the rows have landed; make every lane's copies visible to the warp

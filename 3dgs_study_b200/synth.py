@@ -95,9 +95,18 @@ class Scene(NamedTuple):
         return Scene(*[t.to(device) if isinstance(t, torch.Tensor) else t for t in self])
 
 
-def make_scene(P: int, sh_degree: int = 3, seed: int = 0, s_med: Optional[float] = None) -> Scene:
+PRESETS = {
+    # opacity = sigmoid(N(0, 2^2)) -- very opaque splats: a view blends ~7 % of its Gaussians
+    "opaque": (0.0, 2.0),
+    # a second operating point: opacity = sigmoid(N(-2, 1)), median 0.12 -- light passes through many
+    # more layers, several times more Gaussians receive a gradient (the regime of a partly trained scene)
+    "translucent": (-2.0, 1.0),
+}
+
+
+def make_scene(P: int, sh_degree: int = 3, seed: int = 0, s_med: Optional[float] = None, preset: str = "opaque") -> Scene:
     """70 % foreground blob N(0, diag(1.2, 0.45, 1.2)^2), 30 % background shell r ~ U(6,16);
-    log-scales ~ N(ln s_med, 0.7^2) (background x r/3); s_med(P) = 0.006 (3e6/P)^(1/3)."""
+    log-scales ~ N(ln s_med, 0.7^2) (background x r/3); s_med(P) = 0.006 (3e6/P)^(1/3); opacity per PRESETS."""
     g = torch.Generator().manual_seed(seed)
     M = (sh_degree + 1) ** 2
     if s_med is None:
@@ -114,7 +123,8 @@ def make_scene(P: int, sh_degree: int = 3, seed: int = 0, s_med: Optional[float]
     scales[n_fg:] = scales[n_fg:] * (r / 3.0)
     q = torch.randn(P, 4, generator=g)
     q = q / q.norm(dim=1, keepdim=True).clamp_min(1e-12)
-    opac = torch.sigmoid(2.0 * torch.randn(P, 1, generator=g))
+    o_mean, o_std = PRESETS[preset]
+    opac = torch.sigmoid(o_mean + o_std * torch.randn(P, 1, generator=g))
     shs = torch.empty(P, M, 3)
     shs[:, 0, :] = 0.5 * torch.randn(P, 3, generator=g)
     if M > 1:

@@ -68,7 +68,10 @@ __global__ void __launch_bounds__(256) mufu_kernel(float* out) {
 #pragma unroll
             for (int k = 0; k < CHAINS; k++) {
                 if (OP == 0) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(x[k]));
-                else asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(x[k]));
+                else {   // 1/x + 1: without the add ptxas folds rcp(rcp(x)) back into x; the FADD pipe is 8x wider than MUFU
+                    asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(x[k]));
+                    x[k] += 1.0f;
+                }
             }
     }
     float s = 0.f;
