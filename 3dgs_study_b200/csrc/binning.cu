@@ -42,7 +42,11 @@ constexpr int RS_TILE = RS_THREADS * RS_ITEMS;              // 4096 elements per
 constexpr int DEPTH_MAXBINS = 2048;                         // 3 passes x <= 11 bits cover any 32-bit key range
 constexpr int TILE_MAXBINS = 512;                           // tile columns / rows: images up to 8192 x 8192
 
-inline int radix_blocks(size_t n) { return (int)((n + RS_TILE - 1) / RS_TILE) > 0 ? (int)((n + RS_TILE - 1) / RS_TILE) : 1; }
+// blocks covering n elements, rounded up to a multiple of 4 (the column scan walks matrix rows 16 bytes at a time)
+inline int radix_blocks(size_t n) {
+    const int b = (int)((n + RS_TILE - 1) / RS_TILE);
+    return b > 0 ? (b + 3) & ~3 : 4;
+}
 
 // Element count of a pass: a device word (u64 when `wide`) clipped to a host-known bound.
 struct Count {
@@ -84,16 +88,25 @@ struct TileTraits {
     static constexpr int MAXBINS = TILE_MAXBINS;
     static constexpr bool STAGE = true;
     int gx, nbins, by_row;
-    unsigned long long magic;  // floor(2^32 / gx) + 1: tile / gx = (tile * magic) >> 32 exactly for tile < 2^20, gx <= 512
+    uint32_t magic;            // floor(2^32 / gx) + 1: tile / gx = umulhi(tile, magic) exactly for tile < 2^20, 2 <= gx <= 512
     __device__ __forceinline__ void init() {}
     __device__ __forceinline__ bool valid(K) const { return true; }
     __device__ __forceinline__ uint32_t digit(K k) const {
         const uint32_t t = (uint32_t)k;
-        const uint32_t q = (uint32_t)(((unsigned long long)t * magic) >> 32);
+        const uint32_t q = gx == 1 ? t : __umulhi(t, magic);
         return by_row ? q : t - q * (uint32_t)gx;
     }
     __device__ __forceinline__ int bins() const { return nbins; }
 };
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_wait_all() {
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
 
 // In-place exclusive scan of s[0..n), n <= 2048, by a 256-thread block (s fully written and synchronised by the
 // caller; synchronised again on return).
@@ -125,9 +138,12 @@ __device__ __forceinline__ void block_excl_scan(uint32_t* s, int n, uint32_t* s_
 }
 
 // ---- one radix pass: count / colscan / scatter ---------------------------------------------------------
+// count: 16-byte loads (8 u16 / 4 u32 keys each), all of a thread's loads in flight before the first histogram update
 template <class TR>
 __global__ void __launch_bounds__(RS_THREADS) radix_count_kernel(TR tr, const typename TR::KeyT* __restrict__ keys, Count cnt,
                                                                  int stride, uint32_t* __restrict__ matrix) {
+    using KeyT = typename TR::KeyT;
+    constexpr int VEC = 16 / sizeof(KeyT), NLOAD = RS_ITEMS / VEC;
     __shared__ unsigned s_hist[TR::MAXBINS];
     const unsigned n = load_count(cnt);
     const unsigned base = blockIdx.x * (unsigned)RS_TILE;
@@ -135,19 +151,26 @@ __global__ void __launch_bounds__(RS_THREADS) radix_count_kernel(TR tr, const ty
     tr.init();
     const int bins = tr.bins(), tid = threadIdx.x;
     for (int d = tid; d < bins; d += RS_THREADS) s_hist[d] = 0u;
+    uint4 raw[NLOAD];
+#pragma unroll
+    for (int l = 0; l < NLOAD; l++) {
+        const unsigned idx = base + (unsigned)(l * RS_THREADS + tid) * VEC;
+        raw[l] = idx < n ? __ldg(reinterpret_cast<const uint4*>(keys + idx)) : make_uint4(0u, 0u, 0u, 0u);   // padded arrays: in bounds
+    }
     __syncthreads();
-#pragma unroll 4
-    for (int e = 0; e < RS_ITEMS; e++) {
-        const unsigned idx = base + e * RS_THREADS + tid;
-        if (idx < n) {
-            const typename TR::KeyT k = keys[idx];
-            if (tr.valid(k)) atomicAdd(&s_hist[tr.digit(k)], 1u);
-        }
+#pragma unroll
+    for (int l = 0; l < NLOAD; l++) {
+        const unsigned idx = base + (unsigned)(l * RS_THREADS + tid) * VEC;
+        const KeyT* kk = reinterpret_cast<const KeyT*>(&raw[l]);
+#pragma unroll
+        for (int e = 0; e < VEC; e++)
+            if (idx + e < n && tr.valid(kk[e])) atomicAdd(&s_hist[tr.digit(kk[e])], 1u);
     }
     __syncthreads();
     for (int d = tid; d < bins; d += RS_THREADS) matrix[(size_t)d * stride + blockIdx.x] = s_hist[d];
 }
 
+// colscan: one warp per digit; a lane takes 4 consecutive blocks per step (the row stride is a multiple of 4)
 template <class TR>
 __global__ void __launch_bounds__(RS_THREADS) radix_colscan_kernel(TR tr, Count cnt, int stride, uint32_t* __restrict__ matrix,
                                                                    uint32_t* __restrict__ totals) {
@@ -157,43 +180,80 @@ __global__ void __launch_bounds__(RS_THREADS) radix_colscan_kernel(TR tr, Count 
     if (d >= tr.bins()) return;
     const unsigned n = load_count(cnt);
     const int nb = (int)((n + RS_TILE - 1) / RS_TILE);
-    uint32_t* row = matrix + (size_t)d * stride;
+    uint4* row = reinterpret_cast<uint4*>(matrix + (size_t)d * stride);
     uint32_t run = 0;
-    for (int b0 = 0; b0 < nb; b0 += 32) {
-        const int b = b0 + lane;
-        const uint32_t v = b < nb ? row[b] : 0u;
-        uint32_t incl = v;
+    for (int b0 = 0; b0 < nb; b0 += 128) {
+        const int b = b0 + 4 * lane;
+        uint4 v = b < nb ? row[b >> 2] : make_uint4(0u, 0u, 0u, 0u);
+        if (b + 1 >= nb) v.y = 0u;
+        if (b + 2 >= nb) v.z = 0u;
+        if (b + 3 >= nb) v.w = 0u;
+        const uint32_t sum = v.x + v.y + v.z + v.w;
+        uint32_t incl = sum;
 #pragma unroll
         for (int s = 1; s < 32; s <<= 1) {
             const uint32_t t = __shfl_up_sync(FULLMASK, incl, s);
             if (lane >= s) incl += t;
         }
-        if (b < nb) row[b] = run + incl - v;
+        const uint32_t e0 = run + incl - sum;
+        if (b < nb) row[b >> 2] = make_uint4(e0, e0 + v.x, e0 + v.x + v.y, e0 + v.x + v.y + v.z);
         run += __shfl_sync(FULLMASK, incl, 31);
     }
     if (lane == 0) totals[d] = run;
 }
 
+// scatter.  Shared memory (dynamic): digit bases, per-warp digit counts, the block's 4096 (key, value) pairs as they
+// arrive (cp.async, in flight while the digit bases are scanned) and -- staged passes -- again in sorted order.
 template <class TR>
-__global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(TR tr, const typename TR::KeyT* __restrict__ keys_in,
-                                                                   const uint32_t* __restrict__ vals_in,
-                                                                   typename TR::KeyT* __restrict__ keys_out,
-                                                                   uint32_t* __restrict__ vals_out, Count cnt, int stride,
-                                                                   const uint32_t* __restrict__ matrix,
-                                                                   const uint32_t* __restrict__ totals, int2* __restrict__ ranges) {
+struct ScatterSmem {
     using KeyT = typename TR::KeyT;
+    static constexpr int MB = TR::MAXBINS;
+    static constexpr size_t off_base = 0;
+    static constexpr size_t off_lstart = off_base + sizeof(uint32_t) * MB;
+    static constexpr size_t off_whist = off_lstart + (TR::STAGE ? sizeof(uint32_t) * MB : 0);
+    static constexpr size_t off_ikey = off_whist + sizeof(uint16_t) * RS_WARPS * MB;
+    static constexpr size_t off_ival = off_ikey + sizeof(KeyT) * RS_TILE;
+    static constexpr size_t off_okey = off_ival + sizeof(uint32_t) * RS_TILE;
+    static constexpr size_t off_oval = off_okey + (TR::STAGE ? sizeof(KeyT) * RS_TILE : 0);
+    static constexpr size_t off_warp = off_oval + (TR::STAGE ? sizeof(uint32_t) * RS_TILE : 0);
+    static constexpr size_t bytes = off_warp + sizeof(uint32_t) * RS_WARPS;
+};
+
+template <class TR>
+__global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, const typename TR::KeyT* __restrict__ keys_in,
+                                                                      const uint32_t* __restrict__ vals_in,
+                                                                      typename TR::KeyT* __restrict__ keys_out,
+                                                                      uint32_t* __restrict__ vals_out, Count cnt, int stride,
+                                                                      const uint32_t* __restrict__ matrix,
+                                                                      const uint32_t* __restrict__ totals, int2* __restrict__ ranges) {
+    using KeyT = typename TR::KeyT;
+    using SM = ScatterSmem<TR>;
     constexpr int MB = TR::MAXBINS;
-    __shared__ uint32_t s_base[MB];                          // global position of this block's first element of each digit
-    __shared__ uint16_t s_whist[RS_WARPS][MB];               // per-warp digit counts -> exclusive prefix over the warps
-    __shared__ uint32_t s_lstart[TR::STAGE ? MB : 1];        // first slot of each digit in the block's sorted order
-    __shared__ KeyT s_key[TR::STAGE ? RS_TILE : 1];
-    __shared__ uint32_t s_val[TR::STAGE ? RS_TILE : 1];
-    __shared__ uint32_t s_warp[RS_WARPS];
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* s_base = reinterpret_cast<uint32_t*>(smem_raw + SM::off_base);      // global position of the block's first element of each digit
+    uint32_t* s_lstart = reinterpret_cast<uint32_t*>(smem_raw + SM::off_lstart);  // first slot of each digit in the block's sorted order
+    uint16_t (*s_whist)[MB] = reinterpret_cast<uint16_t (*)[MB]>(smem_raw + SM::off_whist);   // per-warp counts -> prefix over warps
+    KeyT* s_ikey = reinterpret_cast<KeyT*>(smem_raw + SM::off_ikey);
+    uint32_t* s_ival = reinterpret_cast<uint32_t*>(smem_raw + SM::off_ival);
+    KeyT* s_okey = reinterpret_cast<KeyT*>(smem_raw + SM::off_okey);
+    uint32_t* s_oval = reinterpret_cast<uint32_t*>(smem_raw + SM::off_oval);
+    uint32_t* s_warp = reinterpret_cast<uint32_t*>(smem_raw + SM::off_warp);
+
     const unsigned n = load_count(cnt);
     const unsigned base = blockIdx.x * (unsigned)RS_TILE;
     if (base >= n) return;
+    const int m = (int)min((unsigned)RS_TILE, n - base);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // the block's input on its way to shared memory (16-byte chunks; the arrays are padded, a chunk never leaves them)
+    {
+        constexpr int KV = 16 / sizeof(KeyT);
+        const int kchunks = (m + KV - 1) / KV, vchunks = (m + 3) / 4;
+        for (int c = tid; c < kchunks; c += RS_THREADS) cp_async16(s_ikey + c * KV, keys_in + base + c * KV);
+        if (vals_in)
+            for (int c = tid; c < vchunks; c += RS_THREADS) cp_async16(s_ival + c * 4, vals_in + base + c * 4);
+    }
     tr.init();
-    const int bins = tr.bins(), tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bins = tr.bins();
     for (int d = tid; d < bins; d += RS_THREADS) {
         s_base[d] = __ldg(totals + d);
 #pragma unroll
@@ -202,30 +262,31 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(TR tr, const 
     __syncthreads();
     block_excl_scan(s_base, bins, s_warp);
     for (int d = tid; d < bins; d += RS_THREADS) s_base[d] += __ldg(matrix + (size_t)d * stride + blockIdx.x);
+    cp_async_commit_wait_all();
+    __syncthreads();
 
-    // a warp owns 512 consecutive elements: 16 rounds of 32, in order
-    KeyT k[RS_ITEMS];
-    uint32_t v[RS_ITEMS], rank[RS_ITEMS];
-    const unsigned wbase = base + warp * (RS_ITEMS * 32);
-#pragma unroll
-    for (int e = 0; e < RS_ITEMS; e++) {
-        const unsigned idx = wbase + e * 32 + lane;
-        const bool in = idx < n;
-        k[e] = in ? keys_in[idx] : (KeyT)0;
-        v[e] = vals_in ? (in ? __ldg(vals_in + idx) : 0u) : idx;
-    }
+    // stable ranks: a warp owns 512 consecutive elements, 16 rounds of 32 in order; the lowest lane of every digit
+    // group of a round bumps the warp's private counter of that digit and hands the old value to its group
+    uint32_t rank2[RS_ITEMS / 2];                            // two 16-bit ranks per register (0xffff: not an element)
     const unsigned lt = (1u << lane) - 1u;
+    const int t0 = warp * (RS_ITEMS * 32) + lane;
 #pragma unroll
     for (int e = 0; e < RS_ITEMS; e++) {
-        const unsigned idx = wbase + e * 32 + lane;
-        const bool ok = idx < n && tr.valid(k[e]);
-        const uint32_t dd = ok ? tr.digit(k[e]) : 0xffffffffu;
+        const int t = t0 + e * 32;
+        const KeyT key = s_ikey[t < m ? t : 0];
+        const bool ok = t < m && tr.valid(key);
+        const uint32_t dd = ok ? tr.digit(key) : 0xffffffffu;
         const unsigned peers = __match_any_sync(FULLMASK, dd);
-        const uint32_t prev = ok ? s_whist[warp][dd] : 0u;
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (ok && lane == leader) {
+            old = s_whist[warp][dd];
+            s_whist[warp][dd] = (uint16_t)(old + __popc(peers));
+        }
+        old = __shfl_sync(FULLMASK, old, leader);
         __syncwarp();
-        rank[e] = ok ? prev + __popc(peers & lt) : 0xffffffffu;
-        if (ok && lane == __ffs(peers) - 1) s_whist[warp][dd] = (uint16_t)(prev + __popc(peers));
-        __syncwarp();
+        const uint32_t r = ok ? old + __popc(peers & lt) : 0xffffu;
+        if (e & 1) rank2[e >> 1] |= r << 16; else rank2[e >> 1] = r;
     }
     __syncthreads();
     for (int d = tid; d < bins; d += RS_THREADS) {
@@ -242,11 +303,14 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(TR tr, const 
     if (!TR::STAGE) {
 #pragma unroll
         for (int e = 0; e < RS_ITEMS; e++) {
-            if (rank[e] != 0xffffffffu) {
-                const uint32_t dd = tr.digit(k[e]);
-                const uint32_t pos = s_base[dd] + s_whist[warp][dd] + rank[e];
-                if (keys_out) keys_out[pos] = k[e];
-                vals_out[pos] = v[e];
+            const uint32_t r = (e & 1) ? rank2[e >> 1] >> 16 : rank2[e >> 1] & 0xffffu;
+            if (r != 0xffffu) {
+                const int t = t0 + e * 32;
+                const KeyT key = s_ikey[t];
+                const uint32_t dd = tr.digit(key);
+                const uint32_t pos = s_base[dd] + s_whist[warp][dd] + r;
+                if (keys_out) keys_out[pos] = key;
+                vals_out[pos] = vals_in ? s_ival[t] : base + (unsigned)t;
             }
         }
         return;
@@ -254,26 +318,29 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(TR tr, const 
     block_excl_scan(s_lstart, bins, s_warp);
 #pragma unroll
     for (int e = 0; e < RS_ITEMS; e++) {
-        if (rank[e] != 0xffffffffu) {
-            const uint32_t dd = tr.digit(k[e]);
-            const uint32_t li = s_lstart[dd] + s_whist[warp][dd] + rank[e];
-            s_key[li] = k[e];
-            s_val[li] = v[e];
+        const uint32_t r = (e & 1) ? rank2[e >> 1] >> 16 : rank2[e >> 1] & 0xffffu;
+        if (r != 0xffffu) {
+            const int t = t0 + e * 32;
+            const KeyT key = s_ikey[t];
+            const uint32_t dd = tr.digit(key);
+            const uint32_t li = s_lstart[dd] + s_whist[warp][dd] + r;
+            s_okey[li] = key;
+            s_oval[li] = s_ival[t];
         }
     }
     __syncthreads();
-    const int m = (int)min((unsigned)RS_TILE, n - base);     // every element of a staged pass is valid
-    for (int i = tid; i < m; i += RS_THREADS) {
-        const KeyT key = s_key[i];
-        const uint32_t dd = tr.digit(key);
-        const uint32_t pos = s_base[dd] + ((uint32_t)i - s_lstart[dd]);
-        vals_out[pos] = s_val[i];
+    for (int d = tid; d < bins; d += RS_THREADS) s_base[d] -= s_lstart[d];      // position = s_base[digit] + slot
+    __syncthreads();
+    for (int i = tid; i < m; i += RS_THREADS) {              // every element of a staged pass is valid
+        const KeyT key = s_okey[i];
+        const uint32_t pos = s_base[tr.digit(key)] + (uint32_t)i;
+        vals_out[pos] = s_oval[i];
         if (keys_out) keys_out[pos] = key;
         if (ranges) {
             // all pairs of a tile are contiguous in this pass's output: start = min position, end = max position + 1.
             // The start is kept as max(~position) so that zero-filled ranges are the identity (launch_tile_order decodes).
-            if (i == 0 || s_key[i - 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].x), ~pos);
-            if (i == m - 1 || s_key[i + 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].y), pos + 1u);
+            if (i == 0 || s_okey[i - 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].x), ~pos);
+            if (i == m - 1 || s_okey[i + 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].y), pos + 1u);
         }
     }
 }
@@ -282,9 +349,19 @@ template <class TR>
 cudaError_t radix_pass(TR tr, const typename TR::KeyT* keys_in, const uint32_t* vals_in, typename TR::KeyT* keys_out,
                        uint32_t* vals_out, Count cnt, int blocks, uint32_t* matrix, uint32_t* totals, int2* ranges,
                        cudaStream_t s) {
+    constexpr size_t smem = ScatterSmem<TR>::bytes;
+    static bool configured[64] = {false};                    // per instantiation and device: the attribute is per function
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (!configured[dev & 63]) {
+        e = cudaFuncSetAttribute(radix_scatter_kernel<TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured[dev & 63] = true;
+    }
     radix_count_kernel<TR><<<blocks, RS_THREADS, 0, s>>>(tr, keys_in, cnt, blocks, matrix);
     radix_colscan_kernel<TR><<<(TR::MAXBINS * 32 + RS_THREADS - 1) / RS_THREADS, RS_THREADS, 0, s>>>(tr, cnt, blocks, matrix, totals);
-    radix_scatter_kernel<TR><<<blocks, RS_THREADS, 0, s>>>(tr, keys_in, vals_in, keys_out, vals_out, cnt, blocks, matrix, totals, ranges);
+    radix_scatter_kernel<TR><<<blocks, RS_THREADS, smem, s>>>(tr, keys_in, vals_in, keys_out, vals_out, cnt, blocks, matrix, totals, ranges);
     return cudaGetLastError();
 }
 
@@ -642,7 +719,7 @@ cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, unsigned i
 template <typename K>
 static cudaError_t tile_sort_impl(BinView bv, int gx, int gy, ImgView iv, cudaStream_t s) {
     const Count pairs{iv.counters + CTR_PAIRS, (unsigned)bv.cap, 1};
-    const unsigned long long magic = (1ull << 32) / (unsigned long long)gx + 1ull;
+    const uint32_t magic = gx > 1 ? (uint32_t)((1ull << 32) / (unsigned long long)gx + 1ull) : 0u;
     TileTraits<K> by_col{gx, gx, 0, magic}, by_row{gx, gy, 1, magic};
     cudaError_t e = radix_pass(by_col, (const K*)bv.key_a, (const uint32_t*)bv.val_a, (K*)bv.key_b, bv.val_b, pairs, bv.tblocks,
                                bv.tmatrix, bv.ttotals, nullptr, s);
