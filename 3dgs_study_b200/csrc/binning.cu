@@ -7,14 +7,15 @@
 // Gaussian id), exactly what a stable sort of (tile << 32 | depth) keys emitted in Gaussian order
 // yields -- but the traffic is a fraction of it (see splat_internal.cuh "Binning order"):
 //
-//   1. depth order   stable LSD radix sort of the V visible (depth bits, id) pairs, 3 passes.  The first pass reads
+//   1. depth order   stable LSD radix sort of the V visible (depth bits, id) pairs, 4 passes.  The first pass reads
 //                    the P depth keys in index order, drops the culled ones and supplies the ids itself (no iota
 //                    array, no separate compaction); the digit width adapts to the key range seen by the
-//                    preprocess kernel (min / max in the control block): 26 significant bits -> 3 x 9.
-//   2. offsets       inclusive scan of tiles touched, in depth order (reduce / spine / apply kernels)
+//                    preprocess kernel (min / max in the control block): 26 significant bits -> 4 x 7.
+//   2. offsets       the last depth pass adds the tiles touched by every Gaussian to the pair count of the emit
+//                    block its depth position falls in; one small kernel scans those ~V/256 counts
 //   3. emit          block-cooperative duplicateWithKeys: a block owns 256 consecutive Gaussians of the
-//                    depth order and therefore a CONTIGUOUS output range; consecutive threads write
-//                    consecutive (tile id, Gaussian id) slots, so the writes are fully coalesced
+//                    depth order and therefore a CONTIGUOUS output range (it scans its own 256 counts);
+//                    consecutive threads write consecutive (tile id, Gaussian id) slots: fully coalesced
 //   4. tile sort     stable LSD sort on the tile id, 2 passes: by tile column (tile % gx), then by tile row
 //                    (tile / gx).  The second pass writes only the Gaussian ids (nobody needs sorted keys) and
 //                    publishes the tile ranges itself: all pairs of a tile are contiguous in its output, so the
@@ -26,8 +27,9 @@
 //   colscan  one warp per digit: exclusive scan of its matrix row over the blocks, row total -> totals[digit]
 //   scatter  per block: digit bases (scan of totals) + its matrix column = where its elements of each digit go;
 //            stable ranks inside the block from warp-level match_any (a warp owns 512 consecutive elements,
-//            16 rounds of 32 in order) + a prefix over the 8 warps; the tile passes stage the block in shared
-//            memory in sorted order so that every digit leaves as one contiguous run.
+//            16 rounds of 32 in order) + a prefix over the 8 warps; the block is staged in shared memory in
+//            sorted order so that every digit leaves as one contiguous run (scattered 4-byte stores cost a
+//            whole 32-byte sector each at the L2: measured 89 G sectors/s, 3x the time of the staged form).
 // The element counts (V, R) live in the image buffer's control block and are read by the kernels; grids are
 // sized for the host-known bounds (P, pair capacity) and surplus blocks exit at once.
 #include "splat_internal.cuh"
@@ -39,8 +41,10 @@ namespace {
 constexpr unsigned FULLMASK = 0xffffffffu;
 constexpr int RS_THREADS = 256, RS_WARPS = RS_THREADS / 32, RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;              // 4096 elements per block
-constexpr int DEPTH_MAXBINS = 2048;                         // 3 passes x <= 11 bits cover any 32-bit key range
+constexpr int DEPTH_MAXBINS = 256;                          // 4 passes x <= 8 bits cover any 32-bit key range
+constexpr int DEPTH_PASSES = 4;
 constexpr int TILE_MAXBINS = 512;                           // tile columns / rows: images up to 8192 x 8192
+constexpr int EMIT_THREADS = 256;                           // Gaussians per block of the emit kernel
 
 // blocks covering n elements, rounded up to a multiple of 4 (the column scan walks matrix rows 16 bytes at a time)
 inline int radix_blocks(size_t n) {
@@ -65,21 +69,29 @@ __device__ __forceinline__ unsigned load_count(Count c) {
 struct DepthTraits {
     using KeyT = uint32_t;
     static constexpr int MAXBINS = DEPTH_MAXBINS;
-    static constexpr bool STAGE = false;
+    static constexpr bool STAGE = true;
     const unsigned* ctr;      // control block: key range of the visible Gaussians
     int pass;
+    const uint2* rect;        // last pass only: tiles touched by the Gaussian landing at depth position `pos` are added to
+    uint32_t* emit_part;      //   emit_part[pos / EMIT_THREADS] (the per-block pair counts the emit kernel's offsets come from)
     uint32_t kmin, mask;      // set by init()
     int shift, nbins;
     __device__ __forceinline__ void init() {
         const uint32_t kmn = ~__ldg(ctr + CTR_KMIN_NEG), kmx = __ldg(ctr + CTR_KMAX);
         const uint32_t span = kmx >= kmn ? kmx - kmn : 0u;
         const int bits = 32 - __clz((int)span);             // __clz(0) = 32
-        const int w = max(1, (bits + 2) / 3);               // three passes cover `bits`; w <= 11
+        const int w = max(1, (bits + DEPTH_PASSES - 1) / DEPTH_PASSES);      // the passes cover `bits`; w <= 8
         kmin = kmn; shift = pass * w; mask = (1u << w) - 1u; nbins = 1 << w;
     }
     __device__ __forceinline__ bool valid(uint32_t k) const { return k != 0xffffffffu; }
     __device__ __forceinline__ uint32_t digit(uint32_t k) const { return ((k - kmin) >> shift) & mask; }
     __device__ __forceinline__ int bins() const { return nbins; }
+    __device__ __forceinline__ void on_output(uint32_t pos, uint32_t id) const {
+        if (emit_part) {
+            const uint32_t wh = __ldg(&rect[id].y);
+            atomicAdd(emit_part + pos / EMIT_THREADS, (wh & 0xffffu) * (wh >> 16));
+        }
+    }
 };
 
 template <typename K>
@@ -97,6 +109,7 @@ struct TileTraits {
         return by_row ? q : t - q * (uint32_t)gx;
     }
     __device__ __forceinline__ int bins() const { return nbins; }
+    __device__ __forceinline__ void on_output(uint32_t, uint32_t) const {}
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
@@ -109,8 +122,8 @@ __device__ __forceinline__ void cp_async_commit_wait_all() {
 }
 
 // In-place exclusive scan of s[0..n), n <= 2048, by a 256-thread block (s fully written and synchronised by the
-// caller; synchronised again on return).
-__device__ __forceinline__ void block_excl_scan(uint32_t* s, int n, uint32_t* s_warp) {
+// caller; synchronised again on return).  Returns the total.
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t* s, int n, uint32_t* s_warp) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int per = (n + RS_THREADS - 1) / RS_THREADS;      // <= 8
     const int b0 = tid * per;
@@ -128,23 +141,32 @@ __device__ __forceinline__ void block_excl_scan(uint32_t* s, int n, uint32_t* s_
     }
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    uint32_t run = incl - sum;
-    for (int w = 0; w < warp; w++) run += s_warp[w];
+    uint32_t run = incl - sum, total = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) {
+        const uint32_t t = s_warp[w];
+        if (w < warp) run += t;
+        total += t;
+    }
 #pragma unroll
     for (int k = 0; k < 8; k++) {
         if (k < per && b0 + k < n) { s[b0 + k] = run; run += v[k]; }
     }
     __syncthreads();
+    return total;
 }
 
 // ---- one radix pass: count / colscan / scatter ---------------------------------------------------------
 // count: 16-byte loads (8 u16 / 4 u32 keys each), all of a thread's loads in flight before the first histogram update
 template <class TR>
 __global__ void __launch_bounds__(RS_THREADS) radix_count_kernel(TR tr, const typename TR::KeyT* __restrict__ keys, Count cnt,
-                                                                 int stride, uint32_t* __restrict__ matrix) {
+                                                                 int stride, uint32_t* __restrict__ matrix,
+                                                                 uint32_t* __restrict__ zero_ptr, int zero_n) {
     using KeyT = typename TR::KeyT;
     constexpr int VEC = 16 / sizeof(KeyT), NLOAD = RS_ITEMS / VEC;
     __shared__ unsigned s_hist[TR::MAXBINS];
+    // housekeeping for a later stage (the emit kernel's per-block pair counts start from zero)
+    for (int i = blockIdx.x * RS_THREADS + threadIdx.x; i < zero_n; i += gridDim.x * RS_THREADS) zero_ptr[i] = 0u;
     const unsigned n = load_count(cnt);
     const unsigned base = blockIdx.x * (unsigned)RS_TILE;
     if (base >= n) return;
@@ -170,36 +192,58 @@ __global__ void __launch_bounds__(RS_THREADS) radix_count_kernel(TR tr, const ty
     for (int d = tid; d < bins; d += RS_THREADS) matrix[(size_t)d * stride + blockIdx.x] = s_hist[d];
 }
 
-// colscan: one warp per digit; a lane takes 4 consecutive blocks per step (the row stride is a multiple of 4)
+// colscan: one block per digit.  Its 8 warps take consecutive eighths of the matrix row (a lane 4 consecutive blocks
+// per step: the row stride is a multiple of 4): segment sums first, then every warp scans its segment from its base.
 template <class TR>
 __global__ void __launch_bounds__(RS_THREADS) radix_colscan_kernel(TR tr, Count cnt, int stride, uint32_t* __restrict__ matrix,
                                                                    uint32_t* __restrict__ totals) {
-    const int lane = threadIdx.x & 31;
-    const int d = (blockIdx.x * RS_THREADS + threadIdx.x) >> 5;          // one warp per digit
+    __shared__ uint32_t s_seg[RS_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int d = blockIdx.x;
     tr.init();
     if (d >= tr.bins()) return;
     const unsigned n = load_count(cnt);
     const int nb = (int)((n + RS_TILE - 1) / RS_TILE);
+    const int nq = (nb + 3) >> 2;                                         // 16-byte groups in the row
+    const int per = ((nq + RS_WARPS - 1) / RS_WARPS + 31) & ~31;          // groups per warp, whole steps of 32
+    const int q0 = warp * per, q1 = min(nq, q0 + per);
     uint4* row = reinterpret_cast<uint4*>(matrix + (size_t)d * stride);
-    uint32_t run = 0;
-    for (int b0 = 0; b0 < nb; b0 += 128) {
-        const int b = b0 + 4 * lane;
-        uint4 v = b < nb ? row[b >> 2] : make_uint4(0u, 0u, 0u, 0u);
+    auto load = [&](int q) -> uint4 {
+        uint4 v = q < q1 ? row[q] : make_uint4(0u, 0u, 0u, 0u);
+        const int b = 4 * q;
         if (b + 1 >= nb) v.y = 0u;
         if (b + 2 >= nb) v.z = 0u;
         if (b + 3 >= nb) v.w = 0u;
-        const uint32_t sum = v.x + v.y + v.z + v.w;
-        uint32_t incl = sum;
+        if (b >= nb) v.x = 0u;
+        return v;
+    };
+    uint32_t sum = 0;
+    for (int q = q0 + lane; q < q1; q += 32) { const uint4 v = load(q); sum += v.x + v.y + v.z + v.w; }
+    sum = __reduce_add_sync(FULLMASK, sum);
+    if (lane == 0) s_seg[warp] = sum;
+    __syncthreads();
+    uint32_t run = 0, total = 0;
 #pragma unroll
-        for (int s = 1; s < 32; s <<= 1) {
-            const uint32_t t = __shfl_up_sync(FULLMASK, incl, s);
-            if (lane >= s) incl += t;
+    for (int w = 0; w < RS_WARPS; w++) {
+        const uint32_t t = s_seg[w];
+        if (w < warp) run += t;
+        total += t;
+    }
+    for (int qs = q0; qs < q1; qs += 32) {
+        const int q = qs + lane;
+        const uint4 v = load(q);
+        const uint32_t part = v.x + v.y + v.z + v.w;
+        uint32_t incl = part;
+#pragma unroll
+        for (int sft = 1; sft < 32; sft <<= 1) {
+            const uint32_t t = __shfl_up_sync(FULLMASK, incl, sft);
+            if (lane >= sft) incl += t;
         }
-        const uint32_t e0 = run + incl - sum;
-        if (b < nb) row[b >> 2] = make_uint4(e0, e0 + v.x, e0 + v.x + v.y, e0 + v.x + v.y + v.z);
+        const uint32_t e0 = run + incl - part;
+        if (q < q1) row[q] = make_uint4(e0, e0 + v.x, e0 + v.x + v.y, e0 + v.x + v.y + v.z);
         run += __shfl_sync(FULLMASK, incl, 31);
     }
-    if (lane == 0) totals[d] = run;
+    if (threadIdx.x == 0) totals[d] = total;
 }
 
 // scatter.  Shared memory (dynamic): digit bases, per-warp digit counts, the block's 4096 (key, value) pairs as they
@@ -266,27 +310,37 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
     __syncthreads();
 
     // stable ranks: a warp owns 512 consecutive elements, 16 rounds of 32 in order; the lowest lane of every digit
-    // group of a round bumps the warp's private counter of that digit and hands the old value to its group
+    // group of a round bumps the warp's private counter of that digit and hands the old value to its group.  The
+    // match instructions of 8 rounds are issued together (they depend on nothing but the keys), then the counters
+    // are walked in order.
     uint32_t rank2[RS_ITEMS / 2];                            // two 16-bit ranks per register (0xffff: not an element)
     const unsigned lt = (1u << lane) - 1u;
     const int t0 = warp * (RS_ITEMS * 32) + lane;
 #pragma unroll
-    for (int e = 0; e < RS_ITEMS; e++) {
-        const int t = t0 + e * 32;
-        const KeyT key = s_ikey[t < m ? t : 0];
-        const bool ok = t < m && tr.valid(key);
-        const uint32_t dd = ok ? tr.digit(key) : 0xffffffffu;
-        const unsigned peers = __match_any_sync(FULLMASK, dd);
-        const int leader = __ffs(peers) - 1;
-        uint32_t old = 0;
-        if (ok && lane == leader) {
-            old = s_whist[warp][dd];
-            s_whist[warp][dd] = (uint16_t)(old + __popc(peers));
+    for (int g = 0; g < RS_ITEMS; g += 8) {
+        uint32_t dd[8];
+        unsigned peers[8];
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const int t = t0 + (g + e) * 32;
+            const KeyT key = s_ikey[t < m ? t : 0];
+            dd[e] = (t < m && tr.valid(key)) ? tr.digit(key) : 0xffffffffu;
+            peers[e] = __match_any_sync(FULLMASK, dd[e]);
         }
-        old = __shfl_sync(FULLMASK, old, leader);
-        __syncwarp();
-        const uint32_t r = ok ? old + __popc(peers & lt) : 0xffffu;
-        if (e & 1) rank2[e >> 1] |= r << 16; else rank2[e >> 1] = r;
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const bool ok = dd[e] != 0xffffffffu;
+            const int leader = __ffs(peers[e]) - 1;
+            uint32_t old = 0;
+            if (ok && lane == leader) {
+                old = s_whist[warp][dd[e]];
+                s_whist[warp][dd[e]] = (uint16_t)(old + __popc(peers[e]));
+            }
+            old = __shfl_sync(FULLMASK, old, leader);
+            __syncwarp();
+            const uint32_t r = ok ? old + __popc(peers[e] & lt) : 0xffffu;
+            if (e & 1) rank2[(g + e) >> 1] |= r << 16; else rank2[(g + e) >> 1] = r;
+        }
     }
     __syncthreads();
     for (int d = tid; d < bins; d += RS_THREADS) {
@@ -309,13 +363,15 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
                 const KeyT key = s_ikey[t];
                 const uint32_t dd = tr.digit(key);
                 const uint32_t pos = s_base[dd] + s_whist[warp][dd] + r;
+                const uint32_t val = vals_in ? s_ival[t] : base + (unsigned)t;
                 if (keys_out) keys_out[pos] = key;
-                vals_out[pos] = vals_in ? s_ival[t] : base + (unsigned)t;
+                vals_out[pos] = val;
+                tr.on_output(pos, val);
             }
         }
         return;
     }
-    block_excl_scan(s_lstart, bins, s_warp);
+    const int mv = (int)block_excl_scan(s_lstart, bins, s_warp);          // elements of the block that take part
 #pragma unroll
     for (int e = 0; e < RS_ITEMS; e++) {
         const uint32_t r = (e & 1) ? rank2[e >> 1] >> 16 : rank2[e >> 1] & 0xffffu;
@@ -325,22 +381,29 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
             const uint32_t dd = tr.digit(key);
             const uint32_t li = s_lstart[dd] + s_whist[warp][dd] + r;
             s_okey[li] = key;
-            s_oval[li] = s_ival[t];
+            s_oval[li] = vals_in ? s_ival[t] : base + (unsigned)t;
         }
     }
     __syncthreads();
     for (int d = tid; d < bins; d += RS_THREADS) s_base[d] -= s_lstart[d];      // position = s_base[digit] + slot
     __syncthreads();
-    for (int i = tid; i < m; i += RS_THREADS) {              // every element of a staged pass is valid
+    for (int i = tid; i < mv; i += RS_THREADS) {
         const KeyT key = s_okey[i];
+        const uint32_t val = s_oval[i];
         const uint32_t pos = s_base[tr.digit(key)] + (uint32_t)i;
-        vals_out[pos] = s_oval[i];
+        vals_out[pos] = val;
         if (keys_out) keys_out[pos] = key;
+        tr.on_output(pos, val);
         if (ranges) {
             // all pairs of a tile are contiguous in this pass's output: start = min position, end = max position + 1.
-            // The start is kept as max(~position) so that zero-filled ranges are the identity (launch_tile_order decodes).
-            if (i == 0 || s_okey[i - 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].x), ~pos);
-            if (i == m - 1 || s_okey[i + 1] != key) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].y), pos + 1u);
+            // The start is kept as max(~position) so that zero-filled ranges are the identity (launch_tile_order
+            // decodes).  A run boundary inside the block closes the previous tile's run and opens this one's.
+            const KeyT prev = i > 0 ? s_okey[i - 1] : key;
+            if (i == 0 || prev != key) {
+                atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].x), ~pos);
+                if (i > 0) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)prev].y), s_base[tr.digit(prev)] + (uint32_t)i);
+            }
+            if (i == mv - 1) atomicMax(reinterpret_cast<unsigned*>(&ranges[(uint32_t)key].y), pos + 1u);
         }
     }
 }
@@ -348,7 +411,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
 template <class TR>
 cudaError_t radix_pass(TR tr, const typename TR::KeyT* keys_in, const uint32_t* vals_in, typename TR::KeyT* keys_out,
                        uint32_t* vals_out, Count cnt, int blocks, uint32_t* matrix, uint32_t* totals, int2* ranges,
-                       cudaStream_t s) {
+                       cudaStream_t s, uint32_t* zero_ptr = nullptr, int zero_n = 0) {
     constexpr size_t smem = ScatterSmem<TR>::bytes;
     static bool configured[64] = {false};                    // per instantiation and device: the attribute is per function
     int dev = 0;
@@ -359,8 +422,8 @@ cudaError_t radix_pass(TR tr, const typename TR::KeyT* keys_in, const uint32_t* 
         if (e != cudaSuccess) return e;
         configured[dev & 63] = true;
     }
-    radix_count_kernel<TR><<<blocks, RS_THREADS, 0, s>>>(tr, keys_in, cnt, blocks, matrix);
-    radix_colscan_kernel<TR><<<(TR::MAXBINS * 32 + RS_THREADS - 1) / RS_THREADS, RS_THREADS, 0, s>>>(tr, cnt, blocks, matrix, totals);
+    radix_count_kernel<TR><<<blocks, RS_THREADS, 0, s>>>(tr, keys_in, cnt, blocks, matrix, zero_ptr, zero_n);
+    radix_colscan_kernel<TR><<<TR::MAXBINS, RS_THREADS, 0, s>>>(tr, cnt, blocks, matrix, totals);
     radix_scatter_kernel<TR><<<blocks, RS_THREADS, smem, s>>>(tr, keys_in, vals_in, keys_out, vals_out, cnt, blocks, matrix, totals, ranges);
     return cudaGetLastError();
 }
@@ -408,12 +471,12 @@ __global__ void __launch_bounds__(RS_THREADS) scan_reduce_kernel(F f, Count cnt,
     }
 }
 
-// exclusive scan of the block partials, one block (any number of partials)
-__global__ void __launch_bounds__(1024) scan_spine_kernel(Count cnt, uint32_t* __restrict__ part) {
+// exclusive scan of the block partials, one block (any number of partials = ceil(count / per_block))
+__global__ void __launch_bounds__(1024) scan_spine_kernel(Count cnt, int per_block, uint32_t* __restrict__ part) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_carry;
     const unsigned n = load_count(cnt);
-    const int nb = (int)((n + RS_TILE - 1) / RS_TILE);
+    const int nb = (int)((n + per_block - 1) / per_block);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_carry = 0u;
     __syncthreads();
@@ -478,7 +541,7 @@ __global__ void __launch_bounds__(RS_THREADS) scan_apply_kernel(F f, Count cnt, 
 template <class F>
 cudaError_t inclusive_scan(F f, Count cnt, int blocks, uint32_t* part, uint32_t* out, cudaStream_t s) {
     scan_reduce_kernel<F><<<blocks, RS_THREADS, 0, s>>>(f, cnt, part);
-    scan_spine_kernel<<<1, 1024, 0, s>>>(cnt, part);
+    scan_spine_kernel<<<1, 1024, 0, s>>>(cnt, RS_TILE, part);
     scan_apply_kernel<F><<<blocks, RS_THREADS, 0, s>>>(f, cnt, part, out);
     return cudaGetLastError();
 }
@@ -498,9 +561,10 @@ GeomView carve_geom(void* base, int P) {
     g.dval_a = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
     g.dkey_b = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
     g.dval_b = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
-    g.order = g.dval_a;
-    g.offsets = (uint32_t*)(b + off); off += align256(n * sizeof(uint32_t));
+    g.order = g.dval_b;                                      // four passes: depths -> a -> b -> a -> b
     g.dblocks = radix_blocks(n);
+    g.emit_blocks = (int)((n + EMIT_THREADS - 1) / EMIT_THREADS);
+    g.emit_part = (uint32_t*)(b + off); off += align256(((size_t)g.emit_blocks + 1) * sizeof(uint32_t));
     g.scan_part = (uint32_t*)(b + off); off += align256(((size_t)g.dblocks + 1) * sizeof(uint32_t));
     g.dmatrix = (uint32_t*)(b + off); off += align256((size_t)DEPTH_MAXBINS * g.dblocks * sizeof(uint32_t));
     g.dtotals = (uint32_t*)(b + off); off += align256((size_t)DEPTH_MAXBINS * sizeof(uint32_t));
@@ -545,22 +609,23 @@ ImgView carve_image(void* base, int W, int H) {
 
 namespace {
 
-constexpr int EMIT_THREADS = 256;
-
-// Block-cooperative duplicateWithKeys.  Block b owns depth-order positions [256 b, 256 b + 256) and the
-// output slots [offsets[256 b - 1], offsets[256 b + 255]).  Slot k of Gaussian g (rect minx, miny, w, h)
-// is tile (miny + k / w) * gx + minx + k % w: row-major over the rectangle, as the oracle emits.
-// V (visible Gaussians) comes from the control block; slots at or beyond the pair capacity are not written.
+// Block-cooperative duplicateWithKeys.  Block b owns depth-order positions [256 b, 256 b + 256) and a CONTIGUOUS range
+// of output slots: it starts at part[b], the exclusive prefix of the per-block pair counts (accumulated by the last
+// depth pass, scanned by scan_spine_kernel), and the block scans the tiles touched by its own 256 Gaussians itself.
+// Slot k of Gaussian g (rect minx, miny, w, h) is tile (miny + k / w) * gx + minx + k % w: row-major over the
+// rectangle, as the oracle emits.  V (visible Gaussians) comes from the control block; slots at or beyond the pair
+// capacity are not written.
 template <typename KeyT>
 __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int gx, const uint32_t* __restrict__ order,
                                                                  const uint2* __restrict__ rect,
-                                                                 const uint32_t* __restrict__ offsets,
+                                                                 const uint32_t* __restrict__ part,
                                                                  KeyT* __restrict__ keys, uint32_t* __restrict__ vals,
                                                                  unsigned cap, unsigned int* __restrict__ counters) {
     __shared__ uint32_t s_end[EMIT_THREADS];     // inclusive offsets of this block's Gaussians
     __shared__ uint32_t s_id[EMIT_THREADS];
     __shared__ uint2 s_rect[EMIT_THREADS];
-    const int tid = threadIdx.x;
+    __shared__ uint32_t s_wsum[EMIT_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int V = (int)__ldg(counters + CTR_VISIBLE);
     const int j0 = blockIdx.x * EMIT_THREADS;
     if (blockIdx.x == 0 && tid == 0) {           // status of the view (b200splat_forward_status)
@@ -570,12 +635,27 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int gx, const u
         counters[CTR_STATUS + 3] = (hi != 0u || lo > cap) ? 1u : 0u;
     }
     if (j0 >= V) return;
-    const int j = min(j0 + tid, V - 1);
-    const uint32_t id = __ldg(order + j);
+    const uint32_t base = __ldg(part + blockIdx.x);
+    uint32_t id = 0, tiles = 0;
+    uint2 r0 = make_uint2(0u, 0u);
+    if (j0 + tid < V) {
+        id = __ldg(order + j0 + tid);
+        r0 = __ldg(rect + id);
+        tiles = (r0.y & 0xffffu) * (r0.y >> 16);
+    }
     s_id[tid] = id;
-    s_rect[tid] = __ldg(rect + id);
-    s_end[tid] = __ldg(offsets + j);
-    const uint32_t base = j0 == 0 ? 0u : __ldg(offsets + j0 - 1);
+    s_rect[tid] = r0;
+    uint32_t incl = tiles;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULLMASK, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    uint32_t wb = base;
+    for (int w = 0; w < warp; w++) wb += s_wsum[w];
+    s_end[tid] = wb + incl;                      // positions past V repeat the last offset (no tiles)
     __syncthreads();
     // Each thread owns four consecutive output slots (aligned to 4 so full groups go out as one vector store
     // per array): one binary search and one division for the first slot, then a linear walk.
@@ -592,7 +672,7 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int gx, const u
         uint2 r = s_rect[g];
         uint32_t w = r.y & 0xffffu;
         uint32_t gend = s_end[g];
-        uint32_t id = s_id[g];
+        uint32_t gid = s_id[g];
         const uint32_t local = s0 - (gend - w * (r.y >> 16));
         const uint32_t row = local / w;
         uint32_t col = local - row * w;
@@ -606,11 +686,11 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_keys_kernel(int gx, const u
             if (sl >= s0 && sl < end) {
                 while (sl >= gend) {                 // next Gaussian with tiles: restart at its first tile
                     g++;
-                    r = s_rect[g]; w = r.y & 0xffffu; gend = s_end[g]; id = s_id[g];
+                    r = s_rect[g]; w = r.y & 0xffffu; gend = s_end[g]; gid = s_id[g];
                     col = 0;
                     tile = (r.x >> 16) * (uint32_t)gx + (r.x & 0xffffu);
                 }
-                kk[e] = (KeyT)tile; vv[e] = id;
+                kk[e] = (KeyT)tile; vv[e] = gid;
                 col++; tile++;
                 if (col == w) { col = 0; tile += (uint32_t)gx - w; }
             }
@@ -689,18 +769,23 @@ cudaError_t launch_depth_order(GeomView gv, int P, const unsigned int* counters,
     const int blocks = gv.dblocks;
     const Count all{nullptr, (unsigned)P, 0};                         // first pass: every key, culled ones dropped
     const Count vis{counters + CTR_VISIBLE, (unsigned)P, 0};          // then the V visible
-    DepthTraits t0{counters, 0}, t1{counters, 1}, t2{counters, 2};
+    DepthTraits t0{counters, 0, nullptr, nullptr}, t1{counters, 1, nullptr, nullptr}, t2{counters, 2, nullptr, nullptr},
+        t3{counters, 3, gv.rect, gv.emit_part};                       // the last pass also sums the pairs per emit block
     cudaError_t e;
     e = radix_pass(t0, reinterpret_cast<const uint32_t*>(gv.depths), (const uint32_t*)nullptr, gv.dkey_a, gv.dval_a, all, blocks,
-                   gv.dmatrix, gv.dtotals, nullptr, s);
+                   gv.dmatrix, gv.dtotals, nullptr, s, gv.emit_part, gv.emit_blocks + 1);
     if (e != cudaSuccess) return e;
     e = radix_pass(t1, (const uint32_t*)gv.dkey_a, (const uint32_t*)gv.dval_a, gv.dkey_b, gv.dval_b, vis, blocks, gv.dmatrix,
                    gv.dtotals, nullptr, s);
     if (e != cudaSuccess) return e;
-    e = radix_pass(t2, (const uint32_t*)gv.dkey_b, (const uint32_t*)gv.dval_b, (uint32_t*)nullptr, gv.order, vis, blocks, gv.dmatrix,
+    e = radix_pass(t2, (const uint32_t*)gv.dkey_b, (const uint32_t*)gv.dval_b, gv.dkey_a, gv.dval_a, vis, blocks, gv.dmatrix,
                    gv.dtotals, nullptr, s);
     if (e != cudaSuccess) return e;
-    return inclusive_scan(TilesInDepthOrder{gv.order, gv.rect}, vis, blocks, gv.scan_part, gv.offsets, s);
+    e = radix_pass(t3, (const uint32_t*)gv.dkey_a, (const uint32_t*)gv.dval_a, (uint32_t*)nullptr, gv.order, vis, blocks, gv.dmatrix,
+                   gv.dtotals, nullptr, s);
+    if (e != cudaSuccess) return e;
+    scan_spine_kernel<<<1, 1024, 0, s>>>(vis, EMIT_THREADS, gv.emit_part);     // pair counts per emit block -> their offsets
+    return cudaGetLastError();
 }
 
 cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, unsigned int* counters, cudaStream_t s) {
@@ -708,10 +793,10 @@ cudaError_t launch_emit(GeomView gv, int P, int W, int H, BinView bv, unsigned i
     const int gx = (W + TILE - 1) / TILE;
     const int blocks = (P + EMIT_THREADS - 1) / EMIT_THREADS;
     if (bv.key_bytes == 2)
-        emit_keys_kernel<uint16_t><<<blocks, EMIT_THREADS, 0, s>>>(gx, gv.order, gv.rect, gv.offsets, (uint16_t*)bv.key_a, bv.val_a,
+        emit_keys_kernel<uint16_t><<<blocks, EMIT_THREADS, 0, s>>>(gx, gv.order, gv.rect, gv.emit_part, (uint16_t*)bv.key_a, bv.val_a,
                                                                   (unsigned)bv.cap, counters);
     else
-        emit_keys_kernel<uint32_t><<<blocks, EMIT_THREADS, 0, s>>>(gx, gv.order, gv.rect, gv.offsets, (uint32_t*)bv.key_a, bv.val_a,
+        emit_keys_kernel<uint32_t><<<blocks, EMIT_THREADS, 0, s>>>(gx, gv.order, gv.rect, gv.emit_part, (uint32_t*)bv.key_a, bv.val_a,
                                                                   (unsigned)bv.cap, counters);
     return cudaGetLastError();
 }

@@ -10,10 +10,10 @@
 //                              rec[3i+1] = (hA, B, hC, thr)   hA = -A/2, hC = -C/2 (exact), power threshold
 //                              rec[3i+2] = (o, r, g, b)       effective opacity, colour
 //     rect     uint2[P]      tile rectangle (minx | miny << 16, w | h << 16); w*h = tiles touched (0 = culled)
-//     dkey_a/b u32[P] x2, dval_a/b u32[P] x2   ping-pong arrays of the depth sort; after its three passes
-//                            dval_a = `order`: the ids of the V visible Gaussians by (depth bits, id)
-//     offsets  u32[P]        inclusive scan of tiles touched IN DEPTH ORDER (V entries)
-//     scan_part, dmatrix, dtotals   block partials of the scan; digit-count matrix / totals of the depth-sort passes
+//     dkey_a/b u32[P] x2, dval_a/b u32[P] x2   ping-pong arrays of the depth sort; after its four passes
+//                            dval_b = `order`: the ids of the V visible Gaussians by (depth bits, id)
+//     emit_part u32[P/256+1] pairs emitted before each block of 256 depth positions
+//     scan_part, dmatrix, dtotals   block partials of the export scan; digit-count matrix / totals of the depth passes
 //   binning buffer (per (tile, Gaussian) pair, `cap` entries -- the pair CAPACITY, >= the pair count R unless the
 //   overflow flag is raised; tile keys are u16 when T <= 65536, else u32)
 //     key_a[cap], val_a[cap]   pairs as emitted (depth order); val_a is overwritten by the final, sorted ids
@@ -58,10 +58,12 @@ int report_error(int code, const char* msg);
 struct GeomView {
     float* depths; float4* rec; uint2* rect;
     uint32_t* dkey_a; uint32_t* dval_a; uint32_t* dkey_b; uint32_t* dval_b;
-    uint32_t* order;            // = dval_a: result of the depth sort
-    uint32_t* offsets; uint32_t* scan_part;
+    uint32_t* order;            // = dval_b: result of the depth sort
+    uint32_t* emit_part;        // pairs per emit block (256 depth positions) -> after the spine scan, their offsets
+    uint32_t* scan_part;        // block partials of the export-only scan
     uint32_t* dmatrix; uint32_t* dtotals;
     int dblocks;                // row stride of dmatrix = radix blocks covering P keys
+    int emit_blocks;
     size_t total;
 };
 struct BinView {
