@@ -86,11 +86,19 @@ struct DepthTraits {
     __device__ __forceinline__ bool valid(uint32_t k) const { return k != 0xffffffffu; }
     __device__ __forceinline__ uint32_t digit(uint32_t k) const { return ((k - kmin) >> shift) & mask; }
     __device__ __forceinline__ int bins() const { return nbins; }
-    __device__ __forceinline__ void on_output(uint32_t pos, uint32_t id) const {
-        if (emit_part) {
+    // called by a whole warp (inactive lanes pass live = false); the lanes that land in the same emit block -- nearly
+    // always all of them: they write consecutive positions -- add their tiles with ONE atomic
+    __device__ __forceinline__ void on_output(bool live, uint32_t pos, uint32_t id) const {
+        if (!emit_part) return;
+        uint32_t tiles = 0;
+        if (live) {
             const uint32_t wh = __ldg(&rect[id].y);
-            atomicAdd(emit_part + pos / EMIT_THREADS, (wh & 0xffffu) * (wh >> 16));
+            tiles = (wh & 0xffffu) * (wh >> 16);
         }
+        const uint32_t blk = live ? pos / EMIT_THREADS : 0xffffffffu;
+        const unsigned peers = __match_any_sync(FULLMASK, blk);
+        const uint32_t sum = __reduce_add_sync(peers, tiles);
+        if (live && (peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) atomicAdd(emit_part + blk, sum);
     }
 };
 
@@ -109,7 +117,7 @@ struct TileTraits {
         return by_row ? q : t - q * (uint32_t)gx;
     }
     __device__ __forceinline__ int bins() const { return nbins; }
-    __device__ __forceinline__ void on_output(uint32_t, uint32_t) const {}
+    __device__ __forceinline__ void on_output(bool, uint32_t, uint32_t) const {}
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
@@ -255,7 +263,7 @@ struct ScatterSmem {
     static constexpr size_t off_base = 0;
     static constexpr size_t off_lstart = off_base + sizeof(uint32_t) * MB;
     static constexpr size_t off_whist = off_lstart + (TR::STAGE ? sizeof(uint32_t) * MB : 0);
-    static constexpr size_t off_ikey = off_whist + sizeof(uint16_t) * RS_WARPS * MB;
+    static constexpr size_t off_ikey = off_whist + sizeof(uint32_t) * RS_WARPS * MB;
     static constexpr size_t off_ival = off_ikey + sizeof(KeyT) * RS_TILE;
     static constexpr size_t off_okey = off_ival + sizeof(uint32_t) * RS_TILE;
     static constexpr size_t off_oval = off_okey + (TR::STAGE ? sizeof(KeyT) * RS_TILE : 0);
@@ -276,7 +284,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_base = reinterpret_cast<uint32_t*>(smem_raw + SM::off_base);      // global position of the block's first element of each digit
     uint32_t* s_lstart = reinterpret_cast<uint32_t*>(smem_raw + SM::off_lstart);  // first slot of each digit in the block's sorted order
-    uint16_t (*s_whist)[MB] = reinterpret_cast<uint16_t (*)[MB]>(smem_raw + SM::off_whist);   // per-warp counts -> prefix over warps
+    uint32_t (*s_whist)[MB] = reinterpret_cast<uint32_t (*)[MB]>(smem_raw + SM::off_whist);   // per-warp counts -> prefix over warps
     KeyT* s_ikey = reinterpret_cast<KeyT*>(smem_raw + SM::off_ikey);
     uint32_t* s_ival = reinterpret_cast<uint32_t*>(smem_raw + SM::off_ival);
     KeyT* s_okey = reinterpret_cast<KeyT*>(smem_raw + SM::off_okey);
@@ -309,16 +317,17 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
     cp_async_commit_wait_all();
     __syncthreads();
 
-    // stable ranks: a warp owns 512 consecutive elements, 16 rounds of 32 in order; the lowest lane of every digit
-    // group of a round bumps the warp's private counter of that digit and hands the old value to its group.  The
-    // match instructions of 8 rounds are issued together (they depend on nothing but the keys), then the counters
-    // are walked in order.
+    // Stable ranks: a warp owns 512 consecutive elements, 16 rounds of 32 in order.  Per round, the lowest lane of
+    // every digit group adds the group's size to the warp's private counter of that digit and hands the old value to
+    // its group.  Nothing in a round waits for the round before: the match instructions of 8 rounds are issued
+    // together, then their 8 shared-memory atomics (a warp's atomics on one address execute in issue order, which is
+    // what makes the ranks stable), and only then the old values are read back and broadcast.
     uint32_t rank2[RS_ITEMS / 2];                            // two 16-bit ranks per register (0xffff: not an element)
     const unsigned lt = (1u << lane) - 1u;
     const int t0 = warp * (RS_ITEMS * 32) + lane;
 #pragma unroll
     for (int g = 0; g < RS_ITEMS; g += 8) {
-        uint32_t dd[8];
+        uint32_t dd[8], old[8];
         unsigned peers[8];
 #pragma unroll
         for (int e = 0; e < 8; e++) {
@@ -329,16 +338,13 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
         }
 #pragma unroll
         for (int e = 0; e < 8; e++) {
-            const bool ok = dd[e] != 0xffffffffu;
-            const int leader = __ffs(peers[e]) - 1;
-            uint32_t old = 0;
-            if (ok && lane == leader) {
-                old = s_whist[warp][dd[e]];
-                s_whist[warp][dd[e]] = (uint16_t)(old + __popc(peers[e]));
-            }
-            old = __shfl_sync(FULLMASK, old, leader);
-            __syncwarp();
-            const uint32_t r = ok ? old + __popc(peers[e] & lt) : 0xffffu;
+            old[e] = 0u;
+            if (dd[e] != 0xffffffffu && (peers[e] & lt) == 0u) old[e] = atomicAdd(&s_whist[warp][dd[e]], (uint32_t)__popc(peers[e]));
+        }
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const uint32_t o = __shfl_sync(FULLMASK, old[e], __ffs(peers[e]) - 1);
+            const uint32_t r = dd[e] != 0xffffffffu ? o + __popc(peers[e] & lt) : 0xffffu;
             if (e & 1) rank2[(g + e) >> 1] |= r << 16; else rank2[(g + e) >> 1] = r;
         }
     }
@@ -348,7 +354,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
 #pragma unroll
         for (int w = 0; w < RS_WARPS; w++) {
             const uint32_t c = s_whist[w][d];
-            s_whist[w][d] = (uint16_t)run;
+            s_whist[w][d] = run;
             run += c;
         }
         if (TR::STAGE) s_lstart[d] = run;
@@ -366,7 +372,6 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
                 const uint32_t val = vals_in ? s_ival[t] : base + (unsigned)t;
                 if (keys_out) keys_out[pos] = key;
                 vals_out[pos] = val;
-                tr.on_output(pos, val);
             }
         }
         return;
@@ -387,13 +392,16 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
     __syncthreads();
     for (int d = tid; d < bins; d += RS_THREADS) s_base[d] -= s_lstart[d];      // position = s_base[digit] + slot
     __syncthreads();
-    for (int i = tid; i < mv; i += RS_THREADS) {
-        const KeyT key = s_okey[i];
-        const uint32_t val = s_oval[i];
+    for (int i0 = warp * 32; i0 < mv; i0 += RS_THREADS) {    // warp-uniform trip count: on_output is a warp operation
+        const int i = i0 + lane;
+        const bool live = i < mv;
+        const KeyT key = s_okey[live ? i : 0];
+        const uint32_t val = s_oval[live ? i : 0];
         const uint32_t pos = s_base[tr.digit(key)] + (uint32_t)i;
+        tr.on_output(live, pos, val);
+        if (!live) continue;
         vals_out[pos] = val;
         if (keys_out) keys_out[pos] = key;
-        tr.on_output(pos, val);
         if (ranges) {
             // all pairs of a tile are contiguous in this pass's output: start = min position, end = max position + 1.
             // The start is kept as max(~position) so that zero-filled ranges are the identity (launch_tile_order
