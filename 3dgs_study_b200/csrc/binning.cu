@@ -69,7 +69,6 @@ __device__ __forceinline__ unsigned load_count(Count c) {
 struct DepthTraits {
     using KeyT = uint32_t;
     static constexpr int MAXBINS = DEPTH_MAXBINS;
-    static constexpr bool STAGE = true;
     const unsigned* ctr;      // control block: key range of the visible Gaussians
     int pass;
     const uint2* rect;        // last pass only: tiles touched by the Gaussian landing at depth position `pos` are added to
@@ -106,7 +105,6 @@ template <typename K>
 struct TileTraits {
     using KeyT = K;
     static constexpr int MAXBINS = TILE_MAXBINS;
-    static constexpr bool STAGE = true;
     int gx, nbins, by_row;
     uint32_t magic;            // floor(2^32 / gx) + 1: tile / gx = umulhi(tile, magic) exactly for tile < 2^20, 2 <= gx <= 512
     __device__ __forceinline__ void init() {}
@@ -262,12 +260,12 @@ struct ScatterSmem {
     static constexpr int MB = TR::MAXBINS;
     static constexpr size_t off_base = 0;
     static constexpr size_t off_lstart = off_base + sizeof(uint32_t) * MB;
-    static constexpr size_t off_whist = off_lstart + (TR::STAGE ? sizeof(uint32_t) * MB : 0);
+    static constexpr size_t off_whist = off_lstart + sizeof(uint32_t) * MB;
     static constexpr size_t off_ikey = off_whist + sizeof(uint32_t) * RS_WARPS * MB;
     static constexpr size_t off_ival = off_ikey + sizeof(KeyT) * RS_TILE;
     static constexpr size_t off_okey = off_ival + sizeof(uint32_t) * RS_TILE;
-    static constexpr size_t off_oval = off_okey + (TR::STAGE ? sizeof(KeyT) * RS_TILE : 0);
-    static constexpr size_t off_warp = off_oval + (TR::STAGE ? sizeof(uint32_t) * RS_TILE : 0);
+    static constexpr size_t off_oval = off_okey + sizeof(KeyT) * RS_TILE;
+    static constexpr size_t off_warp = off_oval + sizeof(uint32_t) * RS_TILE;
     static constexpr size_t bytes = off_warp + sizeof(uint32_t) * RS_WARPS;
 };
 
@@ -317,23 +315,53 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
     cp_async_commit_wait_all();
     __syncthreads();
 
-    // Stable ranks: a warp owns 512 consecutive elements, 16 rounds of 32 in order.  Per round, the lowest lane of
-    // every digit group adds the group's size to the warp's private counter of that digit and hands the old value to
-    // its group.  Nothing in a round waits for the round before: the match instructions of 8 rounds are issued
-    // together, then their 8 shared-memory atomics (a warp's atomics on one address execute in issue order, which is
-    // what makes the ranks stable), and only then the old values are read back and broadcast.
-    uint32_t rank2[RS_ITEMS / 2];                            // two 16-bit ranks per register (0xffff: not an element)
-    const unsigned lt = (1u << lane) - 1u;
+    // A warp owns 512 consecutive elements: 16 rounds of 32, in order.
+    // 1. per-warp digit counts (shared-memory atomics, any order)
     const int t0 = warp * (RS_ITEMS * 32) + lane;
+#pragma unroll
+    for (int e = 0; e < RS_ITEMS; e++) {
+        const int t = t0 + e * 32;
+        if (t < m) {
+            const KeyT key = s_ikey[t];
+            if (tr.valid(key)) atomicAdd(&s_whist[warp][tr.digit(key)], 1u);
+        }
+    }
+    __syncthreads();
+    // 2. counts -> cursors: slot of the warp's first element of each digit in the block's sorted order
+    for (int d = tid; d < bins; d += RS_THREADS) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) {
+            const uint32_t c = s_whist[w][d];
+            s_whist[w][d] = run;
+            run += c;
+        }
+        s_lstart[d] = run;
+    }
+    __syncthreads();
+    const int mv = (int)block_excl_scan(s_lstart, bins, s_warp);          // elements of the block that take part
+    for (int d = tid; d < bins; d += RS_THREADS) {
+        const uint32_t ls = s_lstart[d];
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) s_whist[w][d] += ls;
+    }
+    __syncthreads();
+    // 3. stable slots.  Per round, the lowest lane of every digit group advances the warp's cursor of that digit by the
+    // group's size and hands the old value to its group.  Nothing in a round waits for the round before: the match
+    // instructions of 8 rounds are issued together, then their 8 shared-memory atomics (a warp's atomics on one
+    // address execute in issue order, which is what makes the order stable), then the old values are broadcast and
+    // the elements go to their slots of the staging arrays.
+    const unsigned lt = (1u << lane) - 1u;
 #pragma unroll
     for (int g = 0; g < RS_ITEMS; g += 8) {
         uint32_t dd[8], old[8];
         unsigned peers[8];
+        KeyT key[8];
 #pragma unroll
         for (int e = 0; e < 8; e++) {
             const int t = t0 + (g + e) * 32;
-            const KeyT key = s_ikey[t < m ? t : 0];
-            dd[e] = (t < m && tr.valid(key)) ? tr.digit(key) : 0xffffffffu;
+            key[e] = s_ikey[t < m ? t : 0];
+            dd[e] = (t < m && tr.valid(key[e])) ? tr.digit(key[e]) : 0xffffffffu;
             peers[e] = __match_any_sync(FULLMASK, dd[e]);
         }
 #pragma unroll
@@ -344,49 +372,12 @@ __global__ void __launch_bounds__(RS_THREADS, 3) radix_scatter_kernel(TR tr, con
 #pragma unroll
         for (int e = 0; e < 8; e++) {
             const uint32_t o = __shfl_sync(FULLMASK, old[e], __ffs(peers[e]) - 1);
-            const uint32_t r = dd[e] != 0xffffffffu ? o + __popc(peers[e] & lt) : 0xffffu;
-            if (e & 1) rank2[(g + e) >> 1] |= r << 16; else rank2[(g + e) >> 1] = r;
-        }
-    }
-    __syncthreads();
-    for (int d = tid; d < bins; d += RS_THREADS) {
-        uint32_t run = 0;
-#pragma unroll
-        for (int w = 0; w < RS_WARPS; w++) {
-            const uint32_t c = s_whist[w][d];
-            s_whist[w][d] = run;
-            run += c;
-        }
-        if (TR::STAGE) s_lstart[d] = run;
-    }
-    __syncthreads();
-    if (!TR::STAGE) {
-#pragma unroll
-        for (int e = 0; e < RS_ITEMS; e++) {
-            const uint32_t r = (e & 1) ? rank2[e >> 1] >> 16 : rank2[e >> 1] & 0xffffu;
-            if (r != 0xffffu) {
-                const int t = t0 + e * 32;
-                const KeyT key = s_ikey[t];
-                const uint32_t dd = tr.digit(key);
-                const uint32_t pos = s_base[dd] + s_whist[warp][dd] + r;
-                const uint32_t val = vals_in ? s_ival[t] : base + (unsigned)t;
-                if (keys_out) keys_out[pos] = key;
-                vals_out[pos] = val;
+            if (dd[e] != 0xffffffffu) {
+                const int t = t0 + (g + e) * 32;
+                const uint32_t li = o + __popc(peers[e] & lt);
+                s_okey[li] = key[e];
+                s_oval[li] = vals_in ? s_ival[t] : base + (unsigned)t;
             }
-        }
-        return;
-    }
-    const int mv = (int)block_excl_scan(s_lstart, bins, s_warp);          // elements of the block that take part
-#pragma unroll
-    for (int e = 0; e < RS_ITEMS; e++) {
-        const uint32_t r = (e & 1) ? rank2[e >> 1] >> 16 : rank2[e >> 1] & 0xffffu;
-        if (r != 0xffffu) {
-            const int t = t0 + e * 32;
-            const KeyT key = s_ikey[t];
-            const uint32_t dd = tr.digit(key);
-            const uint32_t li = s_lstart[dd] + s_whist[warp][dd] + r;
-            s_okey[li] = key;
-            s_oval[li] = vals_in ? s_ival[t] : base + (unsigned)t;
         }
     }
     __syncthreads();
