@@ -273,7 +273,7 @@ int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const f
     if (n_src < 1 || n_src > B200SPLAT_MAX_VIEWS) return fail(B200SPLAT_ERR_INVALID_ARG, "n_src must be in [1, B200SPLAT_MAX_VIEWS]");
     if (store && n_src != 1) return fail(B200SPLAT_ERR_INVALID_ARG, "store mode takes exactly one source");
     if (P == 0) return B200SPLAT_OK;
-    if (!means3D || !rows || !counts || !campos || !dL_dsh || !dL_dgeom) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
+    if (!means3D || !rows || !counts || !dL_dsh || !dL_dgeom) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
     if (!aligned16(dL_dgeom)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dgeom must be 16-byte aligned");
     for (int v = 0; v < n_src; v++)
         if (!rows[v] || !counts[v]) return fail(B200SPLAT_ERR_INVALID_ARG, "null source");

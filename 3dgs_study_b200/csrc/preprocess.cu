@@ -808,11 +808,17 @@ struct PackedSources {
 
 // The row counts live next to the rows, possibly in a peer's memory: one warp fetches them once (n_src remote
 // loads) instead of every warp of the accumulate kernel hammering the same few remote words.
-__global__ void gather_counts_kernel(PackedSources src, unsigned* __restrict__ local_counts) {
-    if ((int)threadIdx.x < src.n) local_counts[threadIdx.x] = *reinterpret_cast<const volatile unsigned*>(src.count[threadIdx.x]);
+// With fetch_cam, the camera centre of every source view comes the same way: words 4..6 of the 64-byte header the
+// row count sits in (the caller put it there), so no collective is needed to tell the ranks each other's cameras.
+__global__ void gather_counts_kernel(PackedSources src, unsigned* __restrict__ local_counts, int fetch_cam) {
+    const int v = threadIdx.x >> 2, k = threadIdx.x & 3;         // 4 threads per source: count, cx, cy, cz
+    if (v >= src.n) return;
+    const volatile unsigned* hdr = reinterpret_cast<const volatile unsigned*>(src.count[v]);
+    if (k == 0) local_counts[v] = hdr[0];
+    else if (fetch_cam) local_counts[32 + 3 * v + (k - 1)] = hdr[3 + k];
 }
 
-__device__ unsigned g_packed_counts[64];  // local copies of the sources' row counts (gather_counts_kernel)
+__device__ unsigned g_packed_counts[256]; // two slots of: 32 row counts + 16 x 3 camera-centre words of the sources (gather_counts_kernel)
 
 constexpr int ACC_WARPS = 4;              // warps per block of accumulate_packed_kernel
 constexpr int ACC_RS4 = 13;               // 16-byte words per staged dL/dsh row (odd: conflict-free)
@@ -1031,8 +1037,9 @@ cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, 
     // nothing is allocated, nothing to free
     unsigned* lc = nullptr;
     if ((e = cudaGetSymbolAddress((void**)&lc, g_packed_counts)) != cudaSuccess) return e;
-    lc += store ? 32 : 0;
-    gather_counts_kernel<<<1, 32, 0, s>>>(src, lc);
+    lc += store ? 128 : 0;
+    gather_counts_kernel<<<1, 64, 0, s>>>(src, lc, campos == nullptr);
+    if (!campos) campos = reinterpret_cast<const float*>(lc + 32);
     const bool vec_ok = ((3 * M) & 3) == 0;     // the store flavour relies on the 16-byte path
     if (store && vec_ok && n_src == 1)
         accumulate_packed_kernel<true><<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom);

@@ -537,9 +537,9 @@ def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh
     dev = means3D.device
     P = means3D.shape[0]
     means3D = _f32c(means3D, "means3D", dev)
-    campos = _f32c(campos, "campos", dev)
+    campos = _f32c(campos, "campos", dev)      # None: the camera centres are in the headers counts[v] points at (words 4..6)
     n = len(rows)
-    if len(counts) != n or campos is None or campos.numel() != 3 * n:
+    if len(counts) != n or (campos is not None and campos.numel() != 3 * n):
         raise RuntimeError("rows, counts and campos must describe the same number of views")
     rp, cp = (ctypes.c_void_p * n)(), (ctypes.c_void_p * n)()
     for v in range(n):

@@ -138,6 +138,7 @@ class ViewParallelStep:
         self.last_radii = None
         self._side = None                    # side streams of the factorized / packed exchange
         self._packed = None                  # symmetric buffers of the packed exchange
+        self._local_rows = None              # packed rows of a single-rank step (same layout, plain device memory)
         # peer_memory (factorized, CUDA, world_size > 1): exchange through NVLink peer / multicast mappings
         # (torch symmetric memory) instead of NCCL -- the SH rebuild kernel then READS every peer's colour gradients
         # itself (all-gather fused into the kernel) and the 11 f32 / Gaussian go through an in-switch (NVLS
@@ -250,20 +251,20 @@ class ViewParallelStep:
             geom.record_stream(side); dsh.record_stream(side)
             geom.zero_(); dsh.zero_()
             cleared = torch.cuda.Event(); cleared.record(side)
+        stride = 16 * P + 16                                           # words per view: 64-byte header + P rows
         if G > 1:
             pk = self._setup_packed(P, nv, dev)
             my = pk["ptrs"][dist.get_rank(self.group)]
-            comm.wait_event(start)
-            with torch.cuda.stream(comm):               # every view's camera centre: tiny, off the critical path
-                campos.record_stream(comm)
-                all_campos = torch.empty(G * nv, 3, dtype=torch.float32, device=dev)
-                dist.all_gather_into_tensor(all_campos, campos, group=self.group)
-                gathered = torch.cuda.Event(); gathered.record(comm)
-            base = [my + 4 * k * pk["stride"] for k in range(nv)]
+            buf = pk["buf"]
         else:
-            local = torch.zeros(nv * (16 * P + 16), dtype=torch.float32, device=dev)
-            base = [local.data_ptr() + 4 * k * (16 * P + 16) for k in range(nv)]
-            all_campos, gathered = campos, None
+            if self._local_rows is None or self._local_rows.numel() != nv * stride:
+                self._local_rows = torch.zeros(nv * stride, dtype=torch.float32, device=dev)
+            buf = self._local_rows
+            my = buf.data_ptr()
+        base = [my + 4 * k * stride for k in range(nv)]
+        # header of every view: word 0 = row count (written by the backward), words 4..6 = its camera centre, which is
+        # how the peers learn it (b200splat_accumulate_packed with campos = NULL): no collective anywhere in the step
+        buf.view(nv, stride)[:, 4:7].copy_(campos)
         color = None
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
             dmeans2D = torch.empty(P, 3, dtype=torch.float32, device=dev)
@@ -273,23 +274,19 @@ class ViewParallelStep:
         main.wait_event(cleared)
         # this rank's own rows go in first, before the barrier (i.e. while the slower peers are still rendering):
         # the first view is WRITTEN into the freshly cleared gradients (plain stores), further local views are added
-        C.accumulate_packed(lv.means3D, [base[0] + 64], [base[0]], campos[0:1], M, self.sh_degree, dsh, geom, store=True)
+        C.accumulate_packed(lv.means3D, [base[0] + 64], [base[0]], None, M, self.sh_degree, dsh, geom, store=True)
         if nv > 1:
-            C.accumulate_packed(lv.means3D, [b + 64 for b in base[1:]], base[1:], campos[1:], M, self.sh_degree, dsh, geom)
+            C.accumulate_packed(lv.means3D, [b + 64 for b in base[1:]], base[1:], None, M, self.sh_degree, dsh, geom)
         if G > 1:
-            main.wait_event(gathered)
-            all_campos.record_stream(main)
-            pk["hd"].barrier(channel=0)                 # every rank's rows are in place
+            pk["hd"].barrier(channel=0)                 # every rank's rows (and headers) are in place
             # the peers' rows, read over NVLink; each rank walks its peers in a different rotation, so that at any
             # moment the ranks read from different peers
             me = dist.get_rank(self.group)
             order = [(me + j) % G for j in range(1, G)]
-            bases = [pk["ptrs"][r] + 4 * k * pk["stride"] for r in order for k in range(nv)]
-            peers_campos = torch.roll(all_campos.view(G, nv, 3), shifts=-me, dims=0)[1:].reshape((G - 1) * nv, 3)
+            bases = [pk["ptrs"][r] + 4 * k * stride for r in order for k in range(nv)]
             for lo in range(0, len(bases), 16):         # B200SPLAT_MAX_VIEWS sources per launch
                 hi = min(lo + 16, len(bases))
-                C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], peers_campos[lo:hi].contiguous(),
-                                    M, self.sh_degree, dsh, geom)
+                C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], None, M, self.sh_degree, dsh, geom)
             pk["hd"].barrier(channel=1)                 # every rank has read them: the next step may overwrite
         # the geometry gradients are strided views of the interleaved [P,12] rows
         self.leaves.rotations.grad = geom[:, 0:4]

@@ -257,7 +257,9 @@ B200SPLAT_API int b200splat_sh_grad_from_views(int32_t P, int32_t M, int32_t sh_
  * a bounded number of atomic sectors per second and the exchange is bound by exactly that.  rows[v] / counts[v] are DEVICE
  * pointers (host arrays of n_src entries) and may address a peer GPU's memory mapped into this process: the
  * kernel then reads the peer's rows over NVLink, i.e. the exchange is this kernel -- there is no collective.
- * campos: device array [n_src,3], the camera centre of each source view.
+ * campos: device array [n_src,3], the camera centre of each source view; or NULL: each counts[v] then points at a 64-byte
+ * header {row count, 0, 0, 0, cx, cy, cz, ...} and the kernel takes the camera centre of view v from words 4..6 of it
+ * (the owner of the rows writes it there, so the ranks need no collective to learn each other's cameras).
  * store != 0 (n_src must be 1): the rows are WRITTEN instead of added -- for the first source into freshly
  * cleared gradients, e.g. a rank's own rows while it waits for its peers; nothing else may write the
  * gradients while that launch runs. */
