@@ -126,15 +126,24 @@ class ViewParallelStep:
         # default = the CUDA library through _C, CPU tests inject a torch stand-in
         self._backend = backend
         if exchange is None:
-            # N > 1 on CUDA: the sparse packed-row exchange over peer memory; with an injected backend (CPU tests):
-            # the factorized exchange over the process group; with an injected rasterizer: plain all-reduce
+            # N > 1 on CUDA: "auto" (packed rows over peer memory unless the views touch too many Gaussians for them to
+            # pay, see _auto_decide); with an injected backend (CPU tests): the factorized exchange over the process
+            # group; with an injected rasterizer: plain all-reduce
             if world_size > 1 and rasterize is None:
-                exchange = "packed" if (backend is None and dev.type == "cuda") else "factorized"
+                exchange = "auto" if (backend is None and dev.type == "cuda") else "factorized"
             else:
                 exchange = "allreduce"
-        if exchange not in ("allreduce", "factorized", "packed"):
-            raise ValueError("exchange must be 'allreduce', 'factorized' or 'packed'")
-        self.exchange = exchange
+        if exchange not in ("allreduce", "factorized", "packed", "auto"):
+            raise ValueError("exchange must be 'allreduce', 'factorized', 'packed' or 'auto'")
+        # auto: every AUTO_EVERY steps one step runs packed (its row counts are the measurement), the next step takes
+        # the largest touched fraction over all ranks (one 4-byte max-all-reduce + host read per AUTO_EVERY steps) and
+        # keeps "packed" below AUTO_THRESHOLD, "factorized" above: packed moves 64 B per touched Gaussian and view and
+        # pays 15 L2 reductions for each, factorized moves 12 B + 44 B per Gaussian whatever the view touched
+        # (measured crossover on 8 x B200: BASELINE.md section 5).
+        self._auto = exchange == "auto"
+        self.AUTO_EVERY, self.AUTO_THRESHOLD = 64, 0.18
+        self._step_no, self._probe_pending = 0, False
+        self.exchange = "packed" if self._auto else exchange
         self.last_radii = None
         self._side = None                    # side streams of the factorized / packed exchange
         self._packed = None                  # symmetric buffers of the packed exchange
@@ -180,6 +189,9 @@ class ViewParallelStep:
     def step(self, cams: Sequence, dL_images: Sequence[torch.Tensor], reduce: bool = True, on_forward=None) -> torch.Tensor:
         """`on_forward(image)` (optional) is called right after each view's forward has been enqueued, before its
         backward: the hook a caller uses to start consuming the image (e.g. a device->host copy on another stream)."""
+        if self._auto and self.world_size > 1 and reduce:
+            self._auto_decide(len(cams))
+        self._step_no += 1
         if self.exchange == "factorized":
             return self._step_factorized(cams, dL_images, reduce, on_forward)
         if self.exchange == "packed":
@@ -207,6 +219,20 @@ class ViewParallelStep:
         if reduce and self.world_size > 1:
             self.all_reduce_grads()
         return color.detach()
+
+    def _auto_decide(self, nv):
+        """exchange="auto": see __init__.  Collective (every rank calls step() the same number of times)."""
+        import torch.distributed as dist
+        if self._probe_pending and self._packed is not None:
+            pk = self._packed
+            P = self.leaves.means3D.shape[0]
+            counts = pk["buf"].view(pk["nv"], -1)[:, 0].contiguous().view(torch.int32).max().to(torch.float32).reshape(1)
+            dist.all_reduce(counts, op=dist.ReduceOp.MAX, group=self.group)
+            self.touched_fraction = float(counts.item()) / max(P, 1)
+            self.exchange = "factorized" if self.touched_fraction > self.AUTO_THRESHOLD else "packed"
+            self._probe_pending = False
+        elif self._step_no % self.AUTO_EVERY == 0:
+            self.exchange, self._probe_pending = "packed", True      # this step measures
 
     # -- packed (sparse, peer-memory) exchange ----------------------------------------------------------------
     # A view touches a few per cent of the Gaussians, and every gradient of an untouched one is exactly zero.  Each
@@ -242,15 +268,21 @@ class ViewParallelStep:
             self._side = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
         comm, side = self._side
         campos = torch.stack([c.camera_center.to(dev).float() for c in cams]).contiguous()
-        start = torch.cuda.Event(); start.record(main)
-        # dense gradients: cleared beside the forward pass (the rows are ADDED into them at the end of the step)
+        # Dense gradients (the rows are ADDED into them at the end of the step): 720 MB at 3 M SH3 to clear.  The clear
+        # runs on a side stream UNDER THE FIRST VIEW'S RENDER BACKWARD -- that kernel is FP32-bound and leaves HBM idle,
+        # whereas next to the HBM-bound preprocess / binning kernels at the start of the step it would cost its full
+        # 0.1 ms (measured, profiles/r02_timeline_n2_rank0.txt of the first version).
         geom = torch.empty(P, 12, dtype=torch.float32, device=dev)     # (d rotation 4, d mean 3, d scale 3, d opacity, 0)
         dsh = torch.empty(P, M, 3, dtype=torch.float32, device=dev)
-        side.wait_event(start)
-        with torch.cuda.stream(side):
-            geom.record_stream(side); dsh.record_stream(side)
-            geom.zero_(); dsh.zero_()
-            cleared = torch.cuda.Event(); cleared.record(side)
+        box = {}
+
+        def clear_dense():
+            fwd_done = torch.cuda.Event(); fwd_done.record(main)
+            side.wait_event(fwd_done)
+            with torch.cuda.stream(side):
+                geom.record_stream(side); dsh.record_stream(side)
+                geom.zero_(); dsh.zero_()
+                box["cleared"] = torch.cuda.Event(); box["cleared"].record(side)
         stride = 16 * P + 16                                           # words per view: 64-byte header + P rows
         if G > 1:
             pk = self._setup_packed(P, nv, dev)
@@ -268,10 +300,16 @@ class ViewParallelStep:
         color = None
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
             dmeans2D = torch.empty(P, 3, dtype=torch.float32, device=dev)
-            color, radii = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, on_forward)
+
+            def after_forward(img, first=(k == 0)):
+                if first:
+                    clear_dense()
+                if on_forward is not None:
+                    on_forward(img)
+            color, radii = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, after_forward)
             self._accumulate_stats(dmeans2D, radii)
             self.last_radii = radii
-        main.wait_event(cleared)
+        main.wait_event(box["cleared"])
         # this rank's own rows go in first, before the barrier (i.e. while the slower peers are still rendering):
         # the first view is WRITTEN into the freshly cleared gradients (plain stores), further local views are added
         C.accumulate_packed(lv.means3D, [base[0] + 64], [base[0]], None, M, self.sh_degree, dsh, geom, store=True)

@@ -48,8 +48,9 @@ def parse_args():
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--preset", default="opaque", choices=["opaque", "translucent"],
                     help="opacity distribution of the synthetic scene (3dgs_study_b200/synth.py PRESETS); the headline is 'opaque'")
-    ap.add_argument("--exchange", default=None, choices=["allreduce", "factorized", "packed"],
-                    help="N>1 gradient exchange (default: packed rows over NVLink peer memory); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
+    ap.add_argument("--exchange", default=None, choices=["allreduce", "factorized", "packed", "auto"],
+                    help="N>1 gradient exchange (default auto: packed rows over NVLink peer memory unless the views touch too many "
+                         "Gaussians, then the factorized NCCL exchange); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
     ap.add_argument("--peer-memory", action="store_true", help="factorized exchange through NVLink peer mappings (fused rebuild kernel + multimem all-reduce) instead of NCCL")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train-iter", action="store_true", help="skip the full-training-iteration measurement (N=1 only)")

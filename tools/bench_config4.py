@@ -30,7 +30,7 @@ cams = [synth.make_camera(W, H, yaw=2.0 * np.pi * k / NV).to(dev) for k in range
 dL = synth.make_grad_image(W, H).to(dev)
 mine = vp.shard_views(NV, rank, world)
 st = vp.ViewParallelStep(vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations), D, torch.zeros(3, device=dev),
-                         world_size=world, exchange=a.exchange or ("packed" if world > 1 else "packed"))
+                         world_size=world, exchange=a.exchange or ("packed" if world == 1 else None))
 def step():
     st.step([cams[k] for k in mine], [dL] * len(mine))
 for _ in range(a.warmup):
