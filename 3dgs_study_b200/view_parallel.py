@@ -141,7 +141,7 @@ class ViewParallelStep:
         # pays 15 L2 reductions for each, factorized moves 12 B + 44 B per Gaussian whatever the view touched
         # (measured crossover on 8 x B200: BASELINE.md section 5).
         self._auto = exchange == "auto"
-        self.AUTO_EVERY, self.AUTO_THRESHOLD = 64, 0.18
+        self.AUTO_EVERY, self.AUTO_THRESHOLD = 64, 0.25
         self._step_no, self._probe_pending = 0, False
         self.exchange = "packed" if self._auto else exchange
         self.last_radii = None

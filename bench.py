@@ -198,14 +198,21 @@ def run_ours(a):
     if world > 1:
         dist.barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    step_evs = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps + 1)] if os.environ.get("BENCH_STEP_TIMES") else None
     with ClockSampler(local) as cs:
         torch.cuda.synchronize()
         ev0.record()
         for i in range(a.steps):
+            if step_evs:
+                step_evs[i].record()
             step_resident(a.warmup + i)
         ev1.record()
+        if step_evs:
+            step_evs[a.steps].record()
         torch.cuda.synchronize()
     ms_total = ev0.elapsed_time(ev1)
+    if step_evs and rank == 0:      # diagnostic: device time of every timed step
+        print("step ms: " + " ".join(f"{step_evs[i].elapsed_time(step_evs[i + 1]):.2f}" for i in range(a.steps)), file=sys.stderr)
     if world > 1:
         t = torch.tensor([ms_total], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
