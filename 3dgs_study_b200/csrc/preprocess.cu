@@ -956,6 +956,20 @@ __global__ void export_geom_kernel(int P, const int32_t* __restrict__ radii, Geo
     if (o.rgb) { o.rgb[3 * i] = c.y; o.rgb[3 * i + 1] = c.z; o.rgb[3 * i + 2] = c.w; }
 }
 
+// Function attributes are set once per kernel and device (not on every launch: attribute calls have no place inside a
+// stream capture, and a captured step replays these launches thousands of times).
+template <typename K>
+cudaError_t configure_once(K kernel, bool (&done)[64], bool max_carveout) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (done[dev & 63]) return cudaSuccess;
+    if ((e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024)) != cudaSuccess) return e;
+    if (max_carveout) cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    done[dev & 63] = true;
+    return cudaSuccess;
+}
+
 int coop_shift(int nq) {   // smallest qs with 2^qs >= nq (nq <= 12)
     int qs = 0;
     while ((1 << qs) < nq) qs++;
@@ -985,11 +999,8 @@ cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gauss
     const int M3 = 3 * g.M;
     const int coop = (g.shs && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
     const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
-    cudaFuncSetAttribute(preprocess_fwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    static bool configured[64] = {false};
+    if (cudaError_t e = configure_once(preprocess_fwd_kernel, configured, true); e != cudaSuccess) return e;
     preprocess_fwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(p, gv.depths, gv.rec, gv.rect,
                                                                                          radii, counters, coop, coop_shift(M3 >> 2));
     return cudaGetLastError();
@@ -1013,11 +1024,8 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
     const int M3 = 3 * g.M;
     const int coop = (g.shs && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
     const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
-    cudaFuncSetAttribute(preprocess_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    static bool configured[64] = {false};
+    if (cudaError_t e = configure_once(preprocess_bwd_kernel, configured, true); e != cudaSuccess) return e;
     preprocess_bwd_kernel<<<(g.P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(bp, coop, coop_shift(M3 >> 2), out.dL_dsh ? 1 : 0);
     return cudaGetLastError();
 }
@@ -1035,9 +1043,9 @@ cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     // two slots of 32 words (store / add launches may be queued back to back) in the module's own device memory:
     // nothing is allocated, nothing to free
-    unsigned* lc = nullptr;
-    if ((e = cudaGetSymbolAddress((void**)&lc, g_packed_counts)) != cudaSuccess) return e;
-    lc += store ? 128 : 0;
+    static unsigned* symbol[64] = {nullptr};                 // looked up once per device (not inside a stream capture)
+    if (!symbol[dev & 63] && (e = cudaGetSymbolAddress((void**)&symbol[dev & 63], g_packed_counts)) != cudaSuccess) return e;
+    unsigned* lc = symbol[dev & 63] + (store ? 128 : 0);
     gather_counts_kernel<<<1, 64, 0, s>>>(src, lc, campos == nullptr);
     if (!campos) campos = reinterpret_cast<const float*>(lc + 32);
     const bool vec_ok = ((3 * M) & 3) == 0;     // the store flavour relies on the 16-byte path
@@ -1068,10 +1076,8 @@ cudaError_t launch_sh_grad_from_views(int P, int M, int D, const float* means3D,
     const int coop = (M > 0 && (M3 & 3) == 0 && M <= 16) ? 1 : 0;
     const size_t rows_bytes = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;
     const size_t smem = rows_bytes + (size_t)(PRE_THREADS / 32) * n_views * 96 * sizeof(float);
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(sh_grad_from_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
+    static bool configured[64] = {false};
+    if (cudaError_t e = configure_once(sh_grad_from_views_kernel, configured, false); e != cudaSuccess) return e;
     sh_grad_from_views_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, smem, s>>>(P, M, D, means3D, vg, campos, dL_dsh,
                                                                                           coop, coop_shift(M3 >> 2),
                                                                                           (int)(rows_bytes / 16), vec_ok);

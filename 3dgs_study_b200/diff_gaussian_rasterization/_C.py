@@ -229,6 +229,18 @@ def reset_capacity_policy():
     _cap_state.clear()
 
 
+def capacity_status(device, P, image_height, image_width):
+    """-> (R, capacity, overflow) as last landed in pinned memory for this configuration (no synchronisation), or None:
+    what the capacity policy itself looks at; for callers that replay captured forwards and must check for themselves."""
+    dev = torch.device(device)
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), int(P), int(image_width), int(image_height))
+    st = _cap_state.get(key)
+    if st is None or not st["pending"]:
+        return None
+    lo, hi, cap, over = (int(x) & 0xffffffff for x in st["pinned"].tolist())
+    return lo | (hi << 32), cap, bool(over)
+
+
 def forward_status(imageBuffer, image_height, image_width):
     """-> (R, capacity, overflow) of the view whose image buffer is given (b200splat_forward_status; synchronises)."""
     dev = imageBuffer.device

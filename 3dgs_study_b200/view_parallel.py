@@ -277,10 +277,10 @@ class ViewParallelStep:
         box = {}
 
         def clear_dense():
+            # (no record_stream: the main stream waits for `cleared` before it touches, and long before it frees, them)
             fwd_done = torch.cuda.Event(); fwd_done.record(main)
             side.wait_event(fwd_done)
             with torch.cuda.stream(side):
-                geom.record_stream(side); dsh.record_stream(side)
                 geom.zero_(); dsh.zero_()
                 box["cleared"] = torch.cuda.Event(); box["cleared"].record(side)
         stride = 16 * P + 16                                           # words per view: 64-byte header + P rows
@@ -579,3 +579,74 @@ class ViewParallelStep:
             for k, v in st.as_dict().items():
                 acc[k[:-3]] = acc.get(k[:-3], 0.0) + v / iters
         return acc, stats
+
+
+class GraphedStep:
+    """One whole step of a ViewParallelStep -- forward, backward, exchange, statistics: some 35 kernel launches and a
+    dozen tensor operations per view -- captured ONCE in a CUDA graph and replayed with one launch per step.
+
+    The step is launch-latency sensitive: at 2 ms per view the Python thread has to queue a kernel every 50 us, and on
+    a host shared by 8 ranks (and their NCCL / NVML threads) it does not always manage; the replayed graph does not
+    care.  What makes the capture possible: the pair count stays on the device (b200splat.h "pair capacity"), the
+    packed exchange has no collective (camera centres travel in the row headers), and the symmetric-memory barrier is
+    a stateless kernel.
+
+    Inputs live in static device buffers (`load()` copies a step's cameras and upstream gradients into them); the
+    intrinsics, image size and number of views are those of the cameras given at capture.  Outputs: `color`,
+    `stepper.grads()`, the stepper's densification statistics -- valid until the next replay.  `step()` checks, one step
+    late and without synchronising, that no replayed forward overflowed its pair capacity; if one did, it re-captures
+    with the capacity the policy has meanwhile raised and raises for the spoiled step."""
+
+    def __init__(self, stepper: ViewParallelStep, cams: Sequence, dL_images: Sequence[torch.Tensor], warmup: int = 3):
+        if stepper.exchange not in ("packed",):
+            raise ValueError("GraphedStep captures the packed-row step (exchange='packed' or 'auto' settled on packed)")
+        self.st = stepper
+        dev = stepper.leaves.means3D.device
+        self.dev = dev
+        self.cam_buf = [torch.empty(35, dtype=torch.float32, device=dev) for _ in cams]
+        self.dL_buf = [torch.empty_like(d, device=dev) for d in dL_images]
+        self.cams = [c._replace(world_view_transform=b[:16].view(4, 4), full_proj_transform=b[16:32].view(4, 4), camera_center=b[32:35])
+                     for c, b in zip(cams, self.cam_buf)]
+        self._shape = (cams[0].image_height, cams[0].image_width)
+        self.load(cams, dL_images)
+        self._capture(warmup)
+
+    def _capture(self, warmup):
+        st, dev = self.st, self.dev
+        auto, st._auto = st._auto, False                  # the mode is fixed for the life of the graph
+        cur = torch.cuda.current_stream(dev)
+        s = torch.cuda.Stream(device=dev)
+        s.wait_stream(cur)
+        with torch.cuda.stream(s):                        # eager warm-up: library streams, symmetric buffers, capacity history
+            for _ in range(max(2, warmup)):
+                st.step(self.cams, self.dL_buf)
+        cur.wait_stream(s)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+            self.color = st.step(self.cams, self.dL_buf)
+        st._auto = auto
+
+    def load(self, cams, dL_images=None):
+        """Copy a step's cameras (and, if given, upstream gradients) into the static inputs; stream-ordered."""
+        for b, c in zip(self.cam_buf, cams):
+            b[:16].copy_(c.world_view_transform.reshape(-1), non_blocking=True)
+            b[16:32].copy_(c.full_proj_transform.reshape(-1), non_blocking=True)
+            b[32:35].copy_(c.camera_center.reshape(-1), non_blocking=True)
+        if dL_images is not None:
+            for b, d in zip(self.dL_buf, dL_images):
+                if b.data_ptr() != d.data_ptr():
+                    b.copy_(d, non_blocking=True)
+
+    def step(self, cams=None, dL_images=None) -> torch.Tensor:
+        import diff_gaussian_rasterization as dgr
+        status = dgr._C.capacity_status(self.dev, self.st.leaves.means3D.shape[0], *self._shape)
+        if status is not None and status[2]:
+            dgr._C.reset_capacity_policy()
+            self._capture(2)                              # the exact first warm-up view sizes the new capacity
+            raise RuntimeError(f"b200splat: a replayed forward produced {status[0]} (tile, Gaussian) pairs, more than the {status[1]} the "
+                               "captured step was sized for; the step has been re-captured, re-run the spoiled step")
+        if cams is not None:
+            self.load(cams, dL_images)
+        self.graph.replay()
+        return self.color

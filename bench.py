@@ -52,6 +52,7 @@ def parse_args():
                     help="N>1 gradient exchange (default auto: packed rows over NVLink peer memory unless the views touch too many "
                          "Gaussians, then the factorized NCCL exchange); allreduce = plain NCCL all-reduce of 59 f32/Gaussian")
     ap.add_argument("--peer-memory", action="store_true", help="factorized exchange through NVLink peer mappings (fused rebuild kernel + multimem all-reduce) instead of NCCL")
+    ap.add_argument("--no-graph", action="store_true", help="queue every kernel of every step from Python instead of replaying the captured step (CUDA graph)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train-iter", action="store_true", help="skip the full-training-iteration measurement (N=1 only)")
     ap.add_argument("--stages", action="store_true", help="print the per-stage table to stderr")
@@ -183,14 +184,31 @@ def run_ours(a):
     dL_cpu = synth.make_grad_image(W, H).pin_memory()
     dL = dL_cpu.to(dev)
     params = vp.GaussianParams(scene.means3D, scene.shs, scene.opacities, scene.scales, scene.rotations)
-    stepper = vp.ViewParallelStep(params, D, bg, world_size=world, exchange=a.exchange, peer_memory="try" if a.peer_memory else False)
+    exchange = a.exchange
+    if exchange is None and world == 1 and not a.no_graph:
+        exchange = "packed"          # the row-producing backward + local accumulate: the same step the ranks run at N > 1
+    stepper = vp.ViewParallelStep(params, D, bg, world_size=world, exchange=exchange, peer_memory="try" if a.peer_memory else False)
 
     def view_of(step):   # rank r renders view (step * world + r) of the orbit
         return (step * world + rank) % n_views
 
+    # The step is captured once in a CUDA graph and replayed (view_parallel.GraphedStep): one launch per step instead
+    # of ~35 kernels + a dozen tensor ops queued from Python.  Only the packed-row step is capturable (no collective, no
+    # host wait); "auto" first settles on a mode with two eager steps.
+    gstep = None
+    if not a.no_graph:
+        for i in range(2):
+            stepper.step([cams[view_of(i)]], [dL])
+        torch.cuda.synchronize()
+        if stepper.exchange == "packed":
+            gstep = vp.GraphedStep(stepper, [cams[view_of(0)]], [dL])
+
     # ---------------- value: inputs resident in HBM -----------------------------------------------
     def step_resident(i):
-        stepper.step([cams[view_of(i)]], [dL])
+        if gstep is not None:
+            gstep.step([cams[view_of(i)]])
+        else:
+            stepper.step([cams[view_of(i)]], [dL])
 
     for i in range(a.warmup):
         step_resident(i)
@@ -268,11 +286,16 @@ def run_ours(a):
                 fwd_done.record(main_stream)
                 with torch.cuda.stream(copy_stream):
                     copy_stream.wait_event(fwd_done)
-                    img.record_stream(copy_stream)
+                    if gstep is None:
+                        img.record_stream(copy_stream)
                     img_hosts[i % 2].copy_(img, non_blocking=True)
                     res_copy[i % 2].record(copy_stream)
 
-            stepper.step([cam], [sl["g"]], on_forward=on_forward)
+            if gstep is not None:     # the step's inputs move from the arrival slot into the graph's static inputs, then one launch
+                gstep.step([cam], [sl["g"]])
+                on_forward(gstep.color)
+            else:
+                stepper.step([cam], [sl["g"]], on_forward=on_forward)
             chk_hosts[i % 2].copy_(stepper.grad_checksum().reshape(1), non_blocking=True)
             img_done.record(main_stream)
             res_main[i % 2].record(main_stream)
@@ -365,6 +388,8 @@ def run_ours(a):
                 "note": "Gaussians are model state resident in HBM (as in the reference); camera + upstream image gradient from pinned host memory and a gradient checksum (the scalar a training loop reads, like loss.item()) back to the host, every step, inside the timed region; the host reads step i's result after queueing step i+1"},
         "e2e_with_image_readback": e2e_img,
         "gpu_launches": int(launches * a.steps) if launches else None,
+        "step_submission": ("one CUDA-graph replay per step (the whole step captured once: view_parallel.GraphedStep)" if gstep is not None
+                            else "every kernel queued from Python"),
         "clocks": clocks, "stages_ms": {k: round(v, 4) for k, v in stages.items()},
         "roofline": roof,
     }

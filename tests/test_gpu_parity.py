@@ -247,3 +247,35 @@ def test_factorized_exchange_pieces_match_direct_path():
                 assert err <= 5e-4, f"{mode} P={P} D={Dg} {name}: {err}"   # float-atomic order differs run to run
             assert torch.allclose(a.xyz_gradient_accum, b.xyz_gradient_accum, rtol=1e-5, atol=1e-12)
             assert torch.equal(a.denom, b.denom) and torch.equal(a.max_radii2D, b.max_radii2D)
+
+
+def test_graphed_step_matches_eager_step():
+    """view_parallel.GraphedStep: the whole packed-row step captured in a CUDA graph and replayed gives what the eagerly
+    queued step gives, view after view, and the densification statistics keep accumulating across replays."""
+    import importlib
+    vp = importlib.import_module("3dgs_study_b200.view_parallel")
+    synth_ = importlib.import_module("3dgs_study_b200.synth")
+    import diff_gaussian_rasterization as dgr
+    dgr._C.reset_capacity_policy()
+    dev = torch.device("cuda:0")
+    P, Dg, W, H = 6000, 3, 240, 136
+    sc = synth_.make_scene(P, Dg, seed=3, s_med=0.04).to(dev)
+    cams = [synth_.make_camera(W, H, yaw=0.3 * k).to(dev) for k in range(4)]
+    dLs = [synth_.make_grad_image(W, H, seed=50 + k).to(dev) for k in range(4)]
+    params = vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations)
+    bg = torch.tensor([0.2, 0.1, 0.3], device=dev)
+    eager = vp.ViewParallelStep(params, Dg, bg, exchange="packed")
+    graphed = vp.ViewParallelStep(params, Dg, bg, exchange="packed")
+    g = vp.GraphedStep(graphed, [cams[0]], [dLs[0]])
+    graphed.reset_densification_stats()                    # the capture's warm-up steps counted too
+    for k in (1, 2, 3, 0, 2):
+        ce = eager.step([cams[k]], [dLs[k]])
+        cg = g.step([cams[k]], [dLs[k]])
+        torch.cuda.synchronize()
+        assert torch.equal(ce, cg)
+        for name, x, y in zip(vp.GaussianParams._fields, eager.grads(), graphed.grads()):
+            err = float((x - y).abs().max()) / max(float(x.abs().max()), 1e-20)
+            assert err <= 5e-4, f"view {k} {name}: {err}"
+    assert torch.allclose(eager.xyz_gradient_accum, graphed.xyz_gradient_accum, rtol=1e-5, atol=1e-12)
+    assert torch.equal(eager.denom, graphed.denom) and float(eager.denom.max()) >= 4
+    dgr._C.reset_capacity_policy()
