@@ -286,15 +286,13 @@ def run_ours(a):
                 fwd_done.record(main_stream)
                 with torch.cuda.stream(copy_stream):
                     copy_stream.wait_event(fwd_done)
-                    if gstep is None:
-                        img.record_stream(copy_stream)
+                    img.record_stream(copy_stream)
                     img_hosts[i % 2].copy_(img, non_blocking=True)
                     res_copy[i % 2].record(copy_stream)
 
-            if gstep is not None:     # the step's inputs move from the arrival slot into the graph's static inputs, then one launch
+            if gstep is not None and not readback_image:   # inputs move from the arrival slot into the graph's static inputs, then one launch
                 gstep.step([cam], [sl["g"]])
-                on_forward(gstep.color)
-            else:
+            else:                     # (the image-readback flavour starts its copy between forward and backward: queued from Python)
                 stepper.step([cam], [sl["g"]], on_forward=on_forward)
             chk_hosts[i % 2].copy_(stepper.grad_checksum().reshape(1), non_blocking=True)
             img_done.record(main_stream)
