@@ -207,6 +207,16 @@ static cudaError_t side_stream(SideStream** out) {
     return cudaSuccess;
 }
 
+int b200splat_zero_fill(int32_t n, void* const* ptrs, const size_t* bytes, void* stream_) {
+    if (n < 0 || n > 8 || (n > 0 && (!ptrs || !bytes))) return fail(B200SPLAT_ERR_INVALID_ARG, "zero_fill takes 0..8 ranges");
+    ZeroRanges zr;
+    zr.n = 0;
+    for (int i = 0; i < n; i++)
+        if (ptrs[i] && bytes[i]) { zr.ptr[zr.n] = ptrs[i]; zr.bytes[zr.n] = bytes[i]; zr.n++; }
+    CU(launch_zero_fill(zr, (cudaStream_t)stream_), "zero_fill");
+    return B200SPLAT_OK;
+}
+
 // Releases what the calling host thread holds inside the library: its helper streams and events.
 void b200splat_shutdown(void) {
     int cur = 0;
@@ -333,14 +343,12 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
     {
         const size_t n = (size_t)P * sizeof(float);
         const b200splat_grads& o = *grads;
-        if (o.dL_dmeans2D) CU(cudaMemsetAsync(o.dL_dmeans2D, 0, 3 * n, ss->stream), "zero dL_dmeans2D");
-        if (o.dL_dcolors) CU(cudaMemsetAsync(o.dL_dcolors, 0, 3 * n, ss->stream), "zero dL_dcolors");
-        if (o.dL_dopacity) CU(cudaMemsetAsync(o.dL_dopacity, 0, n, ss->stream), "zero dL_dopacity");
-        if (o.dL_dmeans3D) CU(cudaMemsetAsync(o.dL_dmeans3D, 0, 3 * n, ss->stream), "zero dL_dmeans3D");
-        if (o.dL_dcov3D) CU(cudaMemsetAsync(o.dL_dcov3D, 0, 6 * n, ss->stream), "zero dL_dcov3D");
-        if (o.dL_dsh) CU(cudaMemsetAsync(o.dL_dsh, 0, 3 * (size_t)g->M * n, ss->stream), "zero dL_dsh");
-        if (o.dL_dscales) CU(cudaMemsetAsync(o.dL_dscales, 0, 3 * n, ss->stream), "zero dL_dscales");
-        if (o.dL_drotations) CU(cudaMemsetAsync(o.dL_drotations, 0, 4 * n, ss->stream), "zero dL_drotations");
+        ZeroRanges zr;
+        zr.n = 0;
+        auto add = [&](void* p, size_t bytes) { if (p) { zr.ptr[zr.n] = p; zr.bytes[zr.n] = bytes; zr.n++; } };
+        add(o.dL_dmeans2D, 3 * n); add(o.dL_dcolors, 3 * n); add(o.dL_dopacity, n); add(o.dL_dmeans3D, 3 * n);
+        add(o.dL_dcov3D, 6 * n); add(o.dL_dsh, 3 * (size_t)g->M * n); add(o.dL_dscales, 3 * n); add(o.dL_drotations, 4 * n);
+        CU(launch_zero_fill(zr, ss->stream), "zero the gradient outputs");
     }
     CU(cudaEventRecord(ss->join, ss->stream), "join");
 

@@ -1091,6 +1091,37 @@ cudaError_t launch_densify_stats(int P, const float* dmeans2D, const int32_t* ra
     return cudaGetLastError();
 }
 
+namespace {
+__global__ void __launch_bounds__(256) zero_fill_kernel(ZeroRanges zr) {
+    const size_t tid = (size_t)blockIdx.x * 256 + threadIdx.x, nthr = (size_t)gridDim.x * 256;
+    for (int r = 0; r < zr.n; r++) {
+        char* base = static_cast<char*>(zr.ptr[r]);
+        const size_t bytes = zr.bytes[r];
+        // head up to 16-byte alignment, body in 16-byte stores (four in flight per thread), tail
+        const size_t head = min(bytes, (size_t)((16 - (reinterpret_cast<uintptr_t>(base) & 15)) & 15));
+        for (size_t i = tid; i < head; i += nthr) base[i] = 0;
+        uint4* body = reinterpret_cast<uint4*>(base + head);
+        const size_t n16 = (bytes - head) >> 4;
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        size_t i = tid;
+        for (; i + 3 * nthr < n16; i += 4 * nthr) { body[i] = z; body[i + nthr] = z; body[i + 2 * nthr] = z; body[i + 3 * nthr] = z; }
+        for (; i < n16; i += nthr) body[i] = z;
+        for (size_t j = head + (n16 << 4) + tid; j < bytes; j += nthr) base[j] = 0;
+    }
+}
+}  // namespace
+
+cudaError_t launch_zero_fill(const ZeroRanges& zr, cudaStream_t s) {
+    if (zr.n <= 0) return cudaSuccess;
+    static int sms[64] = {0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (!sms[dev & 63]) cudaDeviceGetAttribute(&sms[dev & 63], cudaDevAttrMultiProcessorCount, dev);
+    zero_fill_kernel<<<2 * (sms[dev & 63] > 0 ? sms[dev & 63] : 148), 256, 0, s>>>(zr);   // two blocks per SM
+    return cudaGetLastError();
+}
+
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
     if (P == 0) return cudaSuccess;
     mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);

@@ -132,6 +132,11 @@ cudaError_t launch_sh_grad_from_views(int P, int M, int D, const float* means3D,
 cudaError_t launch_densify_stats(int P, const float* dmeans2D, const int32_t* radii, float* accum, float* denom,
                                  float* max_radii, cudaStream_t s);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
+// Background clear: zero up to 8 device ranges with ONE block per SM, so that the clear runs BESIDE a compute-bound
+// kernel (the render backward) instead of taking every thread slot of the GPU for its 0.1 ms the way a full-grid
+// memset does (measured in profiles/r02_timeline_n8_rank0_graph_v1.txt: the two ran back to back).
+struct ZeroRanges { int n; void* ptr[8]; size_t bytes[8]; };
+cudaError_t launch_zero_fill(const ZeroRanges& zr, cudaStream_t s);
 cudaError_t launch_export_geom(int P, const int32_t* radii, GeomView gv, const b200splat_state_out& o, cudaStream_t s);
 cudaError_t launch_export_binning(int P, int W, int H, GeomView gv, BinView bv, ImgView iv, const b200splat_state_out& o, cudaStream_t s);
 

@@ -136,6 +136,8 @@ def lib():
         L.b200splat_image_status_offset.restype = ctypes.c_size_t
         L.b200splat_image_status_offset.argtypes = [ctypes.c_int32, ctypes.c_int32]
         L.b200splat_shutdown.restype = None
+        L.b200splat_zero_fill.restype = ctypes.c_int
+        L.b200splat_zero_fill.argtypes = [ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.b200splat_export_state.restype = ctypes.c_int
         L.b200splat_export_state.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -564,6 +566,24 @@ def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh
         rc = lib().b200splat_accumulate_packed(P, int(M), int(degree), _ptr(means3D), n, rp, cp, _ptr(campos),
                                                _ptr(dL_dsh), _ptr(dL_dgeom), int(bool(store)), _stream_ptr(dev))
     _check(rc, "accumulate_packed")
+
+
+def zero_fill(tensors):
+    """Zero up to 8 contiguous CUDA tensors with the library's background-clear kernel (one block per SM: made to run
+    beside a compute-bound kernel on another stream) on the current stream (b200splat_zero_fill)."""
+    tensors = [t for t in tensors if t is not None and t.numel()]
+    if not tensors:
+        return
+    dev = tensors[0].device
+    n = len(tensors)
+    if n > 8 or any((not t.is_cuda) or (not t.is_contiguous()) or t.device != dev for t in tensors):
+        raise RuntimeError("zero_fill takes up to 8 contiguous CUDA tensors of one device")
+    ptrs, sizes = (ctypes.c_void_p * n)(), (ctypes.c_size_t * n)()
+    for i, t in enumerate(tensors):
+        ptrs[i], sizes[i] = t.data_ptr(), t.numel() * t.element_size()
+    with torch.cuda.device(dev):
+        rc = lib().b200splat_zero_fill(n, ptrs, sizes, _stream_ptr(dev))
+    _check(rc, "zero_fill")
 
 
 def densify_stats(dL_dmeans2D, radii, xyz_gradient_accum, denom, max_radii2D):

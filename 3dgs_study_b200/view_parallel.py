@@ -281,7 +281,7 @@ class ViewParallelStep:
             fwd_done = torch.cuda.Event(); fwd_done.record(main)
             side.wait_event(fwd_done)
             with torch.cuda.stream(side):
-                geom.zero_(); dsh.zero_()
+                C.zero_fill([geom, dsh])           # one block per SM: runs beside the render backward, not before it
                 box["cleared"] = torch.cuda.Event(); box["cleared"].record(side)
         stride = 16 * P + 16                                           # words per view: 64-byte header + P rows
         if G > 1:

@@ -153,6 +153,11 @@ B200SPLAT_API int b200splat_forward_status(const void* image, int32_t width, int
  * leaves there: a caller may copy them to pinned host memory on its own stream instead of synchronising. */
 B200SPLAT_API size_t b200splat_image_status_offset(int32_t width, int32_t height);
 
+/* Background clear: zeroes up to 8 device ranges with ONE block per SM, so that the clear can run beside a
+ * compute-bound kernel on another stream (a full-grid memset takes every thread slot of the GPU while it runs).
+ * Used for the dense gradient outputs, which are cleared while the render backward runs. */
+B200SPLAT_API int b200splat_zero_fill(int32_t n, void* const* ptrs, const size_t* bytes, void* stream);
+
 /* Releases what the calling host thread holds inside the library (helper streams and events). */
 B200SPLAT_API void b200splat_shutdown(void);
 
