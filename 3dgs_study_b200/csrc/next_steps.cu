@@ -13,6 +13,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cub/cub.cuh>
+#include <mutex>
 #include <string>
 
 #include "../../include/b200splat_next.h"
@@ -700,6 +701,30 @@ __global__ void __launch_bounds__(128) knn_search_kernel(int P, const float4* __
     out[ids_sorted[i]] = __fdiv_rn(__fadd_rn(__fadd_rn(best[0], best[1]), best[2]), 3.0f);
 }
 
+// ---- b200splat_dist2_knn3_static: the same search with its scratch in the module's own device memory ----------
+// Scratch for up to B200SPLAT_KNN_STATIC_MAX_POINTS points; every GPU that loads the library holds these 12 MiB until
+// exit.  In host code `g_knn_static_scratch` is only a handle for cudaGetSymbolAddress -- never a device address.
+constexpr size_t KNN_STATIC_BYTES = (size_t)12 << 20;
+static __device__ __align__(256) unsigned char g_knn_static_scratch[KNN_STATIC_BYTES];
+
+// device address of the array on the CURRENT device, looked up once per device
+cudaError_t knn_static_scratch(char** base) {
+    static std::mutex mu;
+    static char* addr[64] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        if ((e = cudaGetSymbolAddress(&p, g_knn_static_scratch)) != cudaSuccess) return e;
+        addr[dev] = static_cast<char*>(p);
+    }
+    *base = addr[dev];
+    return cudaSuccess;
+}
+
 inline bool aligned16p(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 #define CUN(call, where)                                                                   \
@@ -901,6 +926,49 @@ int b200splat_dist2_knn3(int32_t P, const float* xyz, float* out, void* stream_)
     cudaError_t e2 = cudaFreeAsync(base, s);
     CUN(e, "knn kernels");
     CUN(e2, "knn scratch free");
+    return B200SPLAT_OK;
+}
+
+int b200splat_dist2_knn3_static(int32_t P, const float* xyz, float* out, void* stream_) {
+    if (P < 0) return report_error(B200SPLAT_ERR_INVALID_ARG, "knn (static scratch): bad P");
+    if (P > B200SPLAT_KNN_STATIC_MAX_POINTS) {
+        std::string m = "knn (static scratch): " + std::to_string(P) + " points exceed the built-in scratch (maximum " +
+                        std::to_string(B200SPLAT_KNN_STATIC_MAX_POINTS) + "); use b200splat_dist2_knn3";
+        return report_error(B200SPLAT_ERR_INVALID_ARG, m.c_str());
+    }
+    if (P == 0) return B200SPLAT_OK;
+    if (!xyz || !out) return report_error(B200SPLAT_ERR_INVALID_ARG, "knn (static scratch): null argument");
+    cudaStream_t s = (cudaStream_t)stream_;
+    const int n_boxes = (P + KBOX - 1) / KBOX, n_supers = (n_boxes + KSUPER - 1) / KSUPER;
+    size_t sort_bytes = 0;      // size query only: with caller-provided temporary storage the sort allocates nothing
+    CUN(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, (const unsigned*)nullptr, (unsigned*)nullptr,
+                                        (const unsigned*)nullptr, (unsigned*)nullptr, P, 0, 30, s), "knn (static scratch) sort size");
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+    size_t o_b6 = take(6 * sizeof(int)), o_codes = take(sizeof(unsigned) * P), o_codes2 = take(sizeof(unsigned) * P),
+           o_ids = take(sizeof(unsigned) * P), o_ids2 = take(sizeof(unsigned) * P), o_pts = take(sizeof(float4) * (size_t)P),
+           o_boxes = take(sizeof(Box) * (size_t)n_boxes), o_supers = take(sizeof(Box) * (size_t)n_supers),
+           o_sort = take(sort_bytes);
+    if (off > KNN_STATIC_BYTES) return report_error(B200SPLAT_ERR_INVALID_ARG, "knn (static scratch): scratch layout exceeds the built-in array");
+    char* base = nullptr;
+    CUN(knn_static_scratch(&base), "knn (static scratch) symbol address");
+    int* b6 = (int*)(base + o_b6);
+    unsigned *codes = (unsigned*)(base + o_codes), *codes2 = (unsigned*)(base + o_codes2), *ids = (unsigned*)(base + o_ids),
+             *ids2 = (unsigned*)(base + o_ids2);
+    float4* pts = (float4*)(base + o_pts);
+    Box *boxes = (Box*)(base + o_boxes), *supers = (Box*)(base + o_supers);
+    // every word of scratch the kernels read is written earlier in this same sequence (b6 by the init kernel): the previous
+    // call's contents never matter
+    knn_bounds_init_kernel<<<1, 32, 0, s>>>(b6);
+    const int nb = (P + 255) / 256;
+    knn_bounds_kernel<<<nb < 1184 ? nb : 1184, 256, 0, s>>>(P, xyz, b6);
+    knn_morton_kernel<<<nb, 256, 0, s>>>(P, xyz, b6, codes, ids);
+    CUN(cudaGetLastError(), "knn (static scratch) morton");
+    CUN(cub::DeviceRadixSort::SortPairs(base + o_sort, sort_bytes, codes, codes2, ids, ids2, P, 0, 30, s), "knn (static scratch) sort");
+    knn_gather_boxes_kernel<<<n_boxes, KBOX, 0, s>>>(P, xyz, ids2, pts, boxes);
+    knn_super_boxes_kernel<<<n_supers, KSUPER, 0, s>>>(n_boxes, boxes, supers);
+    knn_search_kernel<<<(P + 127) / 128, 128, 0, s>>>(P, pts, ids2, n_boxes, boxes, n_supers, supers, out);
+    CUN(cudaGetLastError(), "knn (static scratch) kernels");
     return B200SPLAT_OK;
 }
 

@@ -42,6 +42,8 @@ def lib():
         L.b200splat_adam_step.argtypes = [i32, vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, vp]
         L.b200splat_dist2_knn3.restype = ctypes.c_int
         L.b200splat_dist2_knn3.argtypes = [i32, vp, vp, vp]
+        L.b200splat_dist2_knn3_static.restype = ctypes.c_int
+        L.b200splat_dist2_knn3_static.argtypes = [i32, vp, vp, vp]
         L.b200splat_ply_write.restype = ctypes.c_int
         L.b200splat_ply_write.argtypes = [ctypes.c_char_p, i64, i32, vp, vp, vp, vp, vp, vp]
         L.b200splat_ply_read_header.restype = ctypes.c_int

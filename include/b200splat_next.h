@@ -16,6 +16,8 @@
  *   b200splat_dist2_knn3
  *       <-> simple_knn._C.distCUDA2 (submodules/simple-knn/spatial.cu:15-26 -> simple_knn.cu:186-221), called
  *           at scene/gaussian_model.py:153 to initialise the scales.
+ *   b200splat_dist2_knn3_static
+ *       no counterpart in the reference: the same search with built-in scratch, no allocation.
  *   b200splat_ply_write / _read_header / _read   (HOST memory; no GPU involved)
  *       <-> GaussianModel.save_ply / load_ply (scene/gaussian_model.py:240-259, 267-320), which go through
  *           the third-party `plyfile` package (absent from this image).
@@ -113,6 +115,18 @@ B200SPLAT_API int b200splat_adam_step(int32_t n_groups, const b200splat_adam_gro
  * fma(dz,dz, fma(dx,dx, dy*dy)) -- the instruction sequence nvcc emits for the reference's expression -- so
  * results are bit-identical to the reference's own build and to an exhaustive search.  Scratch comes from the stream-ordered CUDA allocator. */
 B200SPLAT_API int b200splat_dist2_knn3(int32_t P, const float* xyz, float* out, void* stream);
+
+/* ---- distCUDA2 without any allocation --------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot reach an
+ * allocator at all (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same arguments, same kernels and bit-identical results as b200splat_dist2_knn3, but the scratch (Morton codes, sorted
+ * ids, gathered points, boxes, sort workspace) lives in a 12 MiB array inside the library's own device image, which
+ * every GPU that loads the library holds until exit; the call performs no cudaMalloc / cudaFree / stream-ordered
+ * allocation.  P > B200SPLAT_KNN_STATIC_MAX_POINTS is rejected with B200SPLAT_ERR_INVALID_ARG.  All calls on one GPU
+ * share that array: calls that overlap on the device (different streams, no ordering between them) race -- order them.
+ * Nothing has to be cleared between calls (every scratch word read is written earlier in the same call). */
+#define B200SPLAT_KNN_STATIC_MAX_POINTS 262144
+B200SPLAT_API int b200splat_dist2_knn3_static(int32_t P, const float* xyz, float* out, void* stream);
 
 /* ---- Gaussian PLY file (host memory) --------------------------------------------------------------
  * binary_little_endian 1.0, one `vertex` element, float properties x y z nx ny nz f_dc_0..2

@@ -84,6 +84,7 @@ def test_next_header_symbols_exported_and_plain_c(tmp_path):
     hdr = open(os.path.join(ROOT, "include", "b200splat_next.h")).read()
     names = sorted(set(re.findall(r"B200SPLAT_API\s+[\w\s\*]+?\b(b200splat_\w+)\s*\(", hdr)))
     assert names == ["b200splat_activate_backward", "b200splat_activate_forward", "b200splat_adam_step", "b200splat_dist2_knn3",
+                     "b200splat_dist2_knn3_static",
                      "b200splat_l1_ssim_backward", "b200splat_l1_ssim_forward", "b200splat_l1_ssim_partials", "b200splat_ply_read",
                      "b200splat_ply_read_header", "b200splat_ply_write", "b200splat_training_loss_backward",
                      "b200splat_training_loss_forward"]
