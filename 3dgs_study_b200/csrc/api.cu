@@ -247,7 +247,8 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
                          const void* geom, const void* binning, const void* image, int32_t num_rendered,
                          const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
                          const b200splat_backward_hooks* hooks, float* packed_rows, uint32_t* packed_count,
-                         b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_);
+                         b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_,
+                         void* clean_scratch = nullptr);
 
 int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
                           const void* geom, const void* binning, const void* image, int32_t num_rendered,
@@ -275,6 +276,29 @@ int b200splat_backward_packed(const b200splat_view* view, const b200splat_gaussi
                          packed_rows, packed_count, scratch_alloc, scratch_ctx, times, stream_);
 }
 
+size_t b200splat_backward_scratch_bytes(int32_t P) {
+    if (P <= 0) return 0;
+    return (size_t)P * 12 * sizeof(float) + (((size_t)P + 255) / 256 * 256 + 256) + (size_t)P * sizeof(uint32_t);
+}
+
+int b200splat_backward_packed_clean(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
+                                    const void* geom, const void* binning, const void* image, int32_t num_rendered,
+                                    const float* dL_dout_color, const float* dL_dout_invdepth, float* dL_dmeans2D,
+                                    float* packed_rows, uint32_t* packed_count, void* scratch, size_t scratch_bytes,
+                                    b200splat_stage_times* times, void* stream_) {
+    if (!packed_rows || !packed_count) return fail(B200SPLAT_ERR_INVALID_ARG, "null packed_rows / packed_count");
+    if (!aligned16(packed_rows)) return fail(B200SPLAT_ERR_INVALID_ARG, "packed_rows must be 16-byte aligned");
+    if (g && (!g->shs || g->cov3D_precomp || g->colors_precomp))
+        return fail(B200SPLAT_ERR_INVALID_ARG, "packed rows carry SH-mode, scale/rotation-mode gradients only");
+    if (g && g->P > 0 && (!scratch || !aligned16(scratch) || scratch_bytes < b200splat_backward_scratch_bytes(g->P)))
+        return fail(B200SPLAT_ERR_INVALID_ARG, "clean scratch: null, not 16-byte aligned or smaller than b200splat_backward_scratch_bytes(P)");
+    b200splat_grads only2d;
+    memset(&only2d, 0, sizeof(only2d));
+    only2d.dL_dmeans2D = dL_dmeans2D;
+    return backward_impl(view, g, radii, geom, binning, image, num_rendered, dL_dout_color, dL_dout_invdepth, &only2d, nullptr,
+                         packed_rows, packed_count, nullptr, nullptr, times, stream_, scratch);
+}
+
 int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D, int32_t n_src,
                                 const float* const* rows, const uint32_t* const* counts, const float* campos,
                                 float* dL_dsh, float* dL_dgeom, int32_t store, void* stream_) {
@@ -296,7 +320,8 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
                          const void* geom, const void* binning, const void* image, int32_t num_rendered,
                          const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
                          const b200splat_backward_hooks* hooks, float* packed_rows, uint32_t* packed_count,
-                         b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_) {
+                         b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_,
+                         void* clean_scratch) {
     int rc = validate(view, g);
     if (rc) return rc;
     const bool packed = packed_rows != nullptr;
@@ -307,7 +332,7 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
     if (grads->dL_dsh && !aligned16(grads->dL_dsh)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dsh must be 16-byte aligned");
     if (grads->dL_drotations && !aligned16(grads->dL_drotations))
         return fail(B200SPLAT_ERR_INVALID_ARG, "dL_drotations must be 16-byte aligned");
-    if (!dL_dout_color || !scratch_alloc) return fail(B200SPLAT_ERR_INVALID_ARG, "null dL_dout_color / scratch allocator");
+    if (!dL_dout_color || (!scratch_alloc && !clean_scratch)) return fail(B200SPLAT_ERR_INVALID_ARG, "null dL_dout_color / scratch allocator");
     if (g->P > 0 && (!radii || !geom || !binning || !image)) return fail(B200SPLAT_ERR_INVALID_ARG, "null forward state");
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool debug = view->debug != 0;
@@ -326,7 +351,10 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
     const size_t acc_bytes = (size_t)P * 12 * sizeof(float);
     const size_t flag_bytes = ((size_t)P + 255) / 256 * 256 + 256;
     const size_t idx_bytes = (size_t)P * sizeof(uint32_t);
-    char* scratch = (char*)scratch_alloc(scratch_ctx, acc_bytes + flag_bytes + idx_bytes);
+    // clean scratch (b200splat_backward_packed_clean): caller-owned, all zero on entry, all zero again on return -- the
+    // 150 MB clear in front of the render backward disappears (the consumers re-zero what they read)
+    const bool clean = clean_scratch != nullptr;
+    char* scratch = clean ? (char*)clean_scratch : (char*)scratch_alloc(scratch_ctx, acc_bytes + flag_bytes + idx_bytes);
     if (!scratch) return fail(B200SPLAT_ERR_ALLOC, "allocator returned NULL (backward scratch)");
     float* acc = (float*)scratch;
     uint8_t* touched = (uint8_t*)(scratch + acc_bytes);
@@ -354,7 +382,7 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
 
     StageTimer tm(times != nullptr, stream);
     tm.mark();
-    CU(cudaMemsetAsync(scratch, 0, acc_bytes + flag_bytes, stream), "clear backward scratch");
+    if (!clean) CU(cudaMemsetAsync(scratch, 0, acc_bytes + flag_bytes, stream), "clear backward scratch");
     if (num_rendered > 0)
         STAGE(launch_render_bwd(*view, gv, bv.vals_sorted, iv, dL_dout_color, dL_dout_invdepth, acc, touched, stream), "render backward");
     tm.mark();
@@ -362,10 +390,11 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
         STAGE(launch_masked_colour_grad(P, radii, gv, acc, early_colors, stream), "masked colour gradient");
         if (hooks->after_masked_colors) hooks->after_masked_colors(hooks->ctx);
     }
-    STAGE(launch_compact_active(P, touched, active_idx, active_count, stream), "compact touched Gaussians");
+    STAGE(launch_compact_active(P, touched, clean, active_idx, active_count, stream), "compact touched Gaussians");
     CU(cudaStreamWaitEvent(stream, ss->join, 0), "join wait");
-    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, *grads, active_idx, active_count, packed_rows, packed_count, stream),
+    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, clean, *grads, active_idx, active_count, packed_rows, packed_count, stream),
           "preprocess backward");
+    if (clean) CU(cudaMemsetAsync(active_count, 0, sizeof(unsigned), stream), "reset the touched count");
     tm.mark();
     if (times) {
         CU(cudaStreamSynchronize(stream), "timing sync");

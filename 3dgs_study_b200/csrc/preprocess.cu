@@ -304,6 +304,7 @@ struct BwdParams {
     PreParams p;
     const int32_t* radii;
     const float* acc;    // [P,12] packed render-backward sums
+    int rezero;          // clean-scratch protocol: every accumulator row read here is written back as zeros
     b200splat_grads out;
     const uint32_t* active_idx;     // Gaussians the render backward touched (compact_active_kernel)
     const unsigned* active_count;
@@ -634,6 +635,14 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
             if (q < nq && ((vmask >> row) & 1u)) dst[(size_t)ri * nq + q] = wrows[row * RS4 + q];
         }
     }
+    if (bp.rezero && in_range) {
+        // clean-scratch protocol: the rows this kernel visits are exactly the rows the render backward wrote to.  Down
+        // here, not next to the loads: a store behind a read-only load of the same address makes the thread wait for
+        // the load, and the kernel lives on having all its loads in flight together (measured: 62 -> 131 us up there)
+        float4* row = reinterpret_cast<float4*>(const_cast<float*>(bp.acc)) + 3 * (size_t)i;
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        row[0] = z; row[1] = z; row[2] = z;
+    }
     if (bp.packed_rows) {
         // row t of the packed buffer (b200splat.h "packed gradient rows"): everything the other ranks need from
         // this view for Gaussian i, 64 bytes, written by one lane as four 16-byte stores
@@ -663,7 +672,7 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
 
 // Indices of the Gaussians the render backward touched, in block-arrival order (the consumers write by index, so
 // the order does not matter): one atomic per 1024-thread block.
-__global__ void __launch_bounds__(1024) compact_active_kernel(int P, const uint8_t* __restrict__ touched,
+__global__ void __launch_bounds__(1024) compact_active_kernel(int P, uint8_t* __restrict__ touched, int clear_flags,
                                                               uint32_t* __restrict__ active_idx, unsigned* __restrict__ count) {
     __shared__ unsigned s_warp[32];
     __shared__ unsigned s_base;
@@ -685,7 +694,10 @@ __global__ void __launch_bounds__(1024) compact_active_kernel(int P, const uint8
         if (lane == 31) s_base = incl ? atomicAdd(count, incl) : 0u;
     }
     __syncthreads();
-    if (on) active_idx[s_base + s_warp[warp] + __popc(m & ((1u << lane) - 1u))] = (uint32_t)i;
+    if (on) {
+        active_idx[s_base + s_warp[warp] + __popc(m & ((1u << lane) - 1u))] = (uint32_t)i;
+        if (clear_flags) touched[i] = 0;      // clean-scratch protocol: the flags are all zero again after this kernel
+    }
 }
 
 // Colour gradient of every Gaussian times the SH clamp mask, straight from the render backward's sums: the
@@ -1006,20 +1018,20 @@ cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gauss
     return cudaGetLastError();
 }
 
-cudaError_t launch_compact_active(int P, const uint8_t* touched, uint32_t* active_idx, unsigned* count, cudaStream_t s) {
+cudaError_t launch_compact_active(int P, uint8_t* touched, bool clear_flags, uint32_t* active_idx, unsigned* count, cudaStream_t s) {
     if (P == 0) return cudaSuccess;
-    compact_active_kernel<<<(P + 1023) / 1024, 1024, 0, s>>>(P, touched, active_idx, count);
+    compact_active_kernel<<<(P + 1023) / 1024, 1024, 0, s>>>(P, touched, clear_flags ? 1 : 0, active_idx, count);
     return cudaGetLastError();
 }
 
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
-                                  GeomView gv, const float* acc, const b200splat_grads& out, const uint32_t* active_idx,
+                                  GeomView gv, float* acc, bool rezero_acc, const b200splat_grads& out, const uint32_t* active_idx,
                                   const unsigned* active_count, float* packed_rows, unsigned* packed_count, cudaStream_t s) {
     (void)gv;
     if (g.P == 0) return cudaSuccess;
     BwdParams bp;
     bp.p = make_params(v, g);
-    bp.radii = radii; bp.acc = acc; bp.out = out; bp.active_idx = active_idx; bp.active_count = active_count;
+    bp.radii = radii; bp.acc = acc; bp.rezero = rezero_acc ? 1 : 0; bp.out = out; bp.active_idx = active_idx; bp.active_count = active_count;
     bp.packed_rows = reinterpret_cast<float4*>(packed_rows); bp.packed_count = packed_count;
     const int M3 = 3 * g.M;
     const int coop = (g.shs && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;

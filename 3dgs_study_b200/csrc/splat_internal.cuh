@@ -112,11 +112,11 @@ cudaError_t launch_render_fwd(const b200splat_view& v, GeomView gv, BinView bv, 
 cudaError_t launch_render_bwd(const b200splat_view& v, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
                               const float* dL_dpix, const float* dL_dinvdepth, float* acc, uint8_t* touched, cudaStream_t s);
 // indices of the touched Gaussians, in no particular order; *count (cleared by the caller) receives their number
-cudaError_t launch_compact_active(int P, const uint8_t* touched, uint32_t* active_idx, unsigned* count, cudaStream_t s);
+cudaError_t launch_compact_active(int P, uint8_t* touched, bool clear_flags, uint32_t* active_idx, unsigned* count, cudaStream_t s);
 // Per-Gaussian backward over the touched Gaussians only: writes the rows of `out` they own and nothing else --
 // the caller has zero-filled `out` (every gradient of an untouched Gaussian is exactly zero).
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
-                                  GeomView gv, const float* acc, const b200splat_grads& out, const uint32_t* active_idx,
+                                  GeomView gv, float* acc, bool rezero_acc, const b200splat_grads& out, const uint32_t* active_idx,
                                   const unsigned* active_count, float* packed_rows, unsigned* packed_count, cudaStream_t s);
 // packed_rows != NULL: instead of the dense outputs (only out.dL_dmeans2D is still written), one 64-byte row per
 // touched Gaussian and their number; launch_accumulate_packed adds the rows of any number of views (local or in

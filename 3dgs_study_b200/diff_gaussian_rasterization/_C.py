@@ -122,6 +122,11 @@ def lib():
         L.b200splat_backward_packed.restype = ctypes.c_int
         L.b200splat_backward_packed.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int32] + [ctypes.c_void_p] * 5 + [
             _alloc_fn_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_backward_scratch_bytes.restype = ctypes.c_size_t
+        L.b200splat_backward_scratch_bytes.argtypes = [ctypes.c_int32]
+        L.b200splat_backward_packed_clean.restype = ctypes.c_int
+        L.b200splat_backward_packed_clean.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int32] + [ctypes.c_void_p] * 6 + [
+            ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
         L.b200splat_accumulate_packed.restype = ctypes.c_int
         L.b200splat_accumulate_packed.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int32,
                                                   ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -497,12 +502,15 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
                                         tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
                                         imageBuffer, opacities, packed_rows, packed_count, image_height, image_width,
                                         antialiasing=False, dL_dmeans2D=None, dL_dout_invdepth=None,
-                                        stage_times: StageTimes = None):
+                                        stage_times: StageTimes = None, clean_scratch: Optional[torch.Tensor] = None):
     """The backward pass of one view, producing packed gradient rows (one 64-byte row per Gaussian the view touched)
     for the sparse view-parallel exchange instead of dense gradients (b200splat_backward_packed).
     packed_rows: fp32 CUDA tensor with room for P rows of 16 words, or the raw device address (int) of such a
     buffer; packed_count: int32/uint32 CUDA tensor of one element, or its address.  dL_dmeans2D ([P,3], optional)
-    is still written densely (densification statistics are rank-local)."""
+    is still written densely (densification statistics are rank-local).
+    clean_scratch: a tensor from `clean_backward_scratch(P, device)`, kept by the caller from call to call
+    (b200splat_backward_packed_clean): no allocation and no 150 MB clear per call.  After an exception it must be
+    zero-filled (or replaced) before it is used again."""
     dev = means3D.device
     P = means3D.shape[0]
     H, W = int(image_height), int(image_width)
@@ -528,6 +536,17 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
     view = _View(H, W, float(tan_fovx), float(tan_fovy), float(scale_modifier), int(degree), 0, 0,
                  int(bool(antialiasing)), _ptr(background), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos))
     g = _Gaussians(P, M, _ptr(means3D), _ptr(sh), None, _ptr(opacities), _ptr(scales), _ptr(rotations), None)
+    if clean_scratch is not None:
+        if not (clean_scratch.is_cuda and clean_scratch.device == dev and clean_scratch.is_contiguous()):
+            raise RuntimeError("clean_scratch must be a contiguous CUDA tensor on the Gaussians' device")
+        with torch.cuda.device(dev):
+            rc = lib().b200splat_backward_packed_clean(
+                ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
+                int(R), _ptr(dL_dout_color), _ptr(dL_dout_invdepth), _ptr(dL_dmeans2D), rows_ptr, cnt_ptr,
+                clean_scratch.data_ptr(), clean_scratch.numel() * clean_scratch.element_size(),
+                ctypes.addressof(stage_times) if stage_times is not None else None, _stream_ptr(dev))
+        _check(rc, "backward_packed_clean")
+        return
     ta = _TensorAllocator(dev)
     with torch.cuda.device(dev):
         rc = lib().b200splat_backward_packed(ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer),
@@ -539,6 +558,11 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
     if ta.error is not None:
         raise ta.error
     _check(rc, "backward_packed")
+
+
+def clean_backward_scratch(P: int, device) -> torch.Tensor:
+    """A zero-filled scratch for `rasterize_gaussians_backward_packed(..., clean_scratch=...)`."""
+    return torch.zeros(int(lib().b200splat_backward_scratch_bytes(int(P))), dtype=torch.uint8, device=device)
 
 
 def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh, dL_dgeom, store: bool = False):

@@ -88,7 +88,7 @@ class _CudaBackend:
             out = part if out is None else out.add_(part)
         return out
 
-    def view_fwd_bwd_packed(self, cam, dL, lv, rows_ptr, count_ptr, dmeans2D, on_forward=None):
+    def view_fwd_bwd_packed(self, cam, dL, lv, rows_ptr, count_ptr, dmeans2D, on_forward=None, clean_scratch=None):
         """Forward + backward of one view; the gradients leave as packed rows (sparse exchange)."""
         C, st = self.C, self.st
         R, color, radii, geom, binning, img, _ = C.rasterize_gaussians(
@@ -100,7 +100,8 @@ class _CudaBackend:
         C.rasterize_gaussians_backward_packed(
             st.bg, lv.means3D, radii, lv.scales, lv.rotations, st.scale_modifier, cam.world_view_transform,
             cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, st.sh_degree, cam.camera_center, geom, R,
-            binning, img, lv.opacities, rows_ptr, count_ptr, cam.image_height, cam.image_width, dL_dmeans2D=dmeans2D)
+            binning, img, lv.opacities, rows_ptr, count_ptr, cam.image_height, cam.image_width, dL_dmeans2D=dmeans2D,
+            clean_scratch=clean_scratch)
         return color, radii
 
 
@@ -148,6 +149,7 @@ class ViewParallelStep:
         self._side = None                    # side streams of the factorized / packed exchange
         self._packed = None                  # symmetric buffers of the packed exchange
         self._local_rows = None              # packed rows of a single-rank step (same layout, plain device memory)
+        self._clean_scratch = None           # scratch of the packed backward, clean between calls (b200splat_backward_packed_clean)
         # peer_memory (factorized, CUDA, world_size > 1): exchange through NVLink peer / multicast mappings
         # (torch symmetric memory) instead of NCCL -- the SH rebuild kernel then READS every peer's colour gradients
         # itself (all-gather fused into the kernel) and the 11 f32 / Gaussian go through an in-switch (NVLS
@@ -298,6 +300,7 @@ class ViewParallelStep:
         # how the peers learn it (b200splat_accumulate_packed with campos = NULL): no collective anywhere in the step
         buf.view(nv, stride)[:, 4:7].copy_(campos)
         color = None
+        held = []
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
             dmeans2D = torch.empty(P, 3, dtype=torch.float32, device=dev)
 
@@ -306,8 +309,19 @@ class ViewParallelStep:
                     clear_dense()
                 if on_forward is not None:
                     on_forward(img)
-            color, radii = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, after_forward)
-            self._accumulate_stats(dmeans2D, radii)
+            # the backward's scratch lives as long as the stepper and stays clean from call to call (no per-view clear);
+            # dropped while a call is in flight so that an exception cannot leave a dirty one behind
+            scratch = self._clean_scratch if self._clean_scratch is not None else C.clean_backward_scratch(P, dev)
+            self._clean_scratch = None
+            color, radii = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, after_forward, clean_scratch=scratch)
+            self._clean_scratch = scratch
+            # the densification statistics of the view (one pass over P, ~0.03 ms) leave the critical path: side stream,
+            # joined at the end of the step; `held` keeps their inputs alive until then
+            bwd_done = torch.cuda.Event(); bwd_done.record(main)
+            side.wait_event(bwd_done)
+            with torch.cuda.stream(side):
+                self._accumulate_stats(dmeans2D, radii)
+            held.append((dmeans2D, radii))
             self.last_radii = radii
         main.wait_event(box["cleared"])
         # this rank's own rows go in first, before the barrier (i.e. while the slower peers are still rendering):
@@ -326,6 +340,9 @@ class ViewParallelStep:
                 hi = min(lo + 16, len(bases))
                 C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], None, M, self.sh_degree, dsh, geom)
             pk["hd"].barrier(channel=1)                 # every rank has read them: the next step may overwrite
+        stats_done = torch.cuda.Event(); stats_done.record(side)
+        main.wait_event(stats_done)
+        del held
         # the geometry gradients are strided views of the interleaved [P,12] rows
         self.leaves.rotations.grad = geom[:, 0:4]
         self.leaves.means3D.grad = geom[:, 4:7]

@@ -353,7 +353,7 @@ def run_ours(a):
             t0 = ev[0]["ts"]
             with open(os.path.join(ROOT, "gpurun_out", f"timeline_n{world}_r{rank}.txt"), "w") as f:
                 for e in ev:
-                    if e["dur"] >= 8:
+                    if e["dur"] >= float(os.environ.get("BENCH_TRACE_MIN_US", "8")):
                         f.write(f"{e['ts'] - t0:10.1f} us  dur {e['dur']:8.1f}  stream {e['args'].get('stream')}  {e['name'][:80]}\n")
             os.remove(tr)
         if world > 1:

@@ -274,6 +274,21 @@ B200SPLAT_API int b200splat_backward_packed(const b200splat_view* view, const b2
                        const float* dL_dout_invdepth /* [1,H,W] or NULL */, float* dL_dmeans2D,
                        float* packed_rows, uint32_t* packed_count, b200splat_alloc_fn scratch_alloc,
                        void* scratch_ctx, b200splat_stage_times* times /* nullable */, void* stream);
+/* b200splat_backward_packed with a caller-owned CLEAN scratch instead of an allocator (a training step calls the
+ * backward thousands of times with the same P; the reference allocates and clears its backward buffers per call,
+ * /root/reference/gaussian_renderer/__init__.py:98 -> rasterize_gaussians_backward).  `scratch`: device memory of at least
+ * b200splat_backward_scratch_bytes(P) bytes, 16-byte aligned, ALL ZERO before its first use.  The call leaves it clean
+ * again -- the per-Gaussian backward re-zeroes exactly the accumulator rows it consumed, the compaction the flags it
+ * read -- so the next call needs no clear: the 150 MB memset in front of the render backward (3 M Gaussians) is gone.
+ * If the call returns an error the scratch must be zero-filled by the caller before it is used again.  One scratch per
+ * stream: calls that may overlap on the device need their own. */
+B200SPLAT_API size_t b200splat_backward_scratch_bytes(int32_t P);
+B200SPLAT_API int b200splat_backward_packed_clean(const b200splat_view* view, const b200splat_gaussians* g,
+                       const int32_t* radii, const void* geom, const void* binning, const void* image,
+                       int32_t num_rendered, const float* dL_dout_color,
+                       const float* dL_dout_invdepth /* [1,H,W] or NULL */, float* dL_dmeans2D,
+                       float* packed_rows, uint32_t* packed_count, void* scratch, size_t scratch_bytes,
+                       b200splat_stage_times* times /* nullable */, void* stream);
 B200SPLAT_API int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D,
                        int32_t n_src, const float* const* rows, const uint32_t* const* counts,
                        const float* campos, float* dL_dsh, float* dL_dgeom, int32_t store, void* stream);

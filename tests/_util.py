@@ -3,6 +3,7 @@ CUDA path (through the drop-in operator, i.e. through the C ABI)."""
 from __future__ import annotations
 
 import importlib
+import math
 
 import numpy as np
 import torch
@@ -22,11 +23,23 @@ def rel_err(a, b):
 
 class Case:
     def __init__(self, P, W, H, D=3, seed=0, s_med=None, bg=(0.0, 0.0, 0.0), yaw=0.0, mod=1.0,
-                 precomp_color=False, precomp_cov=False, antialiasing=False, M=None):
+                 precomp_color=False, precomp_cov=False, antialiasing=False, M=None, far=0):
         self.P, self.W, self.H, self.D, self.mod, self.aa = P, W, H, D, mod, antialiasing
         maxdeg = D if M is None else int(round(M ** 0.5)) - 1
         self.scene = synth.make_scene(P, maxdeg, seed=seed, s_med=s_med)
         self.cam = synth.make_camera(W, H, yaw=yaw)
+        if far:
+            # `far` Gaussians moved out along the viewing axis, log-uniform in depth up to ~1e5 scene units: the depth keys
+            # then span 28 significant bits instead of the usual 26 (the depth order sizes its digits from the key range)
+            g = torch.Generator().manual_seed(seed + 99)
+            c = self.cam.camera_center
+            axis = -c / c.norm()
+            d = torch.exp(torch.empty(far).uniform_(math.log(30.0), math.log(1.0e5), generator=g))
+            lateral = (torch.rand(far, 3, generator=g) - 0.5) * 0.3 * d[:, None]
+            lateral = lateral - (lateral @ axis)[:, None] * axis[None, :]
+            self.scene.means3D[:far] = c[None, :] + axis[None, :] * d[:, None] + lateral
+            self.scene.scales[:far] = (0.006 * d)[:, None] * (0.5 + torch.rand(far, 3, generator=g))
+            self.scene.opacities[:far] = 0.2 + 0.6 * torch.rand(far, 1, generator=g)
         self.bg = torch.tensor(bg, dtype=torch.float32)
         self.dL = synth.make_grad_image(W, H, seed=seed + 1)
         self.M = self.scene.shs.shape[1]

@@ -34,7 +34,15 @@ CASES = {
     "huge_splats": dict(P=400, W=640, H=480, D=1, seed=8, s_med=1.2, bg=(0.2, 0.2, 0.2)),
     # 257 x 256 = 65792 tiles > 65536: the 32-bit tile-key instantiations of the binning kernels
     "u32_tile_keys": dict(P=1500, W=4112, H=4096, D=0, seed=12, s_med=0.025),
+    # depth keys spanning 28 significant bits (1 .. 1e5 scene units) instead of the 26 of every other case: the depth order
+    # sizes its digits from the key range the preprocess kernel saw (kmin / kmax in the control block)
+    "deep_range": dict(P=3000, W=200, H=136, D=1, seed=31, s_med=0.04, bg=(0.1, 0.1, 0.1), far=400),
 }
+
+
+def _depth_key_bits(depths, vis):
+    k = depths[vis].view(np.uint32)
+    return int(k.max() - k.min()).bit_length()
 
 
 def _integer_gates(case, fr, R, radii, st):
@@ -58,6 +66,8 @@ def test_forward_state_bit_exact_and_image(name):
     fr = case.oracle_forward(want_invdepth=True)
     R, color, radii, invd, st = case.cuda_state(want_invdepth=True)
     _integer_gates(case, fr, R, radii, st)
+    if name == "deep_range":
+        assert _depth_key_bits(fr.geom.depths, fr.geom.radii > 0) > 27
     assert float(np.abs(n(color) - fr.color).max()) <= IMG_TOL
     assert float(np.abs(n(invd) - fr.invdepth).max()) <= IMG_TOL
     assert float(np.abs(n(st["final_T"]) - fr.final_T).max()) <= IMG_TOL
@@ -247,6 +257,10 @@ def test_factorized_exchange_pieces_match_direct_path():
                 assert err <= 5e-4, f"{mode} P={P} D={Dg} {name}: {err}"   # float-atomic order differs run to run
             assert torch.allclose(a.xyz_gradient_accum, b.xyz_gradient_accum, rtol=1e-5, atol=1e-12)
             assert torch.equal(a.denom, b.denom) and torch.equal(a.max_radii2D, b.max_radii2D)
+            if mode == "packed":
+                # b200splat_backward_packed_clean: accumulator rows, touched flags and their count are all zero again
+                clean = P * 48 + (P + 255) // 256 * 256 + 256
+                assert b._clean_scratch is not None and int(b._clean_scratch[:clean].count_nonzero()) == 0
 
 
 def test_graphed_step_matches_eager_step():
