@@ -301,7 +301,7 @@ int b200splat_backward_packed_clean(const b200splat_view* view, const b200splat_
 
 int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D, int32_t n_src,
                                 const float* const* rows, const uint32_t* const* counts, const float* campos,
-                                float* dL_dsh, float* dL_dgeom, int32_t store, void* stream_) {
+                                float* dL_dsh, float* dL_dgeom, uint8_t* marks, int32_t store, void* stream_) {
     if (P < 0 || M <= 0 || M > 16 || sh_degree < 0 || sh_degree > 3 || M < (sh_degree + 1) * (sh_degree + 1))
         return fail(B200SPLAT_ERR_INVALID_ARG, "bad P / M / sh_degree");
     if (n_src < 1 || n_src > B200SPLAT_MAX_VIEWS) return fail(B200SPLAT_ERR_INVALID_ARG, "n_src must be in [1, B200SPLAT_MAX_VIEWS]");
@@ -312,7 +312,16 @@ int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const f
     for (int v = 0; v < n_src; v++)
         if (!rows[v] || !counts[v]) return fail(B200SPLAT_ERR_INVALID_ARG, "null source");
     CU(launch_accumulate_packed(P, M, sh_degree, means3D, n_src, rows, reinterpret_cast<const unsigned* const*>(counts), campos,
-                                dL_dsh, dL_dgeom, store != 0, (cudaStream_t)stream_), "accumulate_packed");
+                                dL_dsh, dL_dgeom, marks, store != 0, (cudaStream_t)stream_), "accumulate_packed");
+    return B200SPLAT_OK;
+}
+
+int b200splat_clear_accumulated(int32_t P, int32_t M, float* dL_dsh, float* dL_dgeom, uint8_t* marks, void* stream_) {
+    if (P < 0 || M <= 0 || M > 16) return fail(B200SPLAT_ERR_INVALID_ARG, "bad P / M");
+    if (P == 0) return B200SPLAT_OK;
+    if (!dL_dsh || !dL_dgeom || !marks) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
+    if (!aligned16(dL_dgeom)) return fail(B200SPLAT_ERR_INVALID_ARG, "dL_dgeom must be 16-byte aligned");
+    CU(launch_clear_accumulated(P, M, dL_dsh, dL_dgeom, marks, (cudaStream_t)stream_), "clear_accumulated");
     return B200SPLAT_OK;
 }
 

@@ -841,7 +841,8 @@ template <bool STORE>
 __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P, int M, int D, const float* __restrict__ means3D,
                                                                            PackedSources src, const unsigned* __restrict__ local_counts,
                                                                            const float* __restrict__ campos,
-                                                                           float* __restrict__ dL_dsh, float* __restrict__ dL_dgeom) {
+                                                                           float* __restrict__ dL_dsh, float* __restrict__ dL_dgeom,
+                                                                           uint8_t* __restrict__ marks) {
     // A warp takes 32 consecutive rows at a time.  Phase A, one row per lane: the 64-byte row (2 KB contiguous per
     // warp, all loads in flight together -- one NVLink round trip per 32 rows when the rows are a peer's), the mean,
     // the basis and the 3 M products of ITS row, staged in shared memory.  Phase B, one row per iteration, ONE
@@ -880,6 +881,7 @@ __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P
                 if (!ok) idx = 0;
                 const bool has_col = !(q0.y == 0.f && q0.z == 0.f && q0.w == 0.f);   // false: all channels clamped
                 s_idx[wib][lane] = ok ? (idx | (has_col ? 0x80000000u : 0u)) : 0xffffffffu;
+                if (marks && ok) marks[idx] = 1;          // what launch_clear_accumulated goes by
                 s_g4[wib][lane * 3] = q1; s_g4[wib][lane * 3 + 1] = q2; s_g4[wib][lane * 3 + 2] = q3;
                 if (has_col) {
                     const float x = __ldg(means3D + 3 * (size_t)idx), y = __ldg(means3D + 3 * (size_t)idx + 1),
@@ -923,6 +925,32 @@ __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P
                     for (int el = lane; el < M3 && el < 48; el += 32) atomicAdd(drow + el, srow[el]);
                 }
             }
+        }
+    }
+}
+
+// Sparse clear of the dense gradients accumulate_packed_kernel filled: it set marks[i] for every Gaussian it added a row
+// into.  One lane per Gaussian reads its mark (3 MB for 3 M Gaussians); the warp then zeroes each marked Gaussian's dL/dsh
+// row (lanes 0..nq-1, 16 bytes each), its 48-byte geometry row (lanes 12..14) and the mark -- the mirror image of the
+// accumulate kernel's phase B.
+__global__ void __launch_bounds__(256) clear_accumulated_kernel(int P, int M3, float* __restrict__ dL_dsh, float* __restrict__ dL_dgeom,
+                                                                uint8_t* __restrict__ marks) {
+    const int i = blockIdx.x * 256 + threadIdx.x, lane = threadIdx.x & 31;
+    const bool dirty = i < P && marks[i] != 0;
+    unsigned m = __ballot_sync(0xffffffffu, dirty);
+    if (dirty) marks[i] = 0;
+    const int i0 = i - lane, nq = M3 >> 2;
+    const bool vec = (M3 & 3) == 0 && nq <= 12 && (reinterpret_cast<size_t>(dL_dsh) & 15) == 0;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    while (m) {
+        const int r = __ffs(m) - 1;
+        m &= m - 1;
+        const size_t idx = (size_t)(i0 + r);
+        if (lane >= 12 && lane < 15) reinterpret_cast<float4*>(dL_dgeom)[3 * idx + (lane - 12)] = z;
+        if (vec) {
+            if (lane < nq) reinterpret_cast<float4*>(dL_dsh + idx * M3)[lane] = z;
+        } else {
+            for (int el = lane; el < M3; el += 32) dL_dsh[idx * M3 + el] = 0.0f;
         }
     }
 }
@@ -1044,7 +1072,7 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
 
 cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, int n_src, const float* const* rows,
                                      const unsigned* const* counts, const float* campos, float* dL_dsh, float* dL_dgeom,
-                                     int store, cudaStream_t s) {
+                                     uint8_t* marks, int store, cudaStream_t s) {
     if (P == 0 || n_src == 0) return cudaSuccess;
     PackedSources src;
     src.n = n_src;
@@ -1062,9 +1090,9 @@ cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, 
     if (!campos) campos = reinterpret_cast<const float*>(lc + 32);
     const bool vec_ok = ((3 * M) & 3) == 0;     // the store flavour relies on the 16-byte path
     if (store && vec_ok && n_src == 1)
-        accumulate_packed_kernel<true><<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom);
+        accumulate_packed_kernel<true><<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom, marks);
     else
-        accumulate_packed_kernel<false><<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom);
+        accumulate_packed_kernel<false><<<sms * 16, ACC_WARPS * 32, 0, s>>>(P, M, D, means3D, src, lc, campos, dL_dsh, dL_dgeom, marks);
     return cudaGetLastError();
 }
 
@@ -1116,8 +1144,9 @@ __global__ void __launch_bounds__(256) zero_fill_kernel(ZeroRanges zr) {
         const size_t n16 = (bytes - head) >> 4;
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         size_t i = tid;
-        for (; i + 3 * nthr < n16; i += 4 * nthr) { body[i] = z; body[i + nthr] = z; body[i + 2 * nthr] = z; body[i + 3 * nthr] = z; }
-        for (; i < n16; i += nthr) body[i] = z;
+        // streaming stores (evict-first): 850 MB of zeros must not push the render backward's working set out of L2
+        for (; i + 3 * nthr < n16; i += 4 * nthr) { __stcs(body + i, z); __stcs(body + i + nthr, z); __stcs(body + i + 2 * nthr, z); __stcs(body + i + 3 * nthr, z); }
+        for (; i < n16; i += nthr) __stcs(body + i, z);
         for (size_t j = head + (n16 << 4) + tid; j < bytes; j += nthr) base[j] = 0;
     }
 }
@@ -1131,6 +1160,12 @@ cudaError_t launch_zero_fill(const ZeroRanges& zr, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     if (!sms[dev & 63]) cudaDeviceGetAttribute(&sms[dev & 63], cudaDevAttrMultiProcessorCount, dev);
     zero_fill_kernel<<<2 * (sms[dev & 63] > 0 ? sms[dev & 63] : 148), 256, 0, s>>>(zr);   // two blocks per SM
+    return cudaGetLastError();
+}
+
+cudaError_t launch_clear_accumulated(int P, int M, float* dL_dsh, float* dL_dgeom, uint8_t* marks, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    clear_accumulated_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, 3 * M, dL_dsh, dL_dgeom, marks);
     return cudaGetLastError();
 }
 

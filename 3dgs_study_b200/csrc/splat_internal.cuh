@@ -121,9 +121,12 @@ cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gauss
 // packed_rows != NULL: instead of the dense outputs (only out.dL_dmeans2D is still written), one 64-byte row per
 // touched Gaussian and their number; launch_accumulate_packed adds the rows of any number of views (local or in
 // a peer GPU's memory) into dense gradients.
+// Zeroes the rows of dL_dsh / dL_dgeom that launch_accumulate_packed wrote (it sets marks[i] for each), and the marks:
+// the dense gradients of a step are cleared for what they cost, not for P.
+cudaError_t launch_clear_accumulated(int P, int M, float* dL_dsh, float* dL_dgeom, uint8_t* marks, cudaStream_t s);
 cudaError_t launch_accumulate_packed(int P, int M, int D, const float* means3D, int n_src, const float* const* rows,
                                      const unsigned* const* counts, const float* campos, float* dL_dsh, float* dL_dgeom,
-                                     int store, cudaStream_t s);
+                                     uint8_t* marks, int store, cudaStream_t s);
 cudaError_t launch_render_stats(int W, int H, GeomView gv, const uint32_t* vals_sorted, ImgView iv,
                                 unsigned long long* out16, cudaStream_t s);
 cudaError_t launch_masked_colour_grad(int P, const int32_t* radii, GeomView gv, const float* acc, float* dcol, cudaStream_t s);

@@ -127,10 +127,12 @@ def lib():
         L.b200splat_backward_packed_clean.restype = ctypes.c_int
         L.b200splat_backward_packed_clean.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int32] + [ctypes.c_void_p] * 6 + [
             ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_clear_accumulated.restype = ctypes.c_int
+        L.b200splat_clear_accumulated.argtypes = [ctypes.c_int32, ctypes.c_int32] + [ctypes.c_void_p] * 4
         L.b200splat_accumulate_packed.restype = ctypes.c_int
         L.b200splat_accumulate_packed.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_int32,
                                                   ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
-                                                  ctypes.c_int32, ctypes.c_void_p]
+                                                  ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]
         L.b200splat_render_stats.restype = ctypes.c_int
         L.b200splat_render_stats.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int32, ctypes.c_int32,
                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
@@ -262,13 +264,16 @@ def forward_status(imageBuffer, image_height, image_width):
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
                         prefiltered, debug, antialiasing=False, want_invdepth=False, stage_times: StageTimes = None,
-                        exact: Optional[bool] = None, bin_capacity: Optional[int] = None):
+                        exact: Optional[bool] = None, bin_capacity: Optional[int] = None, status_stream=None):
     """-> (num_rendered, out_color [3,H,W], radii [P] i32, geomBuffer, binningBuffer, imgBuffer, invdepth|None)
 
     num_rendered is the pair capacity of the binning buffer (what the backward needs): the exact pair count R when
     the view was rendered in exact mode, an upper bound otherwise; forward_status(imgBuffer, H, W) gives R itself.
     exact=True: wait for R (one host round trip).  bin_capacity=n: allocate for n pairs, never wait, the caller
-    checks forward_status for overflow.  Neither (default): the capacity policy above."""
+    checks forward_status for overflow.  Neither (default): the capacity policy above.
+    status_stream (capacity policy only): a torch stream on which the 16 status bytes travel to pinned memory instead of
+    the current one, so that the kernels queued after the forward do not wait for a copy-engine round trip (0.01 ms);
+    the caller joins that stream before imgBuffer is released (and before a stream capture ends)."""
     if not means3D.is_cuda:
         raise RuntimeError("means3D must be a CUDA tensor (this rasterizer has no CPU path)")
     dev = means3D.device
@@ -345,7 +350,13 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             st["hint"] = _grow(int(num_rendered.value))
         else:                          # status words follow the view to pinned memory; read before the next one
             off = lib().b200splat_image_status_offset(W, H)
-            st["pinned"].copy_(img[off:off + 16].view(torch.int32), non_blocking=True)
+            if status_stream is not None:
+                done = torch.cuda.Event(); done.record(torch.cuda.current_stream(dev))
+                status_stream.wait_event(done)
+                with torch.cuda.stream(status_stream):
+                    st["pinned"].copy_(img[off:off + 16].view(torch.int32), non_blocking=True)
+            else:
+                st["pinned"].copy_(img[off:off + 16].view(torch.int32), non_blocking=True)
             st["pending"] = True
     return (int(num_rendered.value), out_color, radii, bufs.get(1, empty), bufs.get(2, empty), img, invdepth)
 
@@ -560,18 +571,36 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
     _check(rc, "backward_packed")
 
 
+def clear_accumulated(dL_dsh: torch.Tensor, dL_dgeom: torch.Tensor, marks: torch.Tensor):
+    """Zeroes the rows of dL_dsh [P,M,3] / dL_dgeom [P,12] that `accumulate_packed(..., marks=marks)` wrote, and the marks
+    ([P] uint8) by which it finds them (b200splat_clear_accumulated)."""
+    P, M = dL_dsh.shape[0], dL_dsh.shape[1]
+    for t in (dL_dsh, dL_dgeom):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise RuntimeError("clear_accumulated needs contiguous fp32 CUDA tensors")
+    if dL_dgeom.numel() != 12 * P:
+        raise RuntimeError("dL_dgeom must be [P,12]")
+    if not (marks.is_cuda and marks.dtype == torch.uint8 and marks.is_contiguous() and marks.numel() == P):
+        raise RuntimeError("marks must be a contiguous uint8 CUDA tensor [P]")
+    with torch.cuda.device(dL_dsh.device):
+        _check(lib().b200splat_clear_accumulated(P, M, dL_dsh.data_ptr(), dL_dgeom.data_ptr(), marks.data_ptr(),
+                                                 _stream_ptr(dL_dsh.device)), "clear_accumulated")
+
+
 def clean_backward_scratch(P: int, device) -> torch.Tensor:
     """A zero-filled scratch for `rasterize_gaussians_backward_packed(..., clean_scratch=...)`."""
     return torch.zeros(int(lib().b200splat_backward_scratch_bytes(int(P))), dtype=torch.uint8, device=device)
 
 
-def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh, dL_dgeom, store: bool = False):
+def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh, dL_dgeom, store: bool = False,
+                      marks: Optional[torch.Tensor] = None):
     """Adds the packed gradient rows of len(rows) views into dense gradients the caller has cleared: dL_dsh [P,M,3],
     rebuilt from each row's colour gradient and its view's camera centre, and dL_dgeom [P,12] = per Gaussian
     (d rotation[4], d mean[3], d scale[3], d opacity, 0) interleaved (b200splat_accumulate_packed).
     rows[v] / counts[v]: tensors or raw device addresses (ints) -- e.g. a peer GPU's buffers mapped through symmetric
     memory: the kernel then reads them over NVLink.  campos: [len(rows),3] fp32 CUDA tensor.
-    store=True (one source): written instead of added, for the first source into freshly cleared gradients."""
+    store=True (one source): written instead of added, for the first source into freshly cleared gradients.
+    marks ([P] uint8, optional): set to 1 for every Gaussian a row goes into -- what `clear_accumulated` goes by."""
     dev = means3D.device
     P = means3D.shape[0]
     means3D = _f32c(means3D, "means3D", dev)
@@ -586,9 +615,11 @@ def accumulate_packed(means3D, rows, counts, campos, M: int, degree: int, dL_dsh
     for name, t, numel in (("dL_dsh", dL_dsh, 3 * int(M) * P), ("dL_dgeom", dL_dgeom, 12 * P)):
         if t is None or not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == numel):
             raise RuntimeError(f"{name} must be a contiguous fp32 CUDA tensor with {numel} elements")
+    if marks is not None and not (marks.is_cuda and marks.dtype == torch.uint8 and marks.is_contiguous() and marks.numel() == P):
+        raise RuntimeError("marks must be a contiguous uint8 CUDA tensor [P]")
     with torch.cuda.device(dev):
         rc = lib().b200splat_accumulate_packed(P, int(M), int(degree), _ptr(means3D), n, rp, cp, _ptr(campos),
-                                               _ptr(dL_dsh), _ptr(dL_dgeom), int(bool(store)), _stream_ptr(dev))
+                                               _ptr(dL_dsh), _ptr(dL_dgeom), _ptr(marks), int(bool(store)), _stream_ptr(dev))
     _check(rc, "accumulate_packed")
 
 

@@ -88,13 +88,14 @@ class _CudaBackend:
             out = part if out is None else out.add_(part)
         return out
 
-    def view_fwd_bwd_packed(self, cam, dL, lv, rows_ptr, count_ptr, dmeans2D, on_forward=None, clean_scratch=None):
+    def view_fwd_bwd_packed(self, cam, dL, lv, rows_ptr, count_ptr, dmeans2D, on_forward=None, clean_scratch=None,
+                            status_stream=None):
         """Forward + backward of one view; the gradients leave as packed rows (sparse exchange)."""
         C, st = self.C, self.st
         R, color, radii, geom, binning, img, _ = C.rasterize_gaussians(
             st.bg, lv.means3D, None, lv.opacities, lv.scales, lv.rotations, st.scale_modifier, None,
             cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy, cam.image_height,
-            cam.image_width, lv.shs, st.sh_degree, cam.camera_center, False, False)
+            cam.image_width, lv.shs, st.sh_degree, cam.camera_center, False, False, status_stream=status_stream)
         if on_forward is not None:
             on_forward(color)
         C.rasterize_gaussians_backward_packed(
@@ -102,7 +103,7 @@ class _CudaBackend:
             cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, st.sh_degree, cam.camera_center, geom, R,
             binning, img, lv.opacities, rows_ptr, count_ptr, cam.image_height, cam.image_width, dL_dmeans2D=dmeans2D,
             clean_scratch=clean_scratch)
-        return color, radii
+        return color, radii, img
 
 
 class ViewParallelStep:
@@ -149,6 +150,7 @@ class ViewParallelStep:
         self._side = None                    # side streams of the factorized / packed exchange
         self._packed = None                  # symmetric buffers of the packed exchange
         self._local_rows = None              # packed rows of a single-rank step (same layout, plain device memory)
+        self._dense = None                   # dense gradients of the packed exchange (kept and cleared sparsely from step to step)
         self._clean_scratch = None           # scratch of the packed backward, clean between calls (b200splat_backward_packed_clean)
         # peer_memory (factorized, CUDA, world_size > 1): exchange through NVLink peer / multicast mappings
         # (torch symmetric memory) instead of NCCL -- the SH rebuild kernel then READS every peer's colour gradients
@@ -270,21 +272,24 @@ class ViewParallelStep:
             self._side = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
         comm, side = self._side
         campos = torch.stack([c.camera_center.to(dev).float() for c in cams]).contiguous()
-        # Dense gradients (the rows are ADDED into them at the end of the step): 720 MB at 3 M SH3 to clear.  The clear
-        # runs on a side stream UNDER THE FIRST VIEW'S RENDER BACKWARD -- that kernel is FP32-bound and leaves HBM idle,
-        # whereas next to the HBM-bound preprocess / binning kernels at the start of the step it would cost its full
-        # 0.1 ms (measured, profiles/r02_timeline_n2_rank0.txt of the first version).
-        geom = torch.empty(P, 12, dtype=torch.float32, device=dev)     # (d rotation 4, d mean 3, d scale 3, d opacity, 0)
-        dsh = torch.empty(P, M, 3, dtype=torch.float32, device=dev)
+        # Dense gradients (the rows are ADDED into them at the end of the step).  They belong to the stepper and live
+        # from step to step: zero everywhere except the rows the last step's accumulate calls wrote, and exactly those
+        # rows are cleared again (b200splat_clear_accumulated, by the marks the accumulate calls leave) instead of all 0.85 GB
+        # -- a full clear next to the render backward costs that kernel 0.1 ms (measured, whichever way it is launched).
+        # Nobody else may write into `.grad` of the leaves between steps (reading, scaling in place are fine).
+        dn = self._dense
+        if dn is None or dn[0].shape[0] != P or dn[1].shape[1] != M or dn[0].device != dev:
+            dn = self._dense = (torch.zeros(P, 12, dtype=torch.float32, device=dev),    # (d rotation 4, d mean 3, d scale 3,
+                                torch.zeros(P, M, 3, dtype=torch.float32, device=dev),  #  d opacity, 0)
+                                torch.zeros(P, dtype=torch.uint8, device=dev))          # marks: Gaussians with a row added
+        geom, dsh, marks = dn
         box = {}
-
-        def clear_dense():
-            # (no record_stream: the main stream waits for `cleared` before it touches, and long before it frees, them)
-            fwd_done = torch.cuda.Event(); fwd_done.record(main)
-            side.wait_event(fwd_done)
-            with torch.cuda.stream(side):
-                C.zero_fill([geom, dsh])           # one block per SM: runs beside the render backward, not before it
-                box["cleared"] = torch.cuda.Event(); box["cleared"].record(side)
+        # the sparse clear runs beside the forward's first kernels, on the side stream
+        step_start = torch.cuda.Event(); step_start.record(main)
+        side.wait_event(step_start)
+        with torch.cuda.stream(side):
+            C.clear_accumulated(dsh, geom, marks)
+            box["cleared"] = torch.cuda.Event(); box["cleared"].record(side)
         stride = 16 * P + 16                                           # words per view: 64-byte header + P rows
         if G > 1:
             pk = self._setup_packed(P, nv, dev)
@@ -304,16 +309,15 @@ class ViewParallelStep:
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
             dmeans2D = torch.empty(P, 3, dtype=torch.float32, device=dev)
 
-            def after_forward(img, first=(k == 0)):
-                if first:
-                    clear_dense()
+            def after_forward(img):
                 if on_forward is not None:
                     on_forward(img)
             # the backward's scratch lives as long as the stepper and stays clean from call to call (no per-view clear);
             # dropped while a call is in flight so that an exception cannot leave a dirty one behind
             scratch = self._clean_scratch if self._clean_scratch is not None else C.clean_backward_scratch(P, dev)
             self._clean_scratch = None
-            color, radii = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, after_forward, clean_scratch=scratch)
+            color, radii, img = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, after_forward,
+                                                       clean_scratch=scratch, status_stream=side)
             self._clean_scratch = scratch
             # the densification statistics of the view (one pass over P, ~0.03 ms) leave the critical path: side stream,
             # joined at the end of the step; `held` keeps their inputs alive until then
@@ -321,14 +325,14 @@ class ViewParallelStep:
             side.wait_event(bwd_done)
             with torch.cuda.stream(side):
                 self._accumulate_stats(dmeans2D, radii)
-            held.append((dmeans2D, radii))
+            held.append((dmeans2D, radii, img))      # (img: its status words are read on the side stream)
             self.last_radii = radii
         main.wait_event(box["cleared"])
         # this rank's own rows go in first, before the barrier (i.e. while the slower peers are still rendering):
         # the first view is WRITTEN into the freshly cleared gradients (plain stores), further local views are added
-        C.accumulate_packed(lv.means3D, [base[0] + 64], [base[0]], None, M, self.sh_degree, dsh, geom, store=True)
+        C.accumulate_packed(lv.means3D, [base[0] + 64], [base[0]], None, M, self.sh_degree, dsh, geom, store=True, marks=marks)
         if nv > 1:
-            C.accumulate_packed(lv.means3D, [b + 64 for b in base[1:]], base[1:], None, M, self.sh_degree, dsh, geom)
+            C.accumulate_packed(lv.means3D, [b + 64 for b in base[1:]], base[1:], None, M, self.sh_degree, dsh, geom, marks=marks)
         if G > 1:
             pk["hd"].barrier(channel=0)                 # every rank's rows (and headers) are in place
             # the peers' rows, read over NVLink; each rank walks its peers in a different rotation, so that at any
@@ -338,7 +342,7 @@ class ViewParallelStep:
             bases = [pk["ptrs"][r] + 4 * k * stride for r in order for k in range(nv)]
             for lo in range(0, len(bases), 16):         # B200SPLAT_MAX_VIEWS sources per launch
                 hi = min(lo + 16, len(bases))
-                C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], None, M, self.sh_degree, dsh, geom)
+                C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], None, M, self.sh_degree, dsh, geom, marks=marks)
             pk["hd"].barrier(channel=1)                 # every rank has read them: the next step may overwrite
         stats_done = torch.cuda.Event(); stats_done.record(side)
         main.wait_event(stats_done)

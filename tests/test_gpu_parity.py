@@ -263,6 +263,41 @@ def test_factorized_exchange_pieces_match_direct_path():
                 assert b._clean_scratch is not None and int(b._clean_scratch[:clean].count_nonzero()) == 0
 
 
+def test_packed_step_leaves_nothing_of_the_previous_step():
+    """The packed step keeps its dense gradients from step to step and clears only the rows the last step wrote
+    (b200splat_clear_accumulated): after a step on view A, a step on view B must give what a fresh stepper gives for B --
+    also when B touches far fewer Gaussians than A -- and untouched Gaussians must hold exact zeros."""
+    import importlib
+    vp = importlib.import_module("3dgs_study_b200.view_parallel")
+    synth_ = importlib.import_module("3dgs_study_b200.synth")
+    dev = torch.device("cuda:0")
+    P, Dg, W, H = 8000, 2, 240, 136
+    sc = synth_.make_scene(P, Dg, seed=5, s_med=0.04).to(dev)
+    cams = [synth_.make_camera(W, H, yaw=y).to(dev) for y in (0.0, 2.5, 1.2)]
+    dLs = [synth_.make_grad_image(W, H, seed=60 + k).to(dev) for k in range(3)]
+    dLs[1][:, :, W // 4:] = 0.0                      # view B: only a quarter of the image carries gradient
+    params = vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations)
+    bg = torch.tensor([0.2, 0.1, 0.3], device=dev)
+    run = vp.ViewParallelStep(params, Dg, bg, exchange="packed")
+    for k in (0, 1, 2, 1):
+        run.step([cams[k]], [dLs[k]])
+        fresh = vp.ViewParallelStep(params, Dg, bg, exchange="allreduce")
+        fresh.step([cams[k]], [dLs[k]])
+        torch.cuda.synchronize()
+        for name, x, y in zip(vp.GaussianParams._fields, run.grads(), fresh.grads()):
+            err = float((x - y).abs().max()) / max(float(y.abs().max()), 1e-20)
+            assert err <= 5e-4, f"view {k} {name}: {err}"
+            untouched = (y.reshape(P, -1) == 0).all(dim=1)
+            assert int(untouched.sum()) > P // 4 and bool((x.reshape(P, -1)[untouched] == 0).all()), f"view {k} {name}: stale rows"
+    # two views per step: the second one's rows are added onto the first one's
+    run.step([cams[0], cams[2]], [dLs[0], dLs[2]])
+    fresh = vp.ViewParallelStep(params, Dg, bg, exchange="allreduce")
+    fresh.step([cams[0], cams[2]], [dLs[0], dLs[2]])
+    torch.cuda.synchronize()
+    for name, x, y in zip(vp.GaussianParams._fields, run.grads(), fresh.grads()):
+        assert float((x - y).abs().max()) / max(float(y.abs().max()), 1e-20) <= 5e-4, name
+
+
 def test_graphed_step_matches_eager_step():
     """view_parallel.GraphedStep: the whole packed-row step captured in a CUDA graph and replayed gives what the eagerly
     queued step gives, view after view, and the densification statistics keep accumulating across replays."""
