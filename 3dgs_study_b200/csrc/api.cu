@@ -124,8 +124,7 @@ int b200splat_forward(const b200splat_view* view, const b200splat_gaussians* g, 
 
     StageTimer tm(times != nullptr, stream);
     tm.mark();
-    CU(cudaMemsetAsync(iv.counters, 0, CTR_WORDS * sizeof(unsigned int), stream), "clear control block");
-    CU(cudaMemsetAsync(iv.ranges, 0, (size_t)(T > 0 ? T : 1) * sizeof(int2), stream), "clear ranges");
+    CU(cudaMemsetAsync(iv.ranges, 0, iv.clear_bytes, stream), "clear ranges + control block");   // adjacent: one node
     STAGE(launch_preprocess_fwd(*view, *g, gv, out->radii, iv.counters, stream), "preprocess");
     tm.mark();
     STAGE(launch_depth_order(gv, P, iv.counters, stream), "depth order");
@@ -248,7 +247,7 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
                          const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
                          const b200splat_backward_hooks* hooks, float* packed_rows, uint32_t* packed_count,
                          b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_,
-                         void* clean_scratch = nullptr);
+                         void* clean_scratch = nullptr, float* norm_accum = nullptr);
 
 int b200splat_backward_ex(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
                           const void* geom, const void* binning, const void* image, int32_t num_rendered,
@@ -284,8 +283,8 @@ size_t b200splat_backward_scratch_bytes(int32_t P) {
 int b200splat_backward_packed_clean(const b200splat_view* view, const b200splat_gaussians* g, const int32_t* radii,
                                     const void* geom, const void* binning, const void* image, int32_t num_rendered,
                                     const float* dL_dout_color, const float* dL_dout_invdepth, float* dL_dmeans2D,
-                                    float* packed_rows, uint32_t* packed_count, void* scratch, size_t scratch_bytes,
-                                    b200splat_stage_times* times, void* stream_) {
+                                    float* xyz_gradient_accum, float* packed_rows, uint32_t* packed_count, void* scratch,
+                                    size_t scratch_bytes, b200splat_stage_times* times, void* stream_) {
     if (!packed_rows || !packed_count) return fail(B200SPLAT_ERR_INVALID_ARG, "null packed_rows / packed_count");
     if (!aligned16(packed_rows)) return fail(B200SPLAT_ERR_INVALID_ARG, "packed_rows must be 16-byte aligned");
     if (g && (!g->shs || g->cov3D_precomp || g->colors_precomp))
@@ -296,7 +295,7 @@ int b200splat_backward_packed_clean(const b200splat_view* view, const b200splat_
     memset(&only2d, 0, sizeof(only2d));
     only2d.dL_dmeans2D = dL_dmeans2D;
     return backward_impl(view, g, radii, geom, binning, image, num_rendered, dL_dout_color, dL_dout_invdepth, &only2d, nullptr,
-                         packed_rows, packed_count, nullptr, nullptr, times, stream_, scratch);
+                         packed_rows, packed_count, nullptr, nullptr, times, stream_, scratch, xyz_gradient_accum);
 }
 
 int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D, int32_t n_src,
@@ -330,7 +329,7 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
                          const float* dL_dout_color, const float* dL_dout_invdepth, const b200splat_grads* grads,
                          const b200splat_backward_hooks* hooks, float* packed_rows, uint32_t* packed_count,
                          b200splat_alloc_fn scratch_alloc, void* scratch_ctx, b200splat_stage_times* times, void* stream_,
-                         void* clean_scratch) {
+                         void* clean_scratch, float* norm_accum) {
     int rc = validate(view, g);
     if (rc) return rc;
     const bool packed = packed_rows != nullptr;
@@ -401,8 +400,8 @@ static int backward_impl(const b200splat_view* view, const b200splat_gaussians* 
     }
     STAGE(launch_compact_active(P, touched, clean, active_idx, active_count, stream), "compact touched Gaussians");
     CU(cudaStreamWaitEvent(stream, ss->join, 0), "join wait");
-    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, clean, *grads, active_idx, active_count, packed_rows, packed_count, stream),
-          "preprocess backward");
+    STAGE(launch_preprocess_bwd(*view, *g, radii, gv, acc, clean, *grads, active_idx, active_count, packed_rows, packed_count,
+                                norm_accum, clean && packed, stream), "preprocess backward");
     if (clean) CU(cudaMemsetAsync(active_count, 0, sizeof(unsigned), stream), "reset the touched count");
     tm.mark();
     if (times) {
@@ -440,6 +439,14 @@ int b200splat_densify_stats(int32_t P, const float* dL_dmeans2D, const int32_t* 
     if (P == 0) return B200SPLAT_OK;
     if (!dL_dmeans2D || !radii || !xyz_gradient_accum || !denom || !max_radii2D) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
     CU(launch_densify_stats(P, dL_dmeans2D, radii, xyz_gradient_accum, denom, max_radii2D, (cudaStream_t)stream_), "densify_stats");
+    return B200SPLAT_OK;
+}
+
+int b200splat_densify_stats_visible(int32_t P, const int32_t* radii, float* denom, float* max_radii2D, void* stream_) {
+    if (P < 0) return fail(B200SPLAT_ERR_INVALID_ARG, "bad P");
+    if (P == 0) return B200SPLAT_OK;
+    if (!radii || !denom || !max_radii2D) return fail(B200SPLAT_ERR_INVALID_ARG, "null argument");
+    CU(launch_densify_stats_visible(P, radii, denom, max_radii2D, (cudaStream_t)stream_), "densify_stats_visible");
     return B200SPLAT_OK;
 }
 

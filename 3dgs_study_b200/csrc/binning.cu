@@ -615,9 +615,10 @@ ImgView carve_image(void* base, int W, int H) {
     size_t T = (size_t)tiles_of(W, H);
     size_t N = (size_t)W * H;
     v.ranges = (int2*)(b + off); off += align256((T > 0 ? T : 1) * sizeof(int2));
+    v.counters = (unsigned int*)(b + off); off += align256(CTR_WORDS * sizeof(unsigned int));   // right behind the ranges:
+    v.clear_bytes = off;                                                                        //   one clear for both
     v.final_T = (float*)(b + off); off += align256((N > 0 ? N : 1) * sizeof(float));
     v.n_contrib = (uint32_t*)(b + off); off += align256((N > 0 ? N : 1) * sizeof(uint32_t));
-    v.counters = (unsigned int*)(b + off); off += align256(CTR_WORDS * sizeof(unsigned int));
     const size_t Tn = T > 0 ? T : 1;
     v.tile_order = (uint32_t*)(b + off); off += align256(Tn * sizeof(uint32_t));
     v.total = off;

@@ -305,6 +305,8 @@ struct BwdParams {
     const int32_t* radii;
     const float* acc;    // [P,12] packed render-backward sums
     int rezero;          // clean-scratch protocol: every accumulator row read here is written back as zeros
+    int write_header;    // packed mode: packed_count heads a 64-byte header; words 4..6 of it receive the camera centre
+    float* norm_accum;   // packed mode, nullable: xyz_gradient_accum[i] += ||dL/dmean2D[i]|| for the Gaussians visited here
     b200splat_grads out;
     const uint32_t* active_idx;     // Gaussians the render backward touched (compact_active_kernel)
     const unsigned* active_count;
@@ -646,7 +648,13 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
     if (bp.packed_rows) {
         // row t of the packed buffer (b200splat.h "packed gradient rows"): everything the other ranks need from
         // this view for Gaussian i, 64 bytes, written by one lane as four 16-byte stores
-        if (t == 0) *bp.packed_count = __ldg(bp.active_count);
+        if (t == 0) {
+            *bp.packed_count = __ldg(bp.active_count);
+            if (bp.write_header) {      // how the other ranks learn this view's camera (accumulate_packed, campos = NULL)
+                float* hdr = reinterpret_cast<float*>(bp.packed_count);
+                hdr[4] = __ldg(p.campos); hdr[5] = __ldg(p.campos + 1); hdr[6] = __ldg(p.campos + 2);
+            }
+        }
         if (in_range) {
             float4* row = bp.packed_rows + 4 * (size_t)t;
             row[0] = make_float4(__uint_as_float((unsigned)i), dcol[0], dcol[1], dcol[2]);
@@ -654,6 +662,9 @@ __global__ void __launch_bounds__(PRE_THREADS, PRE_MINB_BWD) preprocess_bwd_kern
             row[2] = make_float4(dmean[0], dmean[1], dmean[2], dsc[0]);
             row[3] = make_float4(dsc[1], dsc[2], dop, 0.f);
             if (o.dL_dmeans2D) store3(o.dL_dmeans2D, i, dndc[0], dndc[1], 0.f);
+            // the gradient-norm part of the densification statistics (densify_stats_kernel's first line): a Gaussian this
+            // kernel does not visit has a zero gradient and would add nothing
+            if (bp.norm_accum) bp.norm_accum[i] += sqrtf(dndc[0] * dndc[0] + dndc[1] * dndc[1]);
         }
         return;
     }
@@ -971,6 +982,18 @@ __global__ void densify_stats_kernel(int P, const float* __restrict__ dmeans2D, 
     }
 }
 
+// The part of densify_stats_kernel that needs the radii only (known after the forward): denom and max_radii2D.
+__global__ void densify_stats_visible_kernel(int P, const int32_t* __restrict__ radii, float* __restrict__ denom,
+                                             float* __restrict__ max_radii) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const int r = radii[i];
+    if (r > 0) {
+        denom[i] += 1.0f;
+        max_radii[i] = fmaxf(max_radii[i], (float)r);
+    }
+}
+
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
                                     uint8_t* __restrict__ present) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1046,6 +1069,12 @@ cudaError_t launch_preprocess_fwd(const b200splat_view& v, const b200splat_gauss
     return cudaGetLastError();
 }
 
+cudaError_t launch_densify_stats_visible(int P, const int32_t* radii, float* denom, float* max_radii2D, cudaStream_t s) {
+    if (P == 0) return cudaSuccess;
+    densify_stats_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, denom, max_radii2D);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_compact_active(int P, uint8_t* touched, bool clear_flags, uint32_t* active_idx, unsigned* count, cudaStream_t s) {
     if (P == 0) return cudaSuccess;
     compact_active_kernel<<<(P + 1023) / 1024, 1024, 0, s>>>(P, touched, clear_flags ? 1 : 0, active_idx, count);
@@ -1054,13 +1083,15 @@ cudaError_t launch_compact_active(int P, uint8_t* touched, bool clear_flags, uin
 
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
                                   GeomView gv, float* acc, bool rezero_acc, const b200splat_grads& out, const uint32_t* active_idx,
-                                  const unsigned* active_count, float* packed_rows, unsigned* packed_count, cudaStream_t s) {
+                                  const unsigned* active_count, float* packed_rows, unsigned* packed_count, float* norm_accum,
+                                  bool write_header, cudaStream_t s) {
     (void)gv;
     if (g.P == 0) return cudaSuccess;
     BwdParams bp;
     bp.p = make_params(v, g);
     bp.radii = radii; bp.acc = acc; bp.rezero = rezero_acc ? 1 : 0; bp.out = out; bp.active_idx = active_idx; bp.active_count = active_count;
-    bp.packed_rows = reinterpret_cast<float4*>(packed_rows); bp.packed_count = packed_count;
+    bp.packed_rows = reinterpret_cast<float4*>(packed_rows); bp.packed_count = packed_count; bp.norm_accum = norm_accum;
+    bp.write_header = write_header ? 1 : 0;
     const int M3 = 3 * g.M;
     const int coop = (g.shs && g.M > 0 && (M3 & 3) == 0 && g.M <= 16) ? 1 : 0;
     const size_t smem = coop ? (size_t)(PRE_THREADS / 32) * 32 * (((M3 >> 2) & 1) ? M3 : M3 + 4) * sizeof(float) : 0;

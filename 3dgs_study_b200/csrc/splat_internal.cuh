@@ -77,6 +77,7 @@ struct BinView {
 struct ImgView {
     int2* ranges; float* final_T; uint32_t* n_contrib; unsigned int* counters;
     uint32_t* tile_order;       // tiles by decreasing list length (NULL: index order)
+    size_t clear_bytes;         // ranges + counters are adjacent at the head of the buffer: the bytes a forward clears
     size_t total;
 };
 
@@ -117,7 +118,9 @@ cudaError_t launch_compact_active(int P, uint8_t* touched, bool clear_flags, uin
 // the caller has zero-filled `out` (every gradient of an untouched Gaussian is exactly zero).
 cudaError_t launch_preprocess_bwd(const b200splat_view& v, const b200splat_gaussians& g, const int32_t* radii,
                                   GeomView gv, float* acc, bool rezero_acc, const b200splat_grads& out, const uint32_t* active_idx,
-                                  const unsigned* active_count, float* packed_rows, unsigned* packed_count, cudaStream_t s);
+                                  const unsigned* active_count, float* packed_rows, unsigned* packed_count, float* norm_accum,
+                                  bool write_header, cudaStream_t s);
+cudaError_t launch_densify_stats_visible(int P, const int32_t* radii, float* denom, float* max_radii2D, cudaStream_t s);
 // packed_rows != NULL: instead of the dense outputs (only out.dL_dmeans2D is still written), one 64-byte row per
 // touched Gaussian and their number; launch_accumulate_packed adds the rows of any number of views (local or in
 // a peer GPU's memory) into dense gradients.

@@ -125,8 +125,10 @@ def lib():
         L.b200splat_backward_scratch_bytes.restype = ctypes.c_size_t
         L.b200splat_backward_scratch_bytes.argtypes = [ctypes.c_int32]
         L.b200splat_backward_packed_clean.restype = ctypes.c_int
-        L.b200splat_backward_packed_clean.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int32] + [ctypes.c_void_p] * 6 + [
+        L.b200splat_backward_packed_clean.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int32] + [ctypes.c_void_p] * 7 + [
             ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.b200splat_densify_stats_visible.restype = ctypes.c_int
+        L.b200splat_densify_stats_visible.argtypes = [ctypes.c_int32] + [ctypes.c_void_p] * 4
         L.b200splat_clear_accumulated.restype = ctypes.c_int
         L.b200splat_clear_accumulated.argtypes = [ctypes.c_int32, ctypes.c_int32] + [ctypes.c_void_p] * 4
         L.b200splat_accumulate_packed.restype = ctypes.c_int
@@ -513,7 +515,8 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
                                         tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R, binningBuffer,
                                         imageBuffer, opacities, packed_rows, packed_count, image_height, image_width,
                                         antialiasing=False, dL_dmeans2D=None, dL_dout_invdepth=None,
-                                        stage_times: StageTimes = None, clean_scratch: Optional[torch.Tensor] = None):
+                                        stage_times: StageTimes = None, clean_scratch: Optional[torch.Tensor] = None,
+                                        xyz_gradient_accum: Optional[torch.Tensor] = None):
     """The backward pass of one view, producing packed gradient rows (one 64-byte row per Gaussian the view touched)
     for the sparse view-parallel exchange instead of dense gradients (b200splat_backward_packed).
     packed_rows: fp32 CUDA tensor with room for P rows of 16 words, or the raw device address (int) of such a
@@ -521,7 +524,9 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
     is still written densely (densification statistics are rank-local).
     clean_scratch: a tensor from `clean_backward_scratch(P, device)`, kept by the caller from call to call
     (b200splat_backward_packed_clean): no allocation and no 150 MB clear per call.  After an exception it must be
-    zero-filled (or replaced) before it is used again."""
+    zero-filled (or replaced) before it is used again.
+    xyz_gradient_accum ([P] or [P,1] fp32, with clean_scratch only): the backward adds ||dL/dmean2D|| of the Gaussians it
+    visits into it (the gradient-norm line of `densify_stats`; `densify_stats_visible` does the other two)."""
     dev = means3D.device
     P = means3D.shape[0]
     H, W = int(image_height), int(image_width)
@@ -547,13 +552,17 @@ def rasterize_gaussians_backward_packed(background, means3D, radii, scales, rota
     view = _View(H, W, float(tan_fovx), float(tan_fovy), float(scale_modifier), int(degree), 0, 0,
                  int(bool(antialiasing)), _ptr(background), _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos))
     g = _Gaussians(P, M, _ptr(means3D), _ptr(sh), None, _ptr(opacities), _ptr(scales), _ptr(rotations), None)
+    if xyz_gradient_accum is not None and (clean_scratch is None or not (
+            xyz_gradient_accum.is_cuda and xyz_gradient_accum.dtype == torch.float32 and xyz_gradient_accum.is_contiguous()
+            and xyz_gradient_accum.numel() == P)):
+        raise RuntimeError("xyz_gradient_accum must be a contiguous fp32 CUDA tensor of P elements, and needs clean_scratch")
     if clean_scratch is not None:
         if not (clean_scratch.is_cuda and clean_scratch.device == dev and clean_scratch.is_contiguous()):
             raise RuntimeError("clean_scratch must be a contiguous CUDA tensor on the Gaussians' device")
         with torch.cuda.device(dev):
             rc = lib().b200splat_backward_packed_clean(
                 ctypes.addressof(view), ctypes.addressof(g), _ptr(radii), _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
-                int(R), _ptr(dL_dout_color), _ptr(dL_dout_invdepth), _ptr(dL_dmeans2D), rows_ptr, cnt_ptr,
+                int(R), _ptr(dL_dout_color), _ptr(dL_dout_invdepth), _ptr(dL_dmeans2D), _ptr(xyz_gradient_accum), rows_ptr, cnt_ptr,
                 clean_scratch.data_ptr(), clean_scratch.numel() * clean_scratch.element_size(),
                 ctypes.addressof(stage_times) if stage_times is not None else None, _stream_ptr(dev))
         _check(rc, "backward_packed_clean")
@@ -654,6 +663,21 @@ def densify_stats(dL_dmeans2D, radii, xyz_gradient_accum, denom, max_radii2D):
         rc = lib().b200splat_densify_stats(P, _ptr(dL_dmeans2D), _ptr(radii), _ptr(xyz_gradient_accum), _ptr(denom),
                                            _ptr(max_radii2D), _stream_ptr(dev))
     _check(rc, "densify_stats")
+
+
+def densify_stats_visible(radii, denom, max_radii2D):
+    """In place: denom += 1 and max_radii2D = max(., radii) for radii > 0 -- the lines of `densify_stats` that need the
+    forward's radii only (b200splat_densify_stats_visible)."""
+    dev = radii.device
+    P = radii.shape[0]
+    for t in (denom, max_radii2D):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == P):
+            raise RuntimeError("densify_stats_visible: contiguous fp32 CUDA tensors of P elements required")
+    if radii.dtype != torch.int32:
+        raise RuntimeError("radii must be int32")
+    with torch.cuda.device(dev):
+        _check(lib().b200splat_densify_stats_visible(P, _ptr(radii), _ptr(denom), _ptr(max_radii2D), _stream_ptr(dev)),
+               "densify_stats_visible")
 
 
 def render_stats(P, W, H, num_rendered, geomBuffer, binningBuffer, imageBuffer):

@@ -89,8 +89,11 @@ class _CudaBackend:
         return out
 
     def view_fwd_bwd_packed(self, cam, dL, lv, rows_ptr, count_ptr, dmeans2D, on_forward=None, clean_scratch=None,
-                            status_stream=None):
-        """Forward + backward of one view; the gradients leave as packed rows (sparse exchange)."""
+                            status_stream=None, stats=None):
+        """Forward + backward of one view; the gradients leave as packed rows (sparse exchange).
+        stats = (xyz_gradient_accum, denom, max_radii2D) with clean_scratch and status_stream: the densification
+        statistics of the view are updated on the way -- the radii part on `status_stream` beside the render backward,
+        the gradient norms inside the per-Gaussian backward -- and no dense dL/dmeans2D is produced."""
         C, st = self.C, self.st
         R, color, radii, geom, binning, img, _ = C.rasterize_gaussians(
             st.bg, lv.means3D, None, lv.opacities, lv.scales, lv.rotations, st.scale_modifier, None,
@@ -98,11 +101,19 @@ class _CudaBackend:
             cam.image_width, lv.shs, st.sh_degree, cam.camera_center, False, False, status_stream=status_stream)
         if on_forward is not None:
             on_forward(color)
+        accum = None
+        if stats is not None:
+            accum, denom, max_radii = stats
+            fwd_done = torch.cuda.Event(); fwd_done.record(torch.cuda.current_stream(radii.device))
+            status_stream.wait_event(fwd_done)
+            with torch.cuda.stream(status_stream):
+                C.densify_stats_visible(radii, denom.view(-1), max_radii)
+            accum = accum.view(-1)
         C.rasterize_gaussians_backward_packed(
             st.bg, lv.means3D, radii, lv.scales, lv.rotations, st.scale_modifier, cam.world_view_transform,
             cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, st.sh_degree, cam.camera_center, geom, R,
             binning, img, lv.opacities, rows_ptr, count_ptr, cam.image_height, cam.image_width, dL_dmeans2D=dmeans2D,
-            clean_scratch=clean_scratch)
+            clean_scratch=clean_scratch, xyz_gradient_accum=accum)
         return color, radii, img
 
 
@@ -271,7 +282,6 @@ class ViewParallelStep:
         if self._side is None:
             self._side = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev))
         comm, side = self._side
-        campos = torch.stack([c.camera_center.to(dev).float() for c in cams]).contiguous()
         # Dense gradients (the rows are ADDED into them at the end of the step).  They belong to the stepper and live
         # from step to step: zero everywhere except the rows the last step's accumulate calls wrote, and exactly those
         # rows are cleared again (b200splat_clear_accumulated, by the marks the accumulate calls leave) instead of all 0.85 GB
@@ -301,14 +311,11 @@ class ViewParallelStep:
             buf = self._local_rows
             my = buf.data_ptr()
         base = [my + 4 * k * stride for k in range(nv)]
-        # header of every view: word 0 = row count (written by the backward), words 4..6 = its camera centre, which is
-        # how the peers learn it (b200splat_accumulate_packed with campos = NULL): no collective anywhere in the step
-        buf.view(nv, stride)[:, 4:7].copy_(campos)
+        # header of every view: word 0 = row count, words 4..6 = its camera centre, both written by the backward: that is
+        # how the peers learn them (b200splat_accumulate_packed with campos = NULL), no collective anywhere in the step
         color = None
         held = []
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
-            dmeans2D = torch.empty(P, 3, dtype=torch.float32, device=dev)
-
             def after_forward(img):
                 if on_forward is not None:
                     on_forward(img)
@@ -316,16 +323,13 @@ class ViewParallelStep:
             # dropped while a call is in flight so that an exception cannot leave a dirty one behind
             scratch = self._clean_scratch if self._clean_scratch is not None else C.clean_backward_scratch(P, dev)
             self._clean_scratch = None
-            color, radii, img = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], dmeans2D, after_forward,
-                                                       clean_scratch=scratch, status_stream=side)
+            # the densification statistics of the view are updated on the way (the radii part on the side stream, the
+            # gradient norms inside the per-Gaussian backward): no dense dL/dmeans2D, no separate pass over P at the end
+            color, radii, img = be.view_fwd_bwd_packed(cam, dL, lv, base[k] + 64, base[k], None, after_forward,
+                                                       clean_scratch=scratch, status_stream=side,
+                                                       stats=(self.xyz_gradient_accum, self.denom, self.max_radii2D))
             self._clean_scratch = scratch
-            # the densification statistics of the view (one pass over P, ~0.03 ms) leave the critical path: side stream,
-            # joined at the end of the step; `held` keeps their inputs alive until then
-            bwd_done = torch.cuda.Event(); bwd_done.record(main)
-            side.wait_event(bwd_done)
-            with torch.cuda.stream(side):
-                self._accumulate_stats(dmeans2D, radii)
-            held.append((dmeans2D, radii, img))      # (img: its status words are read on the side stream)
+            held.append((radii, img))                # read on the side stream (radii: statistics, img: its status words)
             self.last_radii = radii
         main.wait_event(box["cleared"])
         # this rank's own rows go in first, before the barrier (i.e. while the slower peers are still rendering):
@@ -344,8 +348,8 @@ class ViewParallelStep:
                 hi = min(lo + 16, len(bases))
                 C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], None, M, self.sh_degree, dsh, geom, marks=marks)
             pk["hd"].barrier(channel=1)                 # every rank has read them: the next step may overwrite
-        stats_done = torch.cuda.Event(); stats_done.record(side)
-        main.wait_event(stats_done)
+        side_done = torch.cuda.Event(); side_done.record(side)
+        main.wait_event(side_done)
         del held
         # the geometry gradients are strided views of the interleaved [P,12] rows
         self.leaves.rotations.grad = geom[:, 0:4]
@@ -644,16 +648,17 @@ class GraphedStep:
         cur.wait_stream(s)
         torch.cuda.synchronize(dev)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+        # captured on a HIGH-priority stream: the kernels of the step's main chain keep that priority in the graph, the side
+        # stream's background work (sparse clear of the dense gradients, radii statistics) fills in around them
+        cap = torch.cuda.Stream(device=dev, priority=-1)
+        with torch.cuda.graph(self.graph, stream=cap, capture_error_mode="thread_local"):
             self.color = st.step(self.cams, self.dL_buf)
         st._auto = auto
 
     def load(self, cams, dL_images=None):
         """Copy a step's cameras (and, if given, upstream gradients) into the static inputs; stream-ordered."""
-        for b, c in zip(self.cam_buf, cams):
-            b[:16].copy_(c.world_view_transform.reshape(-1), non_blocking=True)
-            b[16:32].copy_(c.full_proj_transform.reshape(-1), non_blocking=True)
-            b[32:35].copy_(c.camera_center.reshape(-1), non_blocking=True)
+        for b, c in zip(self.cam_buf, cams):       # one kernel per camera, not three copy-engine round trips
+            torch.cat([c.world_view_transform.reshape(-1), c.full_proj_transform.reshape(-1), c.camera_center.reshape(-1)], out=b)
         if dL_images is not None:
             for b, d in zip(self.dL_buf, dL_images):
                 if b.data_ptr() != d.data_ptr():

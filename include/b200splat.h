@@ -281,14 +281,20 @@ B200SPLAT_API int b200splat_backward_packed(const b200splat_view* view, const b2
  * again -- the per-Gaussian backward re-zeroes exactly the accumulator rows it consumed, the compaction the flags it
  * read -- so the next call needs no clear: the 150 MB memset in front of the render backward (3 M Gaussians) is gone.
  * If the call returns an error the scratch must be zero-filled by the caller before it is used again.  One scratch per
- * stream: calls that may overlap on the device need their own. */
+ * stream: calls that may overlap on the device need their own.
+ * packed_count must point at the 64-byte header b200splat_accumulate_packed reads with campos = NULL: the call writes
+ * the row count to word 0 and the view's camera centre to words 4..6.
+ * xyz_gradient_accum != NULL: the per-Gaussian backward also adds ||dL/dmean2D[i]|| of every Gaussian it visits into
+ * xyz_gradient_accum[i] -- the gradient-norm line of b200splat_densify_stats (a Gaussian it does not visit has a zero
+ * gradient); together with b200splat_densify_stats_visible after the forward that is the whole statistics update, and
+ * dL_dmeans2D can be NULL (no dense [P,3] output to clear and write). */
 B200SPLAT_API size_t b200splat_backward_scratch_bytes(int32_t P);
 B200SPLAT_API int b200splat_backward_packed_clean(const b200splat_view* view, const b200splat_gaussians* g,
                        const int32_t* radii, const void* geom, const void* binning, const void* image,
                        int32_t num_rendered, const float* dL_dout_color,
-                       const float* dL_dout_invdepth /* [1,H,W] or NULL */, float* dL_dmeans2D,
-                       float* packed_rows, uint32_t* packed_count, void* scratch, size_t scratch_bytes,
-                       b200splat_stage_times* times /* nullable */, void* stream);
+                       const float* dL_dout_invdepth /* [1,H,W] or NULL */, float* dL_dmeans2D /* nullable */,
+                       float* xyz_gradient_accum /* [P] or NULL */, float* packed_rows, uint32_t* packed_count,
+                       void* scratch, size_t scratch_bytes, b200splat_stage_times* times /* nullable */, void* stream);
 B200SPLAT_API int b200splat_accumulate_packed(int32_t P, int32_t M, int32_t sh_degree, const float* means3D,
                        int32_t n_src, const float* const* rows, const uint32_t* const* counts,
                        const float* campos, float* dL_dsh, float* dL_dgeom, uint8_t* marks /* [P] or NULL */,
@@ -310,6 +316,11 @@ B200SPLAT_API int b200splat_clear_accumulated(int32_t P, int32_t M, float* dL_ds
  * All arrays are device pointers of P (dL_dmeans2D: [P,3]) elements. */
 B200SPLAT_API int b200splat_densify_stats(int32_t P, const float* dL_dmeans2D, const int32_t* radii,
                            float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
+
+/* The lines of b200splat_densify_stats that need the forward's radii only: denom[i] += 1 and
+ * max_radii2D[i] = max(max_radii2D[i], radii[i]) for radii[i] > 0.  Can run as soon as the forward has been queued. */
+B200SPLAT_API int b200splat_densify_stats_visible(int32_t P, const int32_t* radii, float* denom, float* max_radii2D,
+                           void* stream);
 
 /* Inspection: workload counters of the render stage of the view whose forward state is given, written
  * to out16 (device, 16 x u64): [0..8] (tile, Gaussian) pairs by number of 8x4-pixel sub-blocks the splat's
