@@ -875,18 +875,49 @@ __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P
     unsigned max_cnt = min(my_cnt, (unsigned)P);
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) max_cnt = max(max_cnt, __shfl_xor_sync(0xffffffffu, max_cnt, d));
-    for (unsigned e0 = (unsigned)warp * 32u; e0 < max_cnt; e0 += (unsigned)n_warps * 32u) {
-        for (int v = 0; v < src.n; v++) {
+    // The (batch, source) items of this warp in order; the 64-byte rows of the NEXT item are fetched before the
+    // reductions of the current one are issued, so that their latency -- an NVLink round trip when the rows are a
+    // peer's -- is hidden behind them (the kernel is latency-bound: 16-24 warps per SM).
+    const unsigned stride = (unsigned)n_warps * 32u;
+    auto advance = [&](unsigned& e0, int& v) -> bool {       // next item with rows in it; false: none left
+        for (;;) {
+            if (++v >= src.n) { v = 0; e0 += stride; }
+            if (e0 >= max_cnt) return false;
+            if (e0 < min(__shfl_sync(0xffffffffu, my_cnt, v), (unsigned)P)) return true;
+        }
+    };
+    // The 32 rows of an item are one contiguous 2 KB run: fetched as four fully coalesced 512-byte accesses (chunk t of
+    // the run = 16-byte words 32 t .. 32 t + 31), not as one 64-byte row per lane -- over NVLink every 32-byte sector
+    // would otherwise be requested twice.  The rows are transposed through shared memory when the item is consumed.
+    auto fetch = [&](unsigned e0, int v, float4& c0, float4& c1, float4& c2, float4& c3) {
+        const unsigned cnt = min(__shfl_sync(0xffffffffu, my_cnt, v), (unsigned)P);
+        const unsigned n16 = 4u * min(32u, cnt - e0);                 // 16-byte words in the run
+        const float4* run = reinterpret_cast<const float4*>(src.rows[v]) + 4 * (size_t)e0;
+        if ((unsigned)lane < n16) c0 = run[lane];
+        if ((unsigned)lane + 32u < n16) c1 = run[lane + 32];
+        if ((unsigned)lane + 64u < n16) c2 = run[lane + 64];
+        if ((unsigned)lane + 96u < n16) c3 = run[lane + 96];
+    };
+    unsigned e0 = (unsigned)warp * 32u - stride;             // advance() steps onto the first item
+    int v = src.n - 1;
+    bool have = advance(e0, v);
+    float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0, q2 = q0, q3 = q0;
+    if (have) fetch(e0, v, q0, q1, q2, q3);
+    while (have) {
+        {
             const unsigned cnt = min(__shfl_sync(0xffffffffu, my_cnt, v), (unsigned)P);
-            if (e0 >= cnt) continue;
             const float cx = __ldg(campos + 3 * v), cy = __ldg(campos + 3 * v + 1), cz = __ldg(campos + 3 * v + 2);
-            const float4* rows = reinterpret_cast<const float4*>(src.rows[v]);
             const unsigned e = e0 + lane;
             const int nrow = (int)min(32u, cnt - e0);
             __syncwarp();
+            {   // transpose: chunks -> the staging area (free until the products are written) -> this lane's row
+                float4* raw = s_row4[wib];
+                raw[lane] = q0; raw[lane + 32] = q1; raw[lane + 64] = q2; raw[lane + 96] = q3;
+                __syncwarp();
+                q0 = raw[4 * lane]; q1 = raw[4 * lane + 1]; q2 = raw[4 * lane + 2]; q3 = raw[4 * lane + 3];
+                __syncwarp();
+            }
             if (e < cnt) {
-                const float4 q0 = rows[4 * (size_t)e], q1 = rows[4 * (size_t)e + 1], q2 = rows[4 * (size_t)e + 2],
-                             q3 = rows[4 * (size_t)e + 3];
                 unsigned idx = __float_as_uint(q0.x);
                 const bool ok = idx < (unsigned)P;       // always true for a well-formed row
                 if (!ok) idx = 0;
@@ -913,6 +944,12 @@ __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P
                         if (4 * q < M3) dstrow[q] = make_float4(pr[4 * q], pr[4 * q + 1], pr[4 * q + 2], pr[4 * q + 3]);
                 }
             }
+            // next item's rows on their way while this item's reductions are issued
+            unsigned ne0 = e0;
+            int nv = v;
+            const bool nhave = advance(ne0, nv);
+            float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0, n3 = n0;
+            if (nhave) fetch(ne0, nv, n0, n1, n2, n3);
             __syncwarp();
             for (int r = 0; r < nrow; r++) {
                 const unsigned tag = s_idx[wib][r];
@@ -936,6 +973,8 @@ __global__ void __launch_bounds__(ACC_WARPS * 32) accumulate_packed_kernel(int P
                     for (int el = lane; el < M3 && el < 48; el += 32) atomicAdd(drow + el, srow[el]);
                 }
             }
+            q0 = n0; q1 = n1; q2 = n2; q3 = n3;
+            e0 = ne0; v = nv; have = nhave;
         }
     }
 }

@@ -563,14 +563,17 @@ class ViewParallelStep:
 
     # -- measurement helpers (CUDA path only) ------------------------------------------------------------
     def launches_per_view(self=None) -> int:
-        """Kernels of THIS library launched per view fwd+bwd (memsets are driver work and are not counted): preprocess 1;
-        depth order 3 radix passes x (count, column scan, scatter) = 9; offsets scan 3; duplicateWithKeys 1; tile sort
-        2 passes x 3 = 6; tile order 1; render forward 1; render backward, compaction of the touched Gaussians,
-        per-Gaussian backward 3; densification statistics 1 -- plus, in the packed exchange, the count gather +
-        accumulate kernels for the rank's own rows and for its peers'."""
-        n = 1 + 9 + 3 + 1 + 6 + 1 + 1 + 3 + 1
+        """Kernels of THIS library launched per view fwd+bwd (memset / copy nodes are driver work and are not counted):
+        preprocess 1; depth order 4 radix passes x (count, column scan, scatter) = 12, offsets spine 1; duplicateWithKeys 1;
+        tile sort 2 passes x 3 = 6; tile order 1; render forward 1; render backward, compaction of the touched Gaussians,
+        per-Gaussian backward 3.  Dense step: + background zero-fill of the gradient outputs 1, densification statistics 1.
+        Packed step: + radii statistics 1, sparse clear of the dense gradients 1, count gather + accumulate 2 for the
+        rank's own rows and 2 more for its peers'."""
+        n = 1 + 12 + 1 + 1 + 6 + 1 + 1 + 3
         if self is not None and getattr(self, "exchange", None) == "packed":
-            n += 2 + (2 if self.world_size > 1 else 0)
+            n += 1 + 1 + 2 + (2 if self.world_size > 1 else 0)
+        else:
+            n += 2
         return n
 
     def stage_profile(self, cam, dL, iters: int = 5):
