@@ -301,10 +301,17 @@ class ViewParallelStep:
             C.clear_accumulated(dsh, geom, marks)
             box["cleared"] = torch.cuda.Event(); box["cleared"].record(side)
         stride = 16 * P + 16                                           # words per view: 64-byte header + P rows
+        rows_free = None
         if G > 1:
             pk = self._setup_packed(P, nv, dev)
             my = pk["ptrs"][dist.get_rank(self.group)]
             buf = pk["buf"]
+            # every rank has read the rows of the previous step (it is past its accumulate calls): they may be overwritten.
+            # On the communication stream, beside the forward; the first backward of this step waits for it.
+            comm.wait_event(step_start)
+            with torch.cuda.stream(comm):
+                pk["hd"].barrier(channel=1)
+                rows_free = torch.cuda.Event(); rows_free.record(comm)
         else:
             if self._local_rows is None or self._local_rows.numel() != nv * stride:
                 self._local_rows = torch.zeros(nv * stride, dtype=torch.float32, device=dev)
@@ -316,9 +323,11 @@ class ViewParallelStep:
         color = None
         held = []
         for k, (cam, dL) in enumerate(zip(cams, dL_images)):
-            def after_forward(img):
+            def after_forward(img, first=(k == 0)):
                 if on_forward is not None:
                     on_forward(img)
+                if first and rows_free is not None:
+                    main.wait_event(rows_free)           # the first backward of the step overwrites this rank's rows
             # the backward's scratch lives as long as the stepper and stays clean from call to call (no per-view clear);
             # dropped while a call is in flight so that an exception cannot leave a dirty one behind
             scratch = self._clean_scratch if self._clean_scratch is not None else C.clean_backward_scratch(P, dev)
@@ -347,7 +356,8 @@ class ViewParallelStep:
             for lo in range(0, len(bases), 16):         # B200SPLAT_MAX_VIEWS sources per launch
                 hi = min(lo + 16, len(bases))
                 C.accumulate_packed(lv.means3D, [b + 64 for b in bases[lo:hi]], bases[lo:hi], None, M, self.sh_degree, dsh, geom, marks=marks)
-            pk["hd"].barrier(channel=1)                 # every rank has read them: the next step may overwrite
+            # (the barrier that lets the ranks overwrite their rows again sits at the START of the next step, beside
+            # its forward: see `rows_free` above)
         side_done = torch.cuda.Event(); side_done.record(side)
         main.wait_event(side_done)
         del held
