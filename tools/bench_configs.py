@@ -24,18 +24,22 @@ def sweep():
         sc = synth.make_scene(P, D, seed=0, preset=PRESET).to(dev)
         cams = [synth.make_camera(W, H, yaw=2.0 * np.pi * k / 8).to(dev) for k in range(8)]
         dL = synth.make_grad_image(W, H).to(dev)
-        st = vp.ViewParallelStep(vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations), D, torch.zeros(3, device=dev))
+        st = vp.ViewParallelStep(vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations), D, torch.zeros(3, device=dev),
+                                 exchange="packed")
         stages, stats = st.stage_profile(cams[0], dL, iters=5)
-        for k in range(4):
-            st.step([cams[k % 8]], [dL])
+        C.reset_capacity_policy()
+        g = vp.GraphedStep(st, [cams[0]], [dL])          # the step bench.py times: packed rows, one graph replay per view
+        for k in range(8):                               # every view of the orbit once: the capacity policy sees the largest R
+            g.step([cams[k % 8]], [dL])
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for k in range(24):
-            st.step([cams[k % 8]], [dL])
+            g.step([cams[k % 8]], [dL])
         e1.record(); torch.cuda.synchronize()
+        del g
         binning = sum(stages.get(k, 0.0) for k in ("scan", "duplicate", "sort", "ranges"))
-        print(json.dumps({"config": "densification sweep 1600x1060 SH3 fwd+bwd, 8-camera orbit", "preset": PRESET, "gaussians": P,
+        print(json.dumps({"config": "densification sweep 1600x1060 SH3 fwd+bwd, 8-camera orbit", "preset": PRESET, "step": "packed rows, CUDA-graph replay", "gaussians": P,
                           "visible": stats["visible"], "R": stats["R"], "touched": stats.get("touched"),
                           "ms_per_view": round(e0.elapsed_time(e1) / 24, 4),
                           "stages_ms": {"preprocess": round(stages.get("preprocess", 0.0), 4), "key_sort(scan+duplicate+sort+ranges)": round(binning, 4),

@@ -19,7 +19,7 @@ def main():
     sc = synth.make_scene(P, D, seed=0).to(dev)
     cams = [synth.make_camera(W, H, yaw=2.0 * np.pi * k / 8).to(dev) for k in range(8)]
     dL = synth.make_grad_image(W, H).to(dev)
-    st = vp.ViewParallelStep(vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations), D, torch.zeros(3, device=dev))
+    st = vp.ViewParallelStep(vp.GaussianParams(sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations), D, torch.zeros(3, device=dev), exchange="packed")     # the step bench.py times
     for i in range(views):
         st.step([cams[i % 8]], [dL])
     torch.cuda.synchronize()
