@@ -588,11 +588,16 @@ class ViewParallelStep:
 
     def stage_profile(self, cam, dL, iters: int = 5):
         """Per-stage device milliseconds (CUDA events on the launch stream, inside the library) averaged
-        over `iters` fwd+bwd passes, plus workload statistics."""
+        over `iters` fwd+bwd passes, plus workload statistics.  The timed passes run the backward the packed step runs
+        (64-byte rows out, clean scratch: no clear in front of the render backward, no dense outputs cleared beside
+        it); the warm-up pass runs the dense backward, from which the number of touched Gaussians is read."""
         import diff_gaussian_rasterization as dgr
         C = dgr._C
         lv = GaussianParams(*[t.detach() for t in self.leaves])
+        P = lv.means3D.shape[0]
         acc, stats = {}, {}
+        scratch = C.clean_backward_scratch(P, lv.means3D.device)
+        rows = torch.zeros(16 * P + 16, dtype=torch.float32, device=lv.means3D.device)
         cap = None          # first pass: exact (waits for R); timed passes: that R with head room, no host wait
         for it in range(iters + 1):
             st = C.StageTimes()
@@ -604,6 +609,15 @@ class ViewParallelStep:
             if cap is None:
                 cap = max(1, int(1.25 * res[0]) + 65536)
             R, color, radii, geom, binning, img, _ = res
+            if it > 0:
+                C.rasterize_gaussians_backward_packed(
+                    self.bg, lv.means3D, radii, lv.scales, lv.rotations, self.scale_modifier, cam.world_view_transform,
+                    cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, self.sh_degree, cam.camera_center, geom, R,
+                    binning, img, lv.opacities, rows.data_ptr() + 64, rows.data_ptr(), cam.image_height, cam.image_width,
+                    stage_times=st, clean_scratch=scratch)
+                for k, v in st.as_dict().items():
+                    acc[k[:-3]] = acc.get(k[:-3], 0.0) + v / iters
+                continue
             g = C.rasterize_gaussians_backward(self.bg, lv.means3D, radii, None, lv.scales, lv.rotations,
                                            self.scale_modifier, None, cam.world_view_transform,
                                            cam.full_proj_transform, cam.tanfovx, cam.tanfovy, dL, lv.shs, self.sh_degree,
@@ -613,9 +627,6 @@ class ViewParallelStep:
                 stats = {"visible": int((radii > 0).sum().item()), "R": C.forward_status(img, cam.image_height, cam.image_width)[0],
                          "touched": int((g[3].abs().sum(dim=1) > 0).sum().item())}
                 stats.update(C.render_stats(lv.means3D.shape[0], cam.image_width, cam.image_height, R, geom, binning, img))
-                continue   # first pass is warm-up
-            for k, v in st.as_dict().items():
-                acc[k[:-3]] = acc.get(k[:-3], 0.0) + v / iters
         return acc, stats
 
 
