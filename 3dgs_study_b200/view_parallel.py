@@ -631,7 +631,7 @@ class ViewParallelStep:
 
 
 class GraphedStep:
-    """One whole step of a ViewParallelStep -- forward, backward, exchange, statistics: some 35 kernel launches and a
+    """One whole step of a ViewParallelStep -- forward, backward, exchange, statistics: some 30 kernel launches and a
     dozen tensor operations per view -- captured ONCE in a CUDA graph and replayed with one launch per step.
 
     The step is launch-latency sensitive: at 2 ms per view the Python thread has to queue a kernel every 50 us, and on
